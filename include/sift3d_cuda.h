@@ -1,0 +1,136 @@
+/* sift3d_cuda.h -- the thin C ABI between the host C library (libsift3D.so, the
+ * drop-in for the reference's public API) and the CUDA layer (libsift3d_cuda.so,
+ * hand-written sm_100a kernels). Plain C types only: no CUDA, C++ or torch types
+ * cross this boundary. Every function returns 0 on success and -1 on failure
+ * (the reference's SIFT3D_SUCCESS / SIFT3D_FAILURE, imtypes.h:21-25) and reports
+ * the reason on stderr, like the reference's SIFT3D_ERR (immacros.h:27-32).
+ *
+ * What each entry point replaces in the reference (paths under /root/reference):
+ *
+ *   sift3d_cuda_plan            resize_SIFT3D sift3d/sift.c:427-475, resize_Pyramid
+ *                               sift3d/imutil.c:1464-1554 (allocation of all levels)
+ *   sift3d_cuda_detect          set_im_SIFT3D sift.c:629-659 (im_scale imutil.c:699),
+ *                               build_gpyr sift.c:662-711 (apply_Sep_FIR_filter
+ *                               imutil.c:1127-1206, im_downsample_2x imutil.c:591),
+ *                               build_dog sift.c:713-732, detect_extrema sift.c:735-871,
+ *                               assign_orientations sift.c:1109-1167 (per-candidate
+ *                               part; the in-order compaction stays in host C)
+ *   sift3d_cuda_describe        do_extract_descriptors sift.c:1561-1596 /
+ *                               extract_descrip sift.c:1442-1536
+ *   sift3d_cuda_blur            apply_Sep_FIR_filter imutil.c:1127-1206 (one blur;
+ *                               exposed for parity tests)
+ *
+ * There is NO CPU fallback behind this interface: if no CUDA device is usable
+ * sift3d_cuda_ctx_create() returns NULL and every caller fails loudly.
+ */
+#ifndef SIFT3D_CUDA_H
+#define SIFT3D_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SIFT3D_CUDA_EXPORT __attribute__((visibility("default")))
+
+#define SIFT3D_CUDA_MAX_FILTERS 16  /* incremental filters per octave (num_kp_levels + 2) */
+#define SIFT3D_CUDA_MAX_OCTAVES 24
+#define SIFT3D_CUDA_MAX_TAPS 129    /* 2 * half_width + 1 */
+#define SIFT3D_CUDA_DESC_NUMEL 768  /* 4*4*4 histograms x 12 icosahedron vertices */
+
+typedef struct sift3d_cuda_ctx sift3d_cuda_ctx;
+
+/* One separable FIR filter (imtypes_private.h:84-95). */
+typedef struct {
+    int width;                          /* 2*half_width + 1 */
+    float taps[SIFT3D_CUDA_MAX_TAPS];   /* normalised, as init_Gauss_filter computes them */
+} sift3d_cuda_filter;
+
+/* Geometry + filters of one pyramid; filled by host C (sift3d_host.c) with the
+ * reference's expressions so that every double->float conversion happens on the
+ * host exactly as in the reference. */
+typedef struct {
+    int nx, ny, nz;                 /* octave-0 dims */
+    double units[3];                /* voxel units the pyramid was (re)sized with;
+                                       octave o >= 1 uses units * 2^o (imutil.c:1545-1548) */
+    int num_octaves;                /* sift.c:442-454 */
+    int num_kp_levels;              /* gpyr has num_kp_levels + 3 levels, s = -1 .. kp+1 */
+    double scales[SIFT3D_CUDA_MAX_OCTAVES][SIFT3D_CUDA_MAX_FILTERS + 1];
+                                    /* [o][i]: scale of level s = -1 + i of octave o,
+                                       sigma0 * pow(2, o + s/num_kp_levels) (imutil.c:1578-1579) */
+    sift3d_cuda_filter first;       /* sigma_n -> scale(-1) (imutil.c:1392-1396) */
+    sift3d_cuda_filter octave[SIFT3D_CUDA_MAX_FILTERS]; /* [i]: level i-1 -> level i */
+} sift3d_cuda_plan_desc;
+
+/* A keypoint / candidate as it crosses the ABI (imtypes_private.h:159-166). */
+typedef struct {
+    int32_t o, s;
+    double x, y, z;     /* octave-local voxel coordinates (integers, sift.c:861-863) */
+    double sd;          /* level scale */
+    float strength;     /* |DoG| at the candidate */
+    float R[9];         /* row-major rotation matrix */
+    int32_t valid;      /* 1 = survived orientation assignment */
+} sift3d_cuda_keypoint;
+
+/* Per-stage device times of the last detect/describe call, in milliseconds
+ * (CUDA events on the context's stream). */
+typedef struct {
+    float h2d, scale, pyramid, dogmax, extrema, order, orient, d2h, total_detect;
+    float desc_h2d, descriptors, desc_d2h, total_describe;
+} sift3d_cuda_timings;
+
+SIFT3D_CUDA_EXPORT int sift3d_cuda_device_count(void);
+
+/* device < 0: use $SIFT3D_CUDA_DEVICE or 0. NULL on failure. */
+SIFT3D_CUDA_EXPORT sift3d_cuda_ctx *sift3d_cuda_ctx_create(int device);
+SIFT3D_CUDA_EXPORT void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx);
+
+/* Pinned host memory for image buffers (so the H2D copy in detect runs at PCIe
+ * speed). Works without a context. */
+SIFT3D_CUDA_EXPORT void *sift3d_cuda_host_alloc(size_t bytes);
+SIFT3D_CUDA_EXPORT void sift3d_cuda_host_free(void *p);
+
+/* (Re)allocate the device pyramid for this geometry. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *desc);
+
+/* Run scale -> pyramid -> DoG max -> extrema -> ordering -> orientation.
+ * image: nx*ny*nz float32, x fastest; on the host unless image_on_device != 0.
+ * units: the units of THIS image (octave 0 uses them; octaves >= 1 use the plan's,
+ * mirroring sift.c:651-656). Results stay on the device until fetched. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image,
+                                          int image_on_device, const double units[3],
+                                          double peak_thresh, double corner_thresh,
+                                          int *num_candidates);
+
+/* All candidates in the reference's scan order (o, s, z, y, x), each with its
+ * orientation result (valid flag + R). out has room for max entries. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_fetch_candidates(sift3d_cuda_ctx *ctx,
+                                                    sift3d_cuda_keypoint *out, int max);
+
+/* Descriptors for num keypoints on the pyramid left by the last detect.
+ * desc: num * 768 float32 on the host (or device if desc_on_device). */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_describe(sift3d_cuda_ctx *ctx,
+                                            const sift3d_cuda_keypoint *keys, int num,
+                                            float *desc, int desc_on_device);
+
+/* Test / inspection hooks. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_level_info(sift3d_cuda_ctx *ctx, int o, int s, int dims[3],
+                                              double units[3], double *scale);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_fetch_level(sift3d_cuda_ctx *ctx, int o, int s, float *host_out);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_dogmax(sift3d_cuda_ctx *ctx, int o, int s, float *out);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_blur(sift3d_cuda_ctx *ctx, const float *host_src,
+                                        float *host_dst, int nx, int ny, int nz,
+                                        const double units[3], const sift3d_cuda_filter *f,
+                                        int force_generic);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_get_timings(sift3d_cuda_ctx *ctx, sift3d_cuda_timings *t);
+/* Number of kernel launches issued by this context since creation. */
+SIFT3D_CUDA_EXPORT uint64_t sift3d_cuda_launch_count(sift3d_cuda_ctx *ctx);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_synchronize(sift3d_cuda_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* SIFT3D_CUDA_H */

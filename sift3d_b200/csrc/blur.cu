@@ -1,0 +1,218 @@
+// blur.cu -- Gaussian scale-space blur, 2x decimation and the max-abs reductions.
+//
+// Reference semantics (paths under /root/reference/sift3d):
+//   apply_Sep_FIR_filter  imutil.c:1127-1206   x pass, then y, then z, fp32 between passes
+//   convolve_sep_gen      imutil.c:742-861     taps spaced unit/units[dim] voxels apart,
+//                                              sampled by linear interpolation; interior
+//                                              [uhw, n-2-uhw] without bounds logic, elsewhere
+//                                              mirror-left / mirror-minus-0.1-right
+//   im_downsample_2x      imutil.c:591-617     dst[x,y,z] = src[2x,2y,2z]
+//   im_max_abs / im_scale imutil.c:681-713     max |v|, then v /= max (true division)
+//   im_subtract           imutil.c:719-739     DoG = G(s) - G(s+1) (never materialised here)
+//
+// Bit parity: the reference build (x86-64, no -mfma) rounds every multiply and every add
+// to fp32 separately and accumulates taps in ascending d. All arithmetic below uses
+// __fmul_rn/__fadd_rn/__fsub_rn/__fdiv_rn so nvcc can never contract it into FMAs.
+#include "common.cuh"
+
+namespace s3d {
+
+// ---------------------------------------------------------------------------------------
+// Literal per-tap sampling (SAMP_AND_ACC, imutil.c:779-796).
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ float samp(const float *__restrict__ line, size_t stride, float c,
+                                      int n, bool scale, float dv) {
+    int lo = (int) c;  // truncation toward zero, as the C cast
+    const float fr = __fsub_rn(c, (float) lo);
+    // Only reachable with lo outside [0, n-2] where the reference itself reads out of
+    // bounds (single mirror on lines shorter than the kernel); keep the access legal.
+    lo = max(0, min(lo, n - 2));
+    float a = line[(size_t) lo * stride];
+    float b = line[(size_t) (lo + 1) * stride];
+    if (scale) {
+        a = __fdiv_rn(a, dv);
+        b = __fdiv_rn(b, dv);
+    }
+    return __fadd_rn(__fmul_rn(__fsub_rn(1.0f, fr), a), __fmul_rn(fr, b));
+}
+
+// One output sample of convolve_sep_gen along a line (imutil.c:798-856).
+__device__ __forceinline__ float conv_point_generic(const float *__restrict__ line,
+                                                    size_t stride, int p, int n,
+                                                    const float *__restrict__ taps, int hw,
+                                                    float uf, int uhw, bool scale, float dv) {
+    const int start = uhw;
+    const int end = n - 2 - uhw;
+    const int dim_end = n - 1;
+    float acc = 0.0f;
+    if (p >= start && p <= end) {
+        // interior pass: the coordinate is carried across taps (imutil.c:803-818)
+        float c = (float) p;
+        for (int d = -hw; d <= hw; d++) {
+            const float tap = taps[d + hw];
+            const float step = __fmul_rn((float) d, uf);
+            c = __fsub_rn(c, step);
+            acc = __fadd_rn(acc, __fmul_rn(tap, samp(line, stride, c, n, scale, dv)));
+            c = __fadd_rn(c, step);
+        }
+    } else {
+        // boundary pass (imutil.c:833-854)
+        for (int d = -hw; d <= hw; d++) {
+            const float tap = taps[d + hw];
+            const float step = __fmul_rn((float) d, uf);
+            float c = __fsub_rn((float) p, step);
+            if ((int) c < 0) {
+                c = -c;
+            } else if ((int) c >= dim_end) {
+                c = __fsub_rn(__fsub_rn(__fmul_rn(2.0f, (float) dim_end), c), 0.1f);
+            }
+            acc = __fadd_rn(acc, __fmul_rn(tap, samp(line, stride, c, n, scale, dv)));
+        }
+    }
+    return acc;
+}
+
+template <int AXIS>
+__global__ void __launch_bounds__(256)
+blur_axis_generic_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny,
+                         int nz, const float *__restrict__ taps, int hw, float uf, int uhw,
+                         const float *__restrict__ divisor) {
+    const size_t total = (size_t) nx * ny * nz;
+    const size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int x = (int) (idx % nx);
+    const int y = (int) ((idx / nx) % ny);
+    const int z = (int) (idx / ((size_t) nx * ny));
+    const int p = AXIS == 0 ? x : (AXIS == 1 ? y : z);
+    const int n = AXIS == 0 ? nx : (AXIS == 1 ? ny : nz);
+    const size_t stride = AXIS == 0 ? 1 : (AXIS == 1 ? (size_t) nx : (size_t) nx * ny);
+    float dv = 0.0f;
+    if (divisor != nullptr) dv = *divisor;
+    const bool scale = dv != 0.0f;  // im_scale leaves an all-zero image alone (imutil.c:706)
+    dst[idx] = conv_point_generic(src + (idx - (size_t) p * stride), stride, p, n, taps, hw, uf,
+                                  uhw, scale, dv);
+}
+
+// ---------------------------------------------------------------------------------------
+// 2x decimation (imutil.c:597-613)
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+downsample_kernel(const float *__restrict__ src, float *__restrict__ dst, int snx, int sny,
+                  int dnx, int dny, int dnz) {
+    const size_t total = (size_t) dnx * dny * dnz;
+    const size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int x = (int) (idx % dnx);
+    const int y = (int) ((idx / dnx) % dny);
+    const int z = (int) (idx / ((size_t) dnx * dny));
+    dst[idx] = src[((size_t) (2 * z) * sny + (size_t) (2 * y)) * snx + (size_t) (2 * x)];
+}
+
+// ---------------------------------------------------------------------------------------
+// max |v| and max |a - b| (imutil.c:681-695, sift.c:822-826). Non-negative floats order
+// like their bit patterns, so the cross-block reduction is an integer atomicMax.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void block_atomic_max(float m, float *out) {
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    __shared__ float wmax[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) wmax[warp] = m;
+    __syncthreads();
+    if (warp == 0) {
+        m = lane < (int) (blockDim.x >> 5) ? wmax[lane] : 0.0f;
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) atomicMax(reinterpret_cast<int *>(out), __float_as_int(m));
+    }
+}
+
+__global__ void __launch_bounds__(256)
+absmax_kernel(const float *__restrict__ a, size_t n, float *__restrict__ out) {
+    float m = 0.0f;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        m = fmaxf(m, fabsf(a[i]));
+    block_atomic_max(m, out);
+}
+
+__global__ void __launch_bounds__(256)
+absdiffmax_kernel(const float *__restrict__ a, const float *__restrict__ b, size_t n,
+                  float *__restrict__ out) {
+    float m = 0.0f;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        m = fmaxf(m, fabsf(__fsub_rn(a[i], b[i])));
+    block_atomic_max(m, out);
+}
+
+// ---------------------------------------------------------------------------------------
+// Launchers
+// ---------------------------------------------------------------------------------------
+static inline AxisSpec axis_spec(int n, double unit, int hw) {
+    AxisSpec a;
+    a.n = n;
+    a.uf = (float) (1.0 / unit);                 // imutil.c:754-755 (unit argument is 1.0)
+    a.uhw = (int) ceilf((float) hw * a.uf);      // imutil.c:756-757
+    return a;
+}
+
+int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, float *tmp_b,
+                int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
+                const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
+                const float *dog_prev, bool force_generic, uint64_t *launches) {
+    (void) force_generic;
+    const int hw = f.width / 2;
+    const size_t total = (size_t) nx * ny * nz;
+    const unsigned blocks = (unsigned) ((total + 255) / 256);
+    const AxisSpec ax = axis_spec(nx, units[0], hw);
+    const AxisSpec ay = axis_spec(ny, units[1], hw);
+    const AxisSpec az = axis_spec(nz, units[2], hw);
+
+    blur_axis_generic_kernel<0><<<blocks, 256, 0, st>>>(src, tmp_a, nx, ny, nz, d_taps, hw, ax.uf,
+                                                        ax.uhw, d_divisor);
+    blur_axis_generic_kernel<1><<<blocks, 256, 0, st>>>(tmp_a, tmp_b, nx, ny, nz, d_taps, hw,
+                                                        ay.uf, ay.uhw, nullptr);
+    blur_axis_generic_kernel<2><<<blocks, 256, 0, st>>>(tmp_b, dst, nx, ny, nz, d_taps, hw, az.uf,
+                                                        az.uhw, nullptr);
+    if (launches) *launches += 3;
+    if (d_dogmax_slot != nullptr && dog_prev != nullptr) {
+        if (launch_absdiffmax(st, dog_prev, dst, total, d_dogmax_slot, launches)) return -1;
+    }
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+int launch_downsample(cudaStream_t st, const float *src, float *dst, int snx, int sny, int snz,
+                      uint64_t *launches) {
+    const int dnx = snx / 2, dny = sny / 2, dnz = snz / 2;
+    const size_t total = (size_t) dnx * dny * dnz;
+    downsample_kernel<<<(unsigned) ((total + 255) / 256), 256, 0, st>>>(src, dst, snx, sny, dnx,
+                                                                       dny, dnz);
+    if (launches) *launches += 1;
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+int launch_absmax(cudaStream_t st, const float *src, size_t n, float *d_out, uint64_t *launches) {
+    S3D_CK(cudaMemsetAsync(d_out, 0, sizeof(float), st));
+    size_t blocks = (n + 256 * 8 - 1) / (256 * 8);
+    if (blocks > (size_t) kNumSMs * 8) blocks = (size_t) kNumSMs * 8;
+    if (blocks < 1) blocks = 1;
+    absmax_kernel<<<(unsigned) blocks, 256, 0, st>>>(src, n, d_out);
+    if (launches) *launches += 1;
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+int launch_absdiffmax(cudaStream_t st, const float *a, const float *b, size_t n, float *d_out,
+                      uint64_t *launches) {
+    S3D_CK(cudaMemsetAsync(d_out, 0, sizeof(float), st));
+    size_t blocks = (n + 256 * 8 - 1) / (256 * 8);
+    if (blocks > (size_t) kNumSMs * 8) blocks = (size_t) kNumSMs * 8;
+    if (blocks < 1) blocks = 1;
+    absdiffmax_kernel<<<(unsigned) blocks, 256, 0, st>>>(a, b, n, d_out);
+    if (launches) *launches += 1;
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace s3d

@@ -1,0 +1,98 @@
+// common.cuh -- shared declarations of the CUDA layer (libsift3d_cuda.so).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/sift3d_cuda.h"
+
+#define S3D_ERR(...) fprintf(stderr, __VA_ARGS__)
+
+#define S3D_CK(call)                                                               \
+    do {                                                                           \
+        cudaError_t e_ = (call);                                                   \
+        if (e_ != cudaSuccess) {                                                   \
+            S3D_ERR("sift3d_cuda: %s failed: %s (%s:%d)\n", #call,                  \
+                    cudaGetErrorString(e_), __FILE__, __LINE__);                   \
+            return -1;                                                             \
+        }                                                                          \
+    } while (0)
+
+namespace s3d {
+
+constexpr int kNumSMs = 148;  // B200
+
+// A pyramid level resident in HBM: dense float32, x fastest (immacros.h:58-59).
+struct Level {
+    float *d = nullptr;
+    int nx = 0, ny = 0, nz = 0;
+    double ux = 1, uy = 1, uz = 1;
+    double scale = 0;
+    size_t nvox() const { return (size_t) nx * ny * nz; }
+};
+
+// Taps passed by value in the kernel parameter bank (constant memory).
+constexpr int kMaxParamTaps = 33;  // half-width <= 16
+struct TapsParam {
+    float k[kMaxParamTaps];
+};
+
+// Per-axis sampling parameters of convolve_sep_gen (imutil.c:748-763).
+struct AxisSpec {
+    int n;        // samples along the axis
+    float uf;     // unit_factor = (float)(unit / units[dim])
+    int uhw;      // (int) ceilf(half_width * unit_factor)
+};
+
+// Candidate extremum as written by the extrema kernel.
+struct Cand {
+    unsigned long long key;  // s << 60 | z << 40 | y << 20 | x
+    float strength;
+    int pad;
+};
+
+// ---- kernels / launchers implemented in the .cu files -----------------------------------
+
+// blur.cu
+int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, float *tmp_b,
+                int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
+                const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
+                const float *dog_prev, bool force_generic, uint64_t *launches);
+int launch_downsample(cudaStream_t st, const float *src, float *dst, int snx, int sny, int snz,
+                      uint64_t *launches);
+int launch_absmax(cudaStream_t st, const float *src, size_t n, float *d_out, uint64_t *launches);
+int launch_absdiffmax(cudaStream_t st, const float *a, const float *b, size_t n, float *d_out,
+                      uint64_t *launches);
+
+// extrema.cu
+int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, int nx, int ny,
+                   int nz, const float *d_dogmax, double peak_thresh, Cand *d_cand, int cap,
+                   int *d_count, uint64_t *launches);
+int launch_order(cudaStream_t st, const Cand *d_in, int n, Cand *d_out, uint64_t *launches);
+
+// orient.cu
+struct OctaveInfo {  // what the per-candidate kernels need to know about one octave
+    const float *lvl[SIFT3D_CUDA_MAX_FILTERS];  // Gaussian level of keypoint level s (gpyr s)
+    double sd[SIFT3D_CUDA_MAX_FILTERS];         // level scale (imutil.c:1578-1579)
+    int o;
+    int nx, ny, nz;
+    float ux, uy, uz;  // level units narrowed to float (sift.c:88-90)
+};
+int launch_orient(cudaStream_t st, const Cand *d_cands, int n, const OctaveInfo &info,
+                  double corner_thresh, sift3d_cuda_keypoint *d_out, uint64_t *launches);
+
+// descriptor.cu
+struct DescJob {
+    const float *img;
+    int nx, ny, nz;
+    float ux, uy, uz;
+    float cx, cy, cz;
+    float sigma;         // (float)(sd * desc_sig_fctr)  (sift.c:1453)
+    float R[9];
+};
+int upload_mesh(void);
+int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, float *d_desc,
+                       uint64_t *launches);
+
+}  // namespace s3d

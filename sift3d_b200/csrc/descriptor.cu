@@ -1,0 +1,291 @@
+// descriptor.cu -- icosahedral gradient-orientation histogram descriptor, one CTA per
+// keypoint with the 4x4x4x12 histogram in shared memory.
+//
+// Reference semantics (sift3d/sift.c):
+//   init_geometry           :148-259    icosahedron; the v[0]<->v[1] swap without idx swap
+//   cart2bary               :268-327    Moller-Trumbore barycentric coordinates
+//   icos_hist_bin           :1254-1291  first face (index order) hit by the gradient ray
+//   SIFT3D_desc_acc_interp  :1295-1399  2x2x2 spatial x 3 barycentric weights
+//   normalize_desc          :1402-1429  L2 norm in double, + DBL_EPSILON
+//   extract_descrip         :1442-1536  window loop, rotate, weight, accumulate,
+//                                       normalise / clamp to 0.2*128/768 / normalise
+#include <float.h>
+#include <math.h>
+
+#include "common.cuh"
+
+namespace s3d {
+
+constexpr int kFaces = 20;
+constexpr int kVerts = 12;
+constexpr int kHistPerDim = 4;
+constexpr int kDescNumel = SIFT3D_CUDA_DESC_NUMEL;
+constexpr double kBaryEps = (double) FLT_EPSILON * 1E1;  // sift.c:40
+constexpr double kDescRadFctr = 2.0;                     // sift.c:44
+
+// Per-face constants of cart2bary that do not depend on the query vector.
+struct MeshConst {
+    float e1[kFaces][3];   // v1 - v0
+    float e2[kFaces][3];   // v2 - v0
+    float t[kFaces][3];    // -v0
+    float q[kFaces][3];    // t x e1
+    float e2q[kFaces];     // e2 . q
+    float ctr[kFaces][3];  // v0 + v1 + v2 (direction of the face centre; selection only)
+    int idx[kFaces][3];    // histogram bin of each barycentric weight
+};
+
+__constant__ MeshConst c_mesh;
+
+static inline void cross3(const float a[3], const float b[3], float o[3]) {
+    o[0] = a[1] * b[2] - a[2] * b[1];
+    o[1] = a[2] * b[0] - a[0] * b[2];
+    o[2] = a[0] * b[1] - a[1] * b[0];
+}
+static inline float dot3(const float a[3], const float b[3]) {
+    return a[0] * b[0] + a[1] * b[1] + a[2] * b[2];
+}
+
+// Build the table the way init_geometry does (host, fp32, x86-64 without FMA so every
+// operation rounds exactly as in the reference build) and upload it.
+int upload_mesh(void) {
+    const double gr = 1.6180339887;  // sift.c:48
+    const float vert[kVerts][3] = {
+        {0, 1, (float) gr},  {0, -1, (float) gr},  {0, 1, (float) -gr}, {0, -1, (float) -gr},
+        {1, (float) gr, 0},  {-1, (float) gr, 0},  {1, (float) -gr, 0}, {-1, (float) -gr, 0},
+        {(float) gr, 0, 1},  {(float) -gr, 0, 1},  {(float) gr, 0, -1}, {(float) -gr, 0, -1}};
+    const int faces[kFaces][3] = {{0, 1, 8},  {0, 8, 4},  {0, 4, 5},   {0, 5, 9},  {0, 9, 1},
+                                  {1, 6, 8},  {8, 6, 10}, {8, 10, 4},  {4, 10, 2}, {4, 2, 5},
+                                  {5, 2, 11}, {5, 11, 9}, {9, 11, 7},  {9, 7, 1},  {1, 7, 6},
+                                  {3, 6, 7},  {3, 7, 11}, {3, 11, 2},  {3, 2, 10}, {3, 10, 6}};
+    MeshConst m;
+    for (int i = 0; i < kFaces; i++) {
+        volatile float v[3][3];
+        for (int j = 0; j < 3; j++) {
+            const int id = faces[i][j];
+            m.idx[i][j] = id;
+            const float x = vert[id][0], y = vert[id][1], z = vert[id][2];
+            const float mag = sqrtf(x * x + y * y + z * z);
+            // SIFT3D_CVEC_SCALE(v + j, 1.0f / mag) expands to v.x * 1.0f / mag (sift.c:228)
+            v[j][0] = x * 1.0f / mag;
+            v[j][1] = y * 1.0f / mag;
+            v[j][2] = z * 1.0f / mag;
+        }
+        float a[3], b[3], n[3], v0[3], v1[3], v2[3];
+        for (int k = 0; k < 3; k++) { v0[k] = v[0][k]; v1[k] = v[1][k]; v2[k] = v[2][k]; }
+        for (int k = 0; k < 3; k++) { a[k] = v2[k] - v1[k]; b[k] = v1[k] - v0[k]; }
+        cross3(a, b, n);
+        if (dot3(n, v0) < 0) {  // sift.c:237-242: vertices swapped, idx left alone
+            for (int k = 0; k < 3; k++) { const float tmp = v0[k]; v0[k] = v1[k]; v1[k] = tmp; }
+        }
+        for (int k = 0; k < 3; k++) {
+            m.e1[i][k] = v1[k] - v0[k];
+            m.e2[i][k] = v2[k] - v0[k];
+            m.t[i][k] = v0[k] * -1.0f;
+            m.ctr[i][k] = v0[k] + v1[k] + v2[k];
+        }
+        cross3(m.t[i], m.e1[i], m.q[i]);
+        m.e2q[i] = dot3(m.e2[i], m.q[i]);
+    }
+    S3D_CK(cudaMemcpyToSymbol(c_mesh, &m, sizeof(m)));
+    return 0;
+}
+
+// cart2bary for face f (sift.c:268-297). Returns false if the reference would `continue`
+// past this face in icos_hist_bin (unstable, or the ray misses the triangle).
+__device__ __forceinline__ bool face_hit(int f, float gx, float gy, float gz, float &bx,
+                                         float &by, float &bz) {
+    const float e2x = c_mesh.e2[f][0], e2y = c_mesh.e2[f][1], e2z = c_mesh.e2[f][2];
+    // p = cart x e2
+    const float px = __fsub_rn(__fmul_rn(gy, e2z), __fmul_rn(gz, e2y));
+    const float py = __fsub_rn(__fmul_rn(gz, e2x), __fmul_rn(gx, e2z));
+    const float pz = __fsub_rn(__fmul_rn(gx, e2y), __fmul_rn(gy, e2x));
+    const float det = __fadd_rn(__fadd_rn(__fmul_rn(c_mesh.e1[f][0], px), __fmul_rn(c_mesh.e1[f][1], py)),
+                                __fmul_rn(c_mesh.e1[f][2], pz));
+    if ((double) fabsf(det) < kBaryEps) return false;
+    const float det_inv = __fdiv_rn(1.0f, det);
+    const float tp = __fadd_rn(__fadd_rn(__fmul_rn(c_mesh.t[f][0], px), __fmul_rn(c_mesh.t[f][1], py)),
+                               __fmul_rn(c_mesh.t[f][2], pz));
+    const float cq = __fadd_rn(__fadd_rn(__fmul_rn(gx, c_mesh.q[f][0]), __fmul_rn(gy, c_mesh.q[f][1])),
+                               __fmul_rn(gz, c_mesh.q[f][2]));
+    by = __fmul_rn(det_inv, tp);
+    bz = __fmul_rn(det_inv, cq);
+    bx = __fsub_rn(__fsub_rn(1.0f, by), bz);
+    const float k = __fmul_rn(c_mesh.e2q[f], det_inv);
+    if ((double) bx < -kBaryEps || (double) by < -kBaryEps || (double) bz < -kBaryEps || k < 0.0f)
+        return false;
+    return true;
+}
+
+constexpr int kDescThreads = 256;
+
+__global__ void __launch_bounds__(kDescThreads)
+descriptor_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ desc_out) {
+    __shared__ float hist[kDescNumel];
+    __shared__ double red[kDescThreads / 32];
+    __shared__ double norm_sh;
+    const int ki = blockIdx.x;
+    if (ki >= n) return;
+    const DescJob J = jobs[ki];
+    for (int i = threadIdx.x; i < kDescNumel; i += kDescThreads) hist[i] = 0.0f;
+    __syncthreads();
+
+    const float *__restrict__ img = J.img;
+    const int nx = J.nx, ny = J.ny, nz = J.nz;
+    const float uxf = J.ux, uyf = J.uy, uzf = J.uz;
+    const float cx = J.cx, cy = J.cy, cz = J.cz;
+    // sift.c:1453-1458
+    const float sigma = J.sigma;
+    const float rad = (float) (kDescRadFctr * (double) sigma);
+    const float half_w = (float) ((double) rad / sqrt(2.0));
+    const float desc_w = __fmul_rn(2.0f, half_w);
+    const float hist_w = __fdiv_rn(desc_w, (float) kHistPerDim);
+    const float bin_fctr = __fdiv_rn(1.0f, hist_w);
+    const float rad2 = __fmul_rn(rad, rad);
+    const float sig2 = __fmul_rn(sigma, sigma);
+    const float ixu = __fdiv_rn(1.0f, uxf), iyu = __fdiv_rn(1.0f, uyf), izu = __fdiv_rn(1.0f, uzf);
+
+    // Window (sift.c:91-99), all-float here because win_radius is a float.
+    const int x0 = (int) fmaxf(floorf(__fsub_rn(cx, __fdiv_rn(rad, uxf))), 1.0f);
+    const int x1 = (int) fminf(ceilf(__fadd_rn(cx, __fdiv_rn(rad, uxf))), (float) (nx - 2));
+    const int y0 = (int) fmaxf(floorf(__fsub_rn(cy, __fdiv_rn(rad, uyf))), 1.0f);
+    const int y1 = (int) fminf(ceilf(__fadd_rn(cy, __fdiv_rn(rad, uyf))), (float) (ny - 2));
+    const int z0 = (int) fmaxf(floorf(__fsub_rn(cz, __fdiv_rn(rad, uzf))), 1.0f);
+    const int z1 = (int) fminf(ceilf(__fadd_rn(cz, __fdiv_rn(rad, uzf))), (float) (nz - 2));
+    const int wx = max(x1 - x0 + 1, 0), wy = max(y1 - y0 + 1, 0), wz = max(z1 - z0 + 1, 0);
+    const int total = wx * wy * wz;
+    const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
+
+    // Rt = R^T (sift.c:1462-1464): Rt[i][j] = R[j][i]
+    const float r00 = J.R[0], r01 = J.R[1], r02 = J.R[2];
+    const float r10 = J.R[3], r11 = J.R[4], r12 = J.R[5];
+    const float r20 = J.R[6], r21 = J.R[7], r22 = J.R[8];
+
+    for (int i = threadIdx.x; i < total; i += kDescThreads) {
+        const int lx = i % wx;
+        const int tq = i / wx;
+        const int ly = tq % wy;
+        const int lz = tq / wy;
+        const int x = x0 + lx, y = y0 + ly, z = z0 + lz;
+        const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
+        const float dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);
+        const float dz = __fmul_rn(__fsub_rn((float) z, cz), uzf);
+        const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+        if (sq > rad2) continue;
+
+        // vkp = Rt * vim (SIFT3D_MUL_MAT_RM_CVEC, immacros.h:326-342)
+        const float kx = __fadd_rn(__fadd_rn(__fmul_rn(r00, dx), __fmul_rn(r10, dy)), __fmul_rn(r20, dz));
+        const float ky = __fadd_rn(__fadd_rn(__fmul_rn(r01, dx), __fmul_rn(r11, dy)), __fmul_rn(r21, dz));
+        const float kz = __fadd_rn(__fadd_rn(__fmul_rn(r02, dx), __fmul_rn(r12, dy)), __fmul_rn(r22, dz));
+        const float vbx = __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
+        const float vby = __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
+        const float vbz = __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
+        if (vbx < 0.0f || vby < 0.0f || vbz < 0.0f || vbx >= (float) kHistPerDim ||
+            vby >= (float) kHistPerDim || vbz >= (float) kHistPerDim)
+            continue;
+
+        const size_t idx = (size_t) z * zs + (size_t) y * ys + x;
+        float gx = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(img[idx + 1], img[idx - 1])), ixu);
+        float gy = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(img[idx + ys], img[idx - ys])), iyu);
+        float gz = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(img[idx + zs], img[idx - zs])), izu);
+        const float w = expf(__fdiv_rn(__fmul_rn(-0.5f, sq), sig2));  // sift.c:1498
+        gx = __fmul_rn(gx, w);
+        gy = __fmul_rn(gy, w);
+        gz = __fmul_rn(gz, w);
+        const float rx = __fadd_rn(__fadd_rn(__fmul_rn(r00, gx), __fmul_rn(r10, gy)), __fmul_rn(r20, gz));
+        const float ry = __fadd_rn(__fadd_rn(__fmul_rn(r01, gx), __fmul_rn(r11, gy)), __fmul_rn(r21, gz));
+        const float rz = __fadd_rn(__fadd_rn(__fmul_rn(r02, gx), __fmul_rn(r12, gy)), __fmul_rn(r22, gz));
+
+        // icos_hist_bin (sift.c:1254-1291)
+        const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz));
+        if ((double) n2 < kBaryEps) continue;
+        // Fast selection: the face whose centre direction is closest to the ray. If the
+        // ray is comfortably inside that face no other face can pass the reference's
+        // (>= -bary_eps) test, so it is also the *first* passing face. Otherwise fall back
+        // to the literal first-hit scan so ties on edges/vertices resolve as in the reference.
+        int best = 0;
+        float bestd = -FLT_MAX;
+#pragma unroll
+        for (int f = 0; f < kFaces; f++) {
+            const float d = fmaf(rx, c_mesh.ctr[f][0], fmaf(ry, c_mesh.ctr[f][1], rz * c_mesh.ctr[f][2]));
+            if (d > bestd) { bestd = d; best = f; }
+        }
+        float bx, by, bz;
+        int face = -1;
+        if (face_hit(best, rx, ry, rz, bx, by, bz) && bx > 1e-3f && by > 1e-3f && bz > 1e-3f) {
+            face = best;
+        } else {
+            for (int f = 0; f < kFaces; f++) {
+                if (face_hit(f, rx, ry, rz, bx, by, bz)) { face = f; break; }
+            }
+        }
+        if (face < 0) continue;  // "unreachable" in the reference (sift.c:1288-1290)
+        const float mag = sqrtf(n2);
+        const int i0 = c_mesh.idx[face][0], i1 = c_mesh.idx[face][1], i2 = c_mesh.idx[face][2];
+
+        // SIFT3D_desc_acc_interp (sift.c:1318-1397)
+        const float fx = __fsub_rn(vbx, floorf(vbx));
+        const float fy = __fsub_rn(vby, floorf(vby));
+        const float fz = __fsub_rn(vbz, floorf(vbz));
+        const int bxi = (int) vbx, byi = (int) vby, bzi = (int) vbz;
+#pragma unroll
+        for (int ddx = 0; ddx < 2; ddx++) {
+#pragma unroll
+            for (int ddy = 0; ddy < 2; ddy++) {
+#pragma unroll
+                for (int ddz = 0; ddz < 2; ddz++) {
+                    const int hx = bxi + ddx, hy = byi + ddy, hz = bzi + ddz;
+                    if (hx >= kHistPerDim || hy >= kHistPerDim || hz >= kHistPerDim) continue;
+                    const float wgt = __fmul_rn(
+                        __fmul_rn(ddx == 0 ? __fsub_rn(1.0f, fx) : fx, ddy == 0 ? __fsub_rn(1.0f, fy) : fy),
+                        ddz == 0 ? __fsub_rn(1.0f, fz) : fz);
+                    const float mw = __fmul_rn(mag, wgt);
+                    float *h = hist + (hx + hy * kHistPerDim + hz * kHistPerDim * kHistPerDim) * kVerts;
+                    atomicAdd(h + i0, __fmul_rn(mw, bx));
+                    atomicAdd(h + i1, __fmul_rn(mw, by));
+                    atomicAdd(h + i2, __fmul_rn(mw, bz));
+                }
+            }
+        }
+    }
+    __syncthreads();
+
+    // normalise, clamp, normalise (sift.c:1513-1526)
+    const float trunc = __fdiv_rn(__fmul_rn(0.2f, 128.0f), (float) kDescNumel);  // sift.c:45
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int pass = 0; pass < 2; pass++) {
+        double ssq = 0.0;
+        for (int i = threadIdx.x; i < kDescNumel; i += kDescThreads) {
+            const float el = hist[i];
+            ssq += (double) el * (double) el;
+        }
+        for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
+        if (lane == 0) red[warp] = ssq;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int wv = 0; wv < kDescThreads / 32; wv++) t += red[wv];
+            norm_sh = sqrt(t) + DBL_EPSILON;
+        }
+        __syncthreads();
+        const float norm_inv = (float) (1.0 / norm_sh);  // sift.c:1423
+        for (int i = threadIdx.x; i < kDescNumel; i += kDescThreads) {
+            float el = __fmul_rn(hist[i], norm_inv);
+            if (pass == 0) el = fminf(el, trunc);
+            hist[i] = el;
+        }
+        __syncthreads();
+    }
+    float *o = desc_out + (size_t) ki * kDescNumel;
+    for (int i = threadIdx.x; i < kDescNumel; i += kDescThreads) o[i] = hist[i];
+}
+
+int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, float *d_desc,
+                       uint64_t *launches) {
+    if (n <= 0) return 0;
+    descriptor_kernel<<<(unsigned) n, kDescThreads, 0, st>>>(d_jobs, n, d_desc);
+    if (launches) *launches += 1;
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace s3d

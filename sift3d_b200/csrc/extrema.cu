@@ -1,0 +1,133 @@
+// extrema.cu -- DoG extremum detection fused with the DoG subtraction, and the
+// deterministic ordering of the candidate list.
+//
+// Reference semantics (sift3d/sift.c:735-871): for s in {0..num_kp_levels-1}, voxels in
+// [1, n-2]^3, D_s = G_s - G_{s+1} (build_dog, sift.c:713-732); accept iff
+// |v| > (float)(peak_thresh * dogmax_s) and v is strictly greater (or strictly smaller) than
+// its 6 face neighbours in D_s and the same voxel in D_{s-1} and D_{s+1}
+// (CMP_PREV/CMP_CUR/CMP_NEXT, sift.c:798-811; CUBOID_EXTREMA is off, sift.c:24).
+// The DoG pyramid is never written to HBM: every D value is one fp32 subtraction of two
+// Gaussian levels, which is exactly what im_subtract stores (imutil.c:734-737).
+#include "common.cuh"
+
+namespace s3d {
+
+struct ExtremaParams {
+    const float *g[SIFT3D_CUDA_MAX_FILTERS + 1];  // Gaussian levels s = -1 .. kp+1
+    float thresh[SIFT3D_CUDA_MAX_FILTERS];        // per keypoint level
+    int num_kp_levels;
+    int nx, ny, nz;
+};
+
+__global__ void __launch_bounds__(256)
+extrema_kernel(const ExtremaParams P, const float *__restrict__ dogmax, float peak_thresh_f,
+               double peak_thresh, Cand *__restrict__ cand, int cap, int *__restrict__ count) {
+    const int nx = P.nx, ny = P.ny, nz = P.nz;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    const int z = blockIdx.z;
+    const bool inside = x >= 1 && x <= nx - 2 && y >= 1 && y <= ny - 2 && z >= 1 && z <= nz - 2;
+    const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
+    const size_t idx = (size_t) z * zs + (size_t) y * ys + x;
+    const unsigned lane = threadIdx.x & 31u;
+
+    for (int s = 0; s < P.num_kp_levels; s++) {
+        bool hit = false;
+        float v = 0.0f;
+        if (inside) {
+            // DoG level s lives between Gaussian levels s and s+1, i.e. g[s+1], g[s+2].
+            const float *__restrict__ ga = P.g[s + 1];
+            const float *__restrict__ gb = P.g[s + 2];
+            v = __fsub_rn(ga[idx], gb[idx]);
+            // peak_thresh = sift3d->peak_thresh * dogmax, stored to a float (sift.c:829)
+            const float thr = (float) (peak_thresh * (double) dogmax[s]);
+            if (v > thr || v < -thr) {
+                const float prev = __fsub_rn(P.g[s][idx], ga[idx]);
+                const float next = __fsub_rn(gb[idx], P.g[s + 3][idx]);
+#define DV(off) __fsub_rn(ga[idx + (off)], gb[idx + (off)])
+                const float xp = DV(1), xm = __fsub_rn(ga[idx - 1], gb[idx - 1]);
+                const float yp = DV(ys), ym = __fsub_rn(ga[idx - ys], gb[idx - ys]);
+                const float zp = DV(zs), zm = __fsub_rn(ga[idx - zs], gb[idx - zs]);
+#undef DV
+                const bool is_max = v > prev && v > xp && v > xm && v > yp && v > ym && v > zm &&
+                                    v > zp && v > next;
+                const bool is_min = v < prev && v < xp && v < xm && v < yp && v < ym && v < zm &&
+                                    v < zp && v < next;
+                hit = is_max || is_min;
+            }
+        }
+        // warp-aggregated append
+        const unsigned ballot = __ballot_sync(0xffffffffu, hit);
+        if (ballot) {
+            int base = 0;
+            const int leader = __ffs(ballot) - 1;
+            if ((int) lane == leader) base = atomicAdd(count, __popc(ballot));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (hit) {
+                const int pos = base + __popc(ballot & ((1u << lane) - 1u));
+                if (pos < cap) {
+                    Cand c;
+                    c.key = ((unsigned long long) s << 60) | ((unsigned long long) z << 40) |
+                            ((unsigned long long) y << 20) | (unsigned long long) x;
+                    c.strength = fabsf(v);
+                    c.pad = 0;
+                    cand[pos] = c;
+                }
+            }
+        }
+    }
+    (void) peak_thresh_f;
+}
+
+// Rank sort: candidate i goes to slot #{j : key_j < key_i}. Keys are unique (one per
+// voxel and level) so the ranks are a permutation; the result is the reference's serial
+// scan order (s, z, y, x) regardless of the order the atomics appended them in.
+__global__ void __launch_bounds__(256)
+order_kernel(const Cand *__restrict__ in, int n, Cand *__restrict__ out) {
+    __shared__ unsigned long long tile[256];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    Cand mine;
+    mine.key = ~0ull;
+    mine.strength = 0.f;
+    mine.pad = 0;
+    if (i < n) mine = in[i];
+    int rank = 0;
+    for (int base = 0; base < n; base += 256) {
+        const int j = base + threadIdx.x;
+        tile[threadIdx.x] = j < n ? in[j].key : ~0ull;
+        __syncthreads();
+        const int lim = min(256, n - base);
+#pragma unroll 8
+        for (int k = 0; k < lim; k++) rank += tile[k] < mine.key ? 1 : 0;
+        __syncthreads();
+    }
+    if (i < n) out[rank] = mine;
+}
+
+int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, int nx, int ny,
+                   int nz, const float *d_dogmax, double peak_thresh, Cand *d_cand, int cap,
+                   int *d_count, uint64_t *launches) {
+    ExtremaParams P;
+    for (int i = 0; i < num_kp_levels + 3; i++) P.g[i] = g[i];
+    P.num_kp_levels = num_kp_levels;
+    P.nx = nx;
+    P.ny = ny;
+    P.nz = nz;
+    S3D_CK(cudaMemsetAsync(d_count, 0, sizeof(int), st));
+    dim3 block(128, 1, 1);
+    dim3 grid((unsigned) ((nx + 127) / 128), (unsigned) ny, (unsigned) nz);
+    extrema_kernel<<<grid, block, 0, st>>>(P, d_dogmax, 0.f, peak_thresh, d_cand, cap, d_count);
+    if (launches) *launches += 1;
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+int launch_order(cudaStream_t st, const Cand *d_in, int n, Cand *d_out, uint64_t *launches) {
+    if (n <= 0) return 0;
+    order_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(d_in, n, d_out);
+    if (launches) *launches += 1;
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace s3d

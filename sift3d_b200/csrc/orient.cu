@@ -1,0 +1,244 @@
+// orient.cu -- structure-tensor orientation assignment, one CTA per candidate, with an
+// in-kernel symmetric 3x3 eigensolver in double (replaces the per-keypoint LAPACK dsyevd_
+// call of the reference, imutil.c:984-1067).
+//
+// Reference semantics (sift3d/sift.c):
+//   assign_orientations        :1109-1167  sigma = ori_sig_fctr * sd, per candidate
+//   assign_eig_ori             :926-1085   window loop, tensor (double), window gradient
+//                                          (float), rejection tests, R construction
+//   IM_LOOP_SPHERE_START       :86-109     window bounds and physical-unit displacement
+//   IM_GET_GRAD_ISO            :140-145    central differences / units
+//   assign_orientation_thresh  :1091-1102  reject if corner score < corner_thresh
+#include <float.h>
+
+#include "common.cuh"
+
+namespace s3d {
+
+constexpr double kMaxEigRatio = 0.90;     // sift.c:38
+constexpr double kOriGradThresh = 1E-10;  // sift.c:39
+constexpr double kOriSigFctr = 1.5;       // sift.c:41
+constexpr double kOriRadFctr = 3.0;       // sift.c:42
+
+// Cyclic Jacobi eigen-decomposition of a symmetric 3x3 in double. Eigenvalues ascending
+// in w (as dsyevd returns them), eigenvectors in the columns of V (as Q after the
+// transpose at imutil.c:1052).
+__device__ void eig3_sym(const double Ain[3][3], double V[3][3], double w[3]) {
+    double A[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            A[i][j] = Ain[i][j];
+            V[i][j] = i == j ? 1.0 : 0.0;
+        }
+    for (int sweep = 0; sweep < 64; sweep++) {
+        const double off = fabs(A[0][1]) + fabs(A[0][2]) + fabs(A[1][2]);
+        if (off == 0.0) break;
+#pragma unroll
+        for (int pq = 0; pq < 3; pq++) {
+            const int p = pq == 2 ? 1 : 0;
+            const int q = pq == 0 ? 1 : 2;
+            const double apq = A[p][q];
+            if (apq == 0.0) continue;
+            const double app = A[p][p], aqq = A[q][q];
+            // Negligible rotation: |apq| below the resolution of both diagonal entries.
+            if (fabs(apq) < DBL_MIN ||
+                (fabs(app) + fabs(apq) == fabs(app) && fabs(aqq) + fabs(apq) == fabs(aqq))) {
+                A[p][q] = A[q][p] = 0.0;
+                continue;
+            }
+            const double theta = (aqq - app) / (2.0 * apq);
+            const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+            const double c = 1.0 / sqrt(t * t + 1.0);
+            const double s = t * c;
+            const double tau = s / (1.0 + c);
+            A[p][p] = app - t * apq;
+            A[q][q] = aqq + t * apq;
+            A[p][q] = A[q][p] = 0.0;
+            const int r = 3 - p - q;  // the remaining index
+            const double arp = A[r][p], arq = A[r][q];
+            A[r][p] = A[p][r] = arp - s * (arq + tau * arp);
+            A[r][q] = A[q][r] = arq + s * (arp - tau * arq);
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const double vkp = V[k][p], vkq = V[k][q];
+                V[k][p] = vkp - s * (vkq + tau * vkp);
+                V[k][q] = vkq + s * (vkp - tau * vkq);
+            }
+        }
+    }
+    w[0] = A[0][0];
+    w[1] = A[1][1];
+    w[2] = A[2][2];
+    // sort ascending (3-element network), permuting the columns of V alongside
+#define S3D_SWAP_COLS(a, b)                                   \
+    if (w[a] > w[b]) {                                        \
+        double tw = w[a]; w[a] = w[b]; w[b] = tw;             \
+        for (int k = 0; k < 3; k++) {                         \
+            double tv = V[k][a]; V[k][a] = V[k][b]; V[k][b] = tv; \
+        }                                                     \
+    }
+    S3D_SWAP_COLS(0, 1)
+    S3D_SWAP_COLS(1, 2)
+    S3D_SWAP_COLS(0, 1)
+#undef S3D_SWAP_COLS
+}
+
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+constexpr int kOrientThreads = 128;
+
+__global__ void __launch_bounds__(kOrientThreads)
+orient_kernel(const Cand *__restrict__ cands, int n, const OctaveInfo info, double corner_thresh,
+              sift3d_cuda_keypoint *__restrict__ out) {
+    const int ci = blockIdx.x;
+    if (ci >= n) return;
+    const Cand cd = cands[ci];
+    const int s = (int) (cd.key >> 60);
+    const int kz = (int) ((cd.key >> 40) & 0xFFFFF);
+    const int ky = (int) ((cd.key >> 20) & 0xFFFFF);
+    const int kx = (int) (cd.key & 0xFFFFF);
+    const float *__restrict__ img = info.lvl[s];
+    const int nx = info.nx, ny = info.ny, nz = info.nz;
+    const float uxf = info.ux, uyf = info.uy, uzf = info.uz;
+    const double sd = info.sd[s];
+    const double sigma = kOriSigFctr * sd;      // sift.c:1125
+    const double rad = sigma * kOriRadFctr;     // sift.c:936
+    const float cx = (float) kx, cy = (float) ky, cz = (float) kz;  // sift.c:1124
+
+    // Window bounds (sift.c:91-99): the double expression is narrowed to float by
+    // floorf/ceilf, compared as float against the int bound, then truncated to int.
+    const int x0 = (int) fmaxf(floorf((float) ((double) cx - rad / (double) uxf)), 1.0f);
+    const int x1 = (int) fminf(ceilf((float) ((double) cx + rad / (double) uxf)), (float) (nx - 2));
+    const int y0 = (int) fmaxf(floorf((float) ((double) cy - rad / (double) uyf)), 1.0f);
+    const int y1 = (int) fminf(ceilf((float) ((double) cy + rad / (double) uyf)), (float) (ny - 2));
+    const int z0 = (int) fmaxf(floorf((float) ((double) cz - rad / (double) uzf)), 1.0f);
+    const int z1 = (int) fminf(ceilf((float) ((double) cz + rad / (double) uzf)), (float) (nz - 2));
+    const int wx = max(x1 - x0 + 1, 0), wy = max(y1 - y0 + 1, 0), wz = max(z1 - z0 + 1, 0);
+    const int total = wx * wy * wz;
+    const double rad2 = rad * rad;
+    const double sig2 = sigma * sigma;
+    const float ixu = __fdiv_rn(1.0f, uxf), iyu = __fdiv_rn(1.0f, uyf), izu = __fdiv_rn(1.0f, uzf);
+    const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
+
+    double a00 = 0, a01 = 0, a02 = 0, a11 = 0, a12 = 0, a22 = 0;
+    double gx = 0, gy = 0, gz = 0;  // window gradient, summed in double, narrowed at the end
+    for (int i = threadIdx.x; i < total; i += kOrientThreads) {
+        const int lx = i % wx;
+        const int t = i / wx;
+        const int ly = t % wy;
+        const int lz = t / wy;
+        const int x = x0 + lx, y = y0 + ly, z = z0 + lz;
+        const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
+        const float dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);
+        const float dz = __fmul_rn(__fsub_rn((float) z, cz), uzf);
+        const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+        if ((double) sq > rad2) continue;
+        // weight = expf(-0.5 * sq_dist / (sigma * sigma)): double argument narrowed to float
+        // (sift.c:972). exp() in double then one rounding is a correctly rounded expf.
+        const float arg = (float) (-0.5 * (double) sq / sig2);
+        const float w = (float) exp((double) arg);
+        const size_t idx = (size_t) z * zs + (size_t) y * ys + x;
+        float vx = __fmul_rn(0.5f, __fsub_rn(img[idx + 1], img[idx - 1]));
+        float vy = __fmul_rn(0.5f, __fsub_rn(img[idx + ys], img[idx - ys]));
+        float vz = __fmul_rn(0.5f, __fsub_rn(img[idx + zs], img[idx - zs]));
+        vx = __fmul_rn(vx, ixu);
+        vy = __fmul_rn(vy, iyu);
+        vz = __fmul_rn(vz, izu);
+        const double wd = (double) w;
+        a00 += (double) vx * (double) vx * wd;
+        a01 += (double) vx * (double) vy * wd;
+        a02 += (double) vx * (double) vz * wd;
+        a11 += (double) vy * (double) vy * wd;
+        a12 += (double) vy * (double) vz * wd;
+        a22 += (double) vz * (double) vz * wd;
+        gx += (double) __fmul_rn(vx, w);
+        gy += (double) __fmul_rn(vy, w);
+        gz += (double) __fmul_rn(vz, w);
+    }
+
+    __shared__ double red[kOrientThreads / 32][9];
+    double vals[9] = {a00, a01, a02, a11, a12, a22, gx, gy, gz};
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        const double r = warp_sum(vals[k]);
+        if (lane == 0) red[warp][k] = r;
+    }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+#pragma unroll
+    for (int k = 0; k < 9; k++) {
+        double r = 0;
+        for (int wv = 0; wv < kOrientThreads / 32; wv++) r += red[wv][k];
+        vals[k] = r;
+    }
+
+    sift3d_cuda_keypoint kp;
+    kp.o = info.o;
+    kp.s = s;
+    kp.x = (double) kx;
+    kp.y = (double) ky;
+    kp.z = (double) kz;
+    kp.sd = sd;
+    kp.strength = cd.strength;
+    for (int k = 0; k < 9; k++) kp.R[k] = 0.0f;
+    kp.valid = 0;
+
+    const float wgx = (float) vals[6], wgy = (float) vals[7], wgz = (float) vals[8];
+    const float gnorm2 = __fadd_rn(__fadd_rn(__fmul_rn(wgx, wgx), __fmul_rn(wgy, wgy)), __fmul_rn(wgz, wgz));
+    bool ok = !(gnorm2 < (float) kOriGradThresh);  // sift.c:997
+    if (ok) {
+        double A[3][3] = {{vals[0], vals[1], vals[2]}, {vals[1], vals[3], vals[4]}, {vals[2], vals[4], vals[5]}};
+        double V[3][3], L[3];
+        eig3_sym(A, V, L);
+        // eigenvalue-ratio stability test (sift.c:1011-1015)
+        if (fabs(L[0] / L[1]) > kMaxEigRatio || fabs(L[1] / L[2]) > kMaxEigRatio) ok = false;
+        if (ok) {
+            double corner = DBL_MAX;
+            float v0[3], v1[3];
+            const float gnorm = sqrtf(gnorm2);
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                const int e = 2 - i;  // descending eigenvalue order (sift.c:1021)
+                float vr0 = (float) V[0][e], vr1 = (float) V[1][e], vr2 = (float) V[2][e];
+                const double d = (double) __fadd_rn(__fadd_rn(__fmul_rn(wgx, vr0), __fmul_rn(wgy, vr1)), __fmul_rn(wgz, vr2));
+                const float vnorm = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(vr0, vr0), __fmul_rn(vr1, vr1)), __fmul_rn(vr2, vr2)));
+                const double cosang = d / (double) __fmul_rn(vnorm, gnorm);
+                corner = fmin(corner, fabs(cosang));
+                const float sgn = d > 0.0 ? 1.0f : -1.0f;
+                vr0 = __fmul_rn(vr0, sgn);
+                vr1 = __fmul_rn(vr1, sgn);
+                vr2 = __fmul_rn(vr2, sgn);
+                kp.R[0 * 3 + i] = vr0;
+                kp.R[1 * 3 + i] = vr1;
+                kp.R[2 * 3 + i] = vr2;
+                if (i == 0) { v0[0] = vr0; v0[1] = vr1; v0[2] = vr2; }
+                else        { v1[0] = vr0; v1[1] = vr1; v1[2] = vr2; }
+            }
+            // third axis = v0 x v1 (sift.c:1054-1059)
+            kp.R[0 * 3 + 2] = __fsub_rn(__fmul_rn(v0[1], v1[2]), __fmul_rn(v0[2], v1[1]));
+            kp.R[1 * 3 + 2] = __fsub_rn(__fmul_rn(v0[2], v1[0]), __fmul_rn(v0[0], v1[2]));
+            kp.R[2 * 3 + 2] = __fsub_rn(__fmul_rn(v0[0], v1[1]), __fmul_rn(v0[1], v1[0]));
+            if (corner < corner_thresh) ok = false;  // sift.c:1100-1101
+        }
+    }
+    kp.valid = ok ? 1 : 0;
+    out[ci] = kp;
+}
+
+int launch_orient(cudaStream_t st, const Cand *d_cands, int n, const OctaveInfo &info,
+                  double corner_thresh, sift3d_cuda_keypoint *d_out, uint64_t *launches) {
+    if (n <= 0) return 0;
+    orient_kernel<<<(unsigned) n, kOrientThreads, 0, st>>>(d_cands, n, info, corner_thresh, d_out);
+    if (launches) *launches += 1;
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace s3d

@@ -1,0 +1,552 @@
+// sift3d_cuda.cu -- context, device arena, pipeline schedule and the C ABI of
+// libsift3d_cuda.so (include/sift3d_cuda.h). One context = one device + one stream +
+// one resident pyramid, mirroring "one detector keeps the last image's pyramid so that
+// descriptors can be extracted later" (sift3d/sift.c:1622-1628).
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+
+using namespace s3d;
+
+namespace {
+
+enum { EV_START, EV_H2D, EV_SCALE, EV_PYR, EV_EXTREMA, EV_ORDER, EV_ORIENT, EV_D2H, EV_COUNT };
+enum { DV_START, DV_H2D, DV_KERNEL, DV_D2H, DV_COUNT };
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+    int ensure(size_t need) {
+        if (need <= bytes) return 0;
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+        S3D_CK(cudaMalloc(&p, need));
+        bytes = need;
+        return 0;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+};
+
+}  // namespace
+
+struct sift3d_cuda_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[EV_COUNT] = {};
+    cudaEvent_t dv[DV_COUNT] = {};
+    uint64_t launches = 0;
+
+    // plan
+    bool planned = false;
+    sift3d_cuda_plan_desc desc;
+    int nlev = 0;  // Gaussian levels per octave = num_kp_levels + 3
+    std::vector<Level> levels;          // [o * nlev + (s + 1)]
+    DevBuf pyr, input, tmp_a, tmp_b;    // arena
+    DevBuf taps;                        // (1 + filters) * SIFT3D_CUDA_MAX_TAPS floats
+    DevBuf scalars;                     // [0] image max-abs; [1 + o*MAX_FILTERS + s] DoG max
+    DevBuf cand_raw, cand_sorted;       // Cand regions, one per octave
+    DevBuf counts;                      // int per octave
+    DevBuf kps;                         // sift3d_cuda_keypoint, compact across octaves
+    std::vector<int> cand_base, cand_cap;
+    int *h_counts = nullptr;            // pinned
+    bool have_pyramid = false;
+    int total_candidates = 0;
+
+    // describe
+    DevBuf desc_jobs, desc_out;
+    sift3d_cuda_timings tm;
+
+    Level &level(int o, int s) { return levels[(size_t) o * nlev + (s + 1)]; }
+    float *d_taps(int filter /* -1 = first */) {
+        return (float *) taps.p + (size_t) (filter + 1) * SIFT3D_CUDA_MAX_TAPS;
+    }
+    float *d_scalar(int i) { return (float *) scalars.p + i; }
+};
+
+static int set_device(sift3d_cuda_ctx *ctx) {
+    S3D_CK(cudaSetDevice(ctx->device));
+    return 0;
+}
+
+extern "C" {
+
+int sift3d_cuda_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+sift3d_cuda_ctx *sift3d_cuda_ctx_create(int device) {
+    int n = sift3d_cuda_device_count();
+    if (n <= 0) {
+        S3D_ERR("sift3d_cuda: no CUDA device available -- this library has no CPU fallback\n");
+        return nullptr;
+    }
+    if (device < 0) {
+        const char *e = getenv("SIFT3D_CUDA_DEVICE");
+        device = e ? atoi(e) : 0;
+    }
+    if (device >= n) {
+        S3D_ERR("sift3d_cuda: device %d requested but only %d visible\n", device, n);
+        return nullptr;
+    }
+    sift3d_cuda_ctx *ctx = new (std::nothrow) sift3d_cuda_ctx();
+    if (!ctx) return nullptr;
+    ctx->device = device;
+    memset(&ctx->tm, 0, sizeof(ctx->tm));
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        S3D_ERR("sift3d_cuda: cannot initialise device %d: %s\n", device,
+                cudaGetErrorString(cudaGetLastError()));
+        delete ctx;
+        return nullptr;
+    }
+    for (int i = 0; i < EV_COUNT; i++) cudaEventCreate(&ctx->ev[i]);
+    for (int i = 0; i < DV_COUNT; i++) cudaEventCreate(&ctx->dv[i]);
+    if (cudaMallocHost((void **) &ctx->h_counts, sizeof(int) * 64) != cudaSuccess ||
+        upload_mesh() != 0) {
+        S3D_ERR("sift3d_cuda: context setup failed\n");
+        sift3d_cuda_ctx_destroy(ctx);
+        return nullptr;
+    }
+    return ctx;
+}
+
+void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    ctx->pyr.release();
+    ctx->input.release();
+    ctx->tmp_a.release();
+    ctx->tmp_b.release();
+    ctx->taps.release();
+    ctx->scalars.release();
+    ctx->cand_raw.release();
+    ctx->cand_sorted.release();
+    ctx->counts.release();
+    ctx->kps.release();
+    ctx->desc_jobs.release();
+    ctx->desc_out.release();
+    if (ctx->h_counts) cudaFreeHost(ctx->h_counts);
+    for (int i = 0; i < EV_COUNT; i++)
+        if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    for (int i = 0; i < DV_COUNT; i++)
+        if (ctx->dv[i]) cudaEventDestroy(ctx->dv[i]);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+void *sift3d_cuda_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (bytes == 0) bytes = 1;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+void sift3d_cuda_host_free(void *p) {
+    if (p) cudaFreeHost(p);
+}
+
+int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
+    if (!ctx || !d) return -1;
+    if (set_device(ctx)) return -1;
+    if (d->num_octaves < 1 || d->num_octaves > SIFT3D_CUDA_MAX_OCTAVES || d->num_kp_levels < 1 ||
+        d->num_kp_levels + 2 > SIFT3D_CUDA_MAX_FILTERS || d->nx < 1 || d->ny < 1 || d->nz < 1) {
+        S3D_ERR("sift3d_cuda_plan: invalid geometry\n");
+        return -1;
+    }
+    if (d->nx >= (1 << 20) || d->ny >= (1 << 20) || d->nz >= (1 << 20)) {
+        S3D_ERR("sift3d_cuda_plan: dimensions must be below 2^20\n");
+        return -1;
+    }
+    S3D_CK(cudaStreamSynchronize(ctx->stream));
+    ctx->planned = false;
+    ctx->have_pyramid = false;
+    ctx->desc = *d;
+    ctx->nlev = d->num_kp_levels + 3;
+    const int nlev = ctx->nlev, noct = d->num_octaves;
+
+    // level geometry: dims halve per octave (imutil.c:1545-1548)
+    ctx->levels.assign((size_t) noct * nlev, Level());
+    size_t total = 0;
+    {
+        int nx = d->nx, ny = d->ny, nz = d->nz;
+        for (int o = 0; o < noct; o++) {
+            if (nx < 1 || ny < 1 || nz < 1) {
+                S3D_ERR("sift3d_cuda_plan: too many octaves for these dimensions\n");
+                return -1;
+            }
+            for (int s = -1; s < nlev - 1; s++) {
+                Level &L = ctx->level(o, s);
+                L.nx = nx; L.ny = ny; L.nz = nz;
+                L.scale = d->scales[o][s + 1];
+                total += (L.nvox() + 63) & ~(size_t) 63;  // 256-byte aligned levels
+            }
+            nx /= 2; ny /= 2; nz /= 2;
+        }
+    }
+    if (ctx->pyr.ensure(total * sizeof(float))) return -1;
+    {
+        size_t off = 0;
+        for (int o = 0; o < noct; o++)
+            for (int s = -1; s < nlev - 1; s++) {
+                Level &L = ctx->level(o, s);
+                L.d = (float *) ctx->pyr.p + off;
+                off += (L.nvox() + 63) & ~(size_t) 63;
+            }
+    }
+    const size_t n0 = (size_t) d->nx * d->ny * d->nz;
+    if (ctx->input.ensure(n0 * sizeof(float)) || ctx->tmp_a.ensure(n0 * sizeof(float)) ||
+        ctx->tmp_b.ensure(n0 * sizeof(float)))
+        return -1;
+
+    // filters
+    const int nfilt = d->num_kp_levels + 2;
+    if (ctx->taps.ensure((size_t) (nfilt + 1) * SIFT3D_CUDA_MAX_TAPS * sizeof(float))) return -1;
+    if (d->first.width < 1 || d->first.width > SIFT3D_CUDA_MAX_TAPS) {
+        S3D_ERR("sift3d_cuda_plan: unsupported filter width %d\n", d->first.width);
+        return -1;
+    }
+    S3D_CK(cudaMemcpyAsync(ctx->d_taps(-1), d->first.taps, sizeof(float) * d->first.width,
+                           cudaMemcpyHostToDevice, ctx->stream));
+    for (int i = 0; i < nfilt; i++) {
+        if (d->octave[i].width < 1 || d->octave[i].width > SIFT3D_CUDA_MAX_TAPS) {
+            S3D_ERR("sift3d_cuda_plan: unsupported filter width %d\n", d->octave[i].width);
+            return -1;
+        }
+        S3D_CK(cudaMemcpyAsync(ctx->d_taps(i), d->octave[i].taps,
+                               sizeof(float) * d->octave[i].width, cudaMemcpyHostToDevice,
+                               ctx->stream));
+    }
+    if (ctx->scalars.ensure(sizeof(float) * (1 + (size_t) noct * SIFT3D_CUDA_MAX_FILTERS)))
+        return -1;
+
+    // candidate regions
+    ctx->cand_base.assign(noct, 0);
+    ctx->cand_cap.assign(noct, 0);
+    size_t cand_total = 0;
+    for (int o = 0; o < noct; o++) {
+        const size_t nv = ctx->level(o, 0).nvox();
+        size_t cap = nv / 32;
+        if (cap < 4096) cap = 4096;
+        if (cap > ((size_t) 1 << 26)) cap = (size_t) 1 << 26;
+        ctx->cand_base[o] = (int) cand_total;
+        ctx->cand_cap[o] = (int) cap;
+        cand_total += cap;
+    }
+    if (ctx->cand_raw.ensure(cand_total * sizeof(Cand)) ||
+        ctx->cand_sorted.ensure(cand_total * sizeof(Cand)) ||
+        ctx->counts.ensure(sizeof(int) * 64) ||
+        ctx->kps.ensure(cand_total * sizeof(sift3d_cuda_keypoint)))
+        return -1;
+    S3D_CK(cudaStreamSynchronize(ctx->stream));
+    ctx->planned = true;
+    return 0;
+}
+
+int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_device,
+                       const double units[3], double peak_thresh, double corner_thresh,
+                       int *num_candidates) {
+    if (!ctx || !ctx->planned || !image || !units) {
+        S3D_ERR("sift3d_cuda_detect: context not planned or NULL argument\n");
+        return -1;
+    }
+    if (set_device(ctx)) return -1;
+    cudaStream_t st = ctx->stream;
+    const sift3d_cuda_plan_desc &D = ctx->desc;
+    const int nlev = ctx->nlev, noct = D.num_octaves, kp = D.num_kp_levels;
+    const size_t n0 = (size_t) D.nx * D.ny * D.nz;
+    ctx->have_pyramid = false;
+
+    // Units: octave 0 takes the units of this image (apply_Sep_FIR_filter copies them from
+    // the source, imutil.c:1145); octaves >= 1 keep what resize_Pyramid assigned when the
+    // dims last changed, doubled per octave (imutil.c:1545-1548, sift.c:651-656).
+    for (int o = 0; o < noct; o++)
+        for (int s = -1; s < nlev - 1; s++) {
+            Level &L = ctx->level(o, s);
+            const double *u = o == 0 ? units : D.units;
+            L.ux = ldexp(u[0], o);
+            L.uy = ldexp(u[1], o);
+            L.uz = ldexp(u[2], o);
+        }
+
+    S3D_CK(cudaEventRecord(ctx->ev[EV_START], st));
+    const float *d_in = image;
+    if (!image_on_device) {
+        S3D_CK(cudaMemcpyAsync(ctx->input.p, image, n0 * sizeof(float), cudaMemcpyHostToDevice, st));
+        d_in = (const float *) ctx->input.p;
+    }
+    S3D_CK(cudaEventRecord(ctx->ev[EV_H2D], st));
+
+    // im_scale: max |v| (imutil.c:681-695); the division is applied on load by the first blur.
+    if (launch_absmax(st, d_in, n0, ctx->d_scalar(0), &ctx->launches)) return -1;
+    S3D_CK(cudaEventRecord(ctx->ev[EV_SCALE], st));
+
+    // build_gpyr (sift.c:662-711)
+    float *ta = (float *) ctx->tmp_a.p, *tb = (float *) ctx->tmp_b.p;
+    {
+        Level &L = ctx->level(0, -1);
+        const double u[3] = {L.ux, L.uy, L.uz};
+        if (launch_blur(st, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
+                        ctx->d_scalar(0), nullptr, nullptr, false, &ctx->launches))
+            return -1;
+    }
+    for (int o = 0; o < noct; o++) {
+        for (int s = 0; s < nlev - 1; s++) {
+            Level &P = ctx->level(o, s - 1);
+            Level &L = ctx->level(o, s);
+            const double u[3] = {P.ux, P.uy, P.uz};
+            // DoG level s-1 = G(s-1) - G(s); its max-abs is needed for keypoint levels only
+            float *slot = nullptr;
+            if (s - 1 >= 0 && s - 1 < kp) slot = ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (s - 1));
+            if (launch_blur(st, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
+                            nullptr, slot, P.d, false, &ctx->launches))
+                return -1;
+        }
+        if (o != noct - 1) {
+            const int ds = (nlev - 2) - 2 > -1 ? (nlev - 2) - 2 : -1;  // sift.c:696-697
+            Level &S = ctx->level(o, ds);
+            Level &T = ctx->level(o + 1, -1);
+            if (launch_downsample(st, S.d, T.d, S.nx, S.ny, S.nz, &ctx->launches)) return -1;
+        }
+    }
+    S3D_CK(cudaEventRecord(ctx->ev[EV_PYR], st));
+
+    // detect_extrema (sift.c:735-871)
+    S3D_CK(cudaMemsetAsync(ctx->counts.p, 0, sizeof(int) * 64, st));
+    for (int o = 0; o < noct; o++) {
+        const float *g[SIFT3D_CUDA_MAX_FILTERS + 1];
+        for (int s = -1; s < nlev - 1; s++) g[s + 1] = ctx->level(o, s).d;
+        Level &L = ctx->level(o, 0);
+        if (launch_extrema(st, g, kp, L.nx, L.ny, L.nz,
+                           ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS), peak_thresh,
+                           (Cand *) ctx->cand_raw.p + ctx->cand_base[o], ctx->cand_cap[o],
+                           (int *) ctx->counts.p + o, &ctx->launches))
+            return -1;
+    }
+    S3D_CK(cudaMemcpyAsync(ctx->h_counts, ctx->counts.p, sizeof(int) * noct,
+                           cudaMemcpyDeviceToHost, st));
+    S3D_CK(cudaEventRecord(ctx->ev[EV_EXTREMA], st));
+    S3D_CK(cudaStreamSynchronize(st));
+    int total = 0;
+    for (int o = 0; o < noct; o++) {
+        if (ctx->h_counts[o] > ctx->cand_cap[o]) {
+            S3D_ERR("sift3d_cuda_detect: octave %d produced %d extrema, capacity %d\n", o,
+                    ctx->h_counts[o], ctx->cand_cap[o]);
+            return -1;
+        }
+        total += ctx->h_counts[o];
+    }
+
+    // scan order (o, s, z, y, x)
+    for (int o = 0; o < noct; o++)
+        if (launch_order(st, (Cand *) ctx->cand_raw.p + ctx->cand_base[o], ctx->h_counts[o],
+                         (Cand *) ctx->cand_sorted.p + ctx->cand_base[o], &ctx->launches))
+            return -1;
+    S3D_CK(cudaEventRecord(ctx->ev[EV_ORDER], st));
+
+    // assign_orientations (sift.c:1109-1143), compact output across octaves
+    int out_base = 0;
+    for (int o = 0; o < noct; o++) {
+        OctaveInfo info;
+        memset(&info, 0, sizeof(info));
+        for (int s = 0; s < kp; s++) {
+            info.lvl[s] = ctx->level(o, s).d;
+            info.sd[s] = ctx->level(o, s).scale;
+        }
+        Level &L = ctx->level(o, 0);
+        info.o = o;
+        info.nx = L.nx; info.ny = L.ny; info.nz = L.nz;
+        info.ux = (float) L.ux; info.uy = (float) L.uy; info.uz = (float) L.uz;
+        if (launch_orient(st, (Cand *) ctx->cand_sorted.p + ctx->cand_base[o], ctx->h_counts[o],
+                          info, corner_thresh, (sift3d_cuda_keypoint *) ctx->kps.p + out_base,
+                          &ctx->launches))
+            return -1;
+        out_base += ctx->h_counts[o];
+    }
+    S3D_CK(cudaEventRecord(ctx->ev[EV_ORIENT], st));
+    ctx->total_candidates = total;
+    ctx->have_pyramid = true;
+    if (num_candidates) *num_candidates = total;
+    return 0;
+}
+
+int sift3d_cuda_fetch_candidates(sift3d_cuda_ctx *ctx, sift3d_cuda_keypoint *out, int max) {
+    if (!ctx || !ctx->have_pyramid || (!out && max > 0)) return -1;
+    if (set_device(ctx)) return -1;
+    int n = ctx->total_candidates < max ? ctx->total_candidates : max;
+    if (n > 0)
+        S3D_CK(cudaMemcpyAsync(out, ctx->kps.p, sizeof(sift3d_cuda_keypoint) * (size_t) n,
+                               cudaMemcpyDeviceToHost, ctx->stream));
+    S3D_CK(cudaEventRecord(ctx->ev[EV_D2H], ctx->stream));
+    S3D_CK(cudaStreamSynchronize(ctx->stream));
+    float ms;
+    sift3d_cuda_timings &t = ctx->tm;
+    cudaEventElapsedTime(&ms, ctx->ev[EV_START], ctx->ev[EV_H2D]); t.h2d = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[EV_H2D], ctx->ev[EV_SCALE]); t.scale = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[EV_SCALE], ctx->ev[EV_PYR]); t.pyramid = ms;
+    t.dogmax = 0;
+    cudaEventElapsedTime(&ms, ctx->ev[EV_PYR], ctx->ev[EV_EXTREMA]); t.extrema = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[EV_EXTREMA], ctx->ev[EV_ORDER]); t.order = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[EV_ORDER], ctx->ev[EV_ORIENT]); t.orient = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[EV_ORIENT], ctx->ev[EV_D2H]); t.d2h = ms;
+    cudaEventElapsedTime(&ms, ctx->ev[EV_START], ctx->ev[EV_D2H]); t.total_detect = ms;
+    return n;
+}
+
+int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys, int num,
+                         float *desc, int desc_on_device) {
+    if (!ctx || !ctx->have_pyramid) {
+        S3D_ERR("sift3d_cuda_describe: no Gaussian pyramid is available; run detect first\n");
+        return -1;
+    }
+    if (num < 1 || !keys || !desc) {
+        S3D_ERR("sift3d_cuda_describe: invalid number of keypoints: %d\n", num);
+        return -1;
+    }
+    if (set_device(ctx)) return -1;
+    cudaStream_t st = ctx->stream;
+    const int noct = ctx->desc.num_octaves, kp = ctx->desc.num_kp_levels;
+    std::vector<DescJob> jobs((size_t) num);
+    for (int i = 0; i < num; i++) {
+        const sift3d_cuda_keypoint &k = keys[i];
+        // any Gaussian level may be addressed (the reference indexes gpyr by key->o, key->s)
+        if (k.o < 0 || k.o >= noct || k.s < -1 || k.s > kp + 1) {
+            S3D_ERR("sift3d_cuda_describe: keypoint %d has invalid octave/level (%d, %d)\n", i,
+                    k.o, k.s);
+            return -1;
+        }
+        const Level &L = ctx->level(k.o, k.s);
+        DescJob &J = jobs[(size_t) i];
+        J.img = L.d;
+        J.nx = L.nx; J.ny = L.ny; J.nz = L.nz;
+        J.ux = (float) L.ux; J.uy = (float) L.uy; J.uz = (float) L.uz;
+        J.cx = (float) k.x; J.cy = (float) k.y; J.cz = (float) k.z;  // sift.c:1474-1476
+        J.sigma = (float) (k.sd * 7.071067812);                        // sift.c:43,1453
+        for (int j = 0; j < 9; j++) J.R[j] = k.R[j];
+    }
+    if (ctx->desc_jobs.ensure(sizeof(DescJob) * (size_t) num)) return -1;
+    float *d_out = desc;
+    if (!desc_on_device) {
+        if (ctx->desc_out.ensure(sizeof(float) * SIFT3D_CUDA_DESC_NUMEL * (size_t) num)) return -1;
+        d_out = (float *) ctx->desc_out.p;
+    }
+    S3D_CK(cudaEventRecord(ctx->dv[DV_START], st));
+    S3D_CK(cudaMemcpyAsync(ctx->desc_jobs.p, jobs.data(), sizeof(DescJob) * (size_t) num,
+                           cudaMemcpyHostToDevice, st));
+    S3D_CK(cudaEventRecord(ctx->dv[DV_H2D], st));
+    if (launch_descriptors(st, (const DescJob *) ctx->desc_jobs.p, num, d_out, &ctx->launches))
+        return -1;
+    S3D_CK(cudaEventRecord(ctx->dv[DV_KERNEL], st));
+    if (!desc_on_device)
+        S3D_CK(cudaMemcpyAsync(desc, d_out, sizeof(float) * SIFT3D_CUDA_DESC_NUMEL * (size_t) num,
+                               cudaMemcpyDeviceToHost, st));
+    S3D_CK(cudaEventRecord(ctx->dv[DV_D2H], st));
+    S3D_CK(cudaStreamSynchronize(st));
+    float ms;
+    cudaEventElapsedTime(&ms, ctx->dv[DV_START], ctx->dv[DV_H2D]); ctx->tm.desc_h2d = ms;
+    cudaEventElapsedTime(&ms, ctx->dv[DV_H2D], ctx->dv[DV_KERNEL]); ctx->tm.descriptors = ms;
+    cudaEventElapsedTime(&ms, ctx->dv[DV_KERNEL], ctx->dv[DV_D2H]); ctx->tm.desc_d2h = ms;
+    cudaEventElapsedTime(&ms, ctx->dv[DV_START], ctx->dv[DV_D2H]); ctx->tm.total_describe = ms;
+    return 0;
+}
+
+int sift3d_cuda_level_info(sift3d_cuda_ctx *ctx, int o, int s, int dims[3], double units[3],
+                           double *scale) {
+    if (!ctx || !ctx->planned || o < 0 || o >= ctx->desc.num_octaves || s < -1 || s > ctx->nlev - 2)
+        return -1;
+    const Level &L = ctx->level(o, s);
+    if (dims) { dims[0] = L.nx; dims[1] = L.ny; dims[2] = L.nz; }
+    if (units) { units[0] = L.ux; units[1] = L.uy; units[2] = L.uz; }
+    if (scale) *scale = L.scale;
+    return 0;
+}
+
+int sift3d_cuda_fetch_level(sift3d_cuda_ctx *ctx, int o, int s, float *host_out) {
+    if (!ctx || !ctx->have_pyramid || !host_out || o < 0 || o >= ctx->desc.num_octaves || s < -1 ||
+        s > ctx->nlev - 2)
+        return -1;
+    if (set_device(ctx)) return -1;
+    const Level &L = ctx->level(o, s);
+    S3D_CK(cudaMemcpyAsync(host_out, L.d, L.nvox() * sizeof(float), cudaMemcpyDeviceToHost,
+                           ctx->stream));
+    S3D_CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int sift3d_cuda_dogmax(sift3d_cuda_ctx *ctx, int o, int s, float *out) {
+    if (!ctx || !ctx->have_pyramid || !out || o < 0 || o >= ctx->desc.num_octaves || s < 0 ||
+        s >= ctx->desc.num_kp_levels)
+        return -1;
+    if (set_device(ctx)) return -1;
+    S3D_CK(cudaMemcpyAsync(out, ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + s), sizeof(float),
+                           cudaMemcpyDeviceToHost, ctx->stream));
+    S3D_CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int sift3d_cuda_blur(sift3d_cuda_ctx *ctx, const float *host_src, float *host_dst, int nx, int ny,
+                     int nz, const double units[3], const sift3d_cuda_filter *f,
+                     int force_generic) {
+    if (!ctx || !host_src || !host_dst || !units || !f || nx < 2 || ny < 2 || nz < 2 ||
+        f->width < 1 || f->width > SIFT3D_CUDA_MAX_TAPS || !(f->width & 1))
+        return -1;
+    if (set_device(ctx)) return -1;
+    const size_t n = (size_t) nx * ny * nz;
+    DevBuf a, b, c, d, t;
+    int ret = -1;
+    if (a.ensure(n * 4) || b.ensure(n * 4) || c.ensure(n * 4) || d.ensure(n * 4) ||
+        t.ensure(sizeof(float) * SIFT3D_CUDA_MAX_TAPS))
+        goto done;
+    if (cudaMemcpyAsync(a.p, host_src, n * 4, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess ||
+        cudaMemcpyAsync(t.p, f->taps, sizeof(float) * f->width, cudaMemcpyHostToDevice,
+                        ctx->stream) != cudaSuccess)
+        goto done;
+    if (launch_blur(ctx->stream, (const float *) a.p, (float *) b.p, (float *) c.p, (float *) d.p,
+                    nx, ny, nz, units, *f, (const float *) t.p, nullptr, nullptr, nullptr,
+                    force_generic != 0, &ctx->launches))
+        goto done;
+    if (cudaMemcpyAsync(host_dst, b.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+        cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+        S3D_ERR("sift3d_cuda_blur: %s\n", cudaGetErrorString(cudaGetLastError()));
+        goto done;
+    }
+    ret = 0;
+done:
+    a.release(); b.release(); c.release(); d.release(); t.release();
+    return ret;
+}
+
+int sift3d_cuda_get_timings(sift3d_cuda_ctx *ctx, sift3d_cuda_timings *t) {
+    if (!ctx || !t) return -1;
+    *t = ctx->tm;
+    return 0;
+}
+
+uint64_t sift3d_cuda_launch_count(sift3d_cuda_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int sift3d_cuda_synchronize(sift3d_cuda_ctx *ctx) {
+    if (!ctx) return -1;
+    if (set_device(ctx)) return -1;
+    S3D_CK(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+}  // extern "C"
