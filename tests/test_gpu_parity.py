@@ -1,0 +1,157 @@
+"""GPU parity tests proper: the CUDA path through the drop-in C API against the oracle
+(oracle/_ref = the unmodified reference compiled from /root/reference; see
+oracle/Makefile) on the same seeded inputs. Run on the B200 box with `-m gpu`."""
+import numpy as np
+import pytest
+
+import parity
+from sift3d_b200.synth import synth_volume
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref():
+    from oracle import refstage
+    assert refstage.available(), "oracle/_ref/libsift3d_refstage.so missing (make -C oracle)"
+    return refstage
+
+
+def _gauss_taps(sigma):
+    """init_Gauss_filter (imutil.c:1267-1319) in numpy, for the blur unit tests."""
+    hw = max(int(np.ceil(sigma * 3.0)), 1)
+    x = (np.arange(2 * hw + 1, dtype=np.float64) - hw) / (sigma + np.finfo(np.float64).eps)
+    k = np.exp(-0.5 * x * x).astype(np.float32)
+    acc = np.float32(0)
+    for v in k:
+        acc = np.float32(acc + v)
+    return (k / acc).astype(np.float32)
+
+
+@pytest.fixture(scope="module")
+def det():
+    import sift3d_b200 as s3
+    d = s3.Detector()
+    yield d
+    d.close()
+
+
+@pytest.mark.parametrize("units", [(1, 1, 1), (2, 2, 2), (4, 4, 4), (8, 8, 8), (0.75, 0.75, 1.5),
+                                   (1.0, 2.0, 0.5)])
+@pytest.mark.parametrize("sigma", [0.5387, 0.9733, 1.5450, 2.4525])
+def test_blur_bit_exact(det, units, sigma):
+    """One separable blur == apply_Sep_FIR_filter, bit for bit, incl. all boundaries."""
+    ref = _ref()
+    rng = np.random.default_rng(int(sigma * 1000) + int(units[0] * 8))
+    vol = rng.standard_normal((23, 20, 37)).astype(np.float32)
+    taps = _gauss_taps(sigma)
+    want = ref.ref_blur(vol, units, taps)
+    got = det.blur(vol, units, taps)
+    rel, nbits = parity.level_error(got, want)
+    assert nbits == 0, f"{nbits} voxels differ (max rel err {rel:.3g})"
+
+
+CASES = [
+    # name, dims (nx, ny, nz), units, blobs, flags
+    ("blobs_64", (64, 64, 64), (1.0, 1.0, 1.0), 64, 0),
+    ("ragged_70x45x33", (70, 45, 33), (1.0, 1.0, 1.0), 40, 0),
+    ("aniso_64x64x48", (64, 64, 48), (0.75, 0.75, 1.5), 48, 0),
+    ("noisy_80", (80, 80, 80), (1.0, 1.0, 1.0), 125, 3),
+]
+
+
+@pytest.mark.parametrize("name,dims,units,blobs,flags", CASES)
+def test_full_pipeline_vs_reference(name, dims, units, blobs, flags):
+    _ref()
+    vol = synth_volume(*dims, num_blobs=blobs, flags=flags)
+    want = parity.run_reference(vol, units)
+    got = parity.run_product(vol, units)
+
+    # pyramid: every Gaussian level of every octave
+    report = []
+    rel, nbits = parity.compare_pyramids(got["det"], want["run"], report)
+    assert rel <= parity.VOXEL_REL_TOL, report
+    assert nbits == 0, [r for r in report if r[3]]
+
+    # candidates: identical list, identical order, identical strength
+    assert parity.cand_tuple_list(got["candidates"]) == parity.cand_tuple_list(want["candidates"])
+    np.testing.assert_array_equal(got["candidates"]["strength"], want["candidates"]["strength"])
+
+    # keypoints after orientation
+    pairs = parity.match_keypoints(want["keys"], got["keys"])
+    assert len(want["keys"]) > 0
+    assert len(pairs) >= parity.KP_MATCH_FRACTION * len(want["keys"])
+    assert len(got["keys"]) <= len(want["keys"]) / parity.KP_MATCH_FRACTION + 1
+    iw = [i for i, _ in pairs]
+    ig = [j for _, j in pairs]
+    np.testing.assert_allclose(got["keys"]["R"][ig], want["keys"]["R"][iw], atol=2e-5)
+    np.testing.assert_allclose(got["kp_matrix"][ig], want["kp_matrix"][iw], atol=parity.KP_POS_TOL)
+
+    # descriptors
+    cos = parity.cosine_rows(got["desc"][ig, 3:], want["desc"][iw, 3:])
+    assert cos.min() >= parity.DESC_COS_MIN, cos.min()
+    np.testing.assert_array_equal(got["desc"][ig, :3], want["desc"][iw, :3])
+
+
+def test_cli_sequence_128_top100():
+    """BASELINE.json configs[0]: kpSift3D's call sequence (cli/kpSift3D.c:116-135) on a
+    128^3 blob volume: detect, keep the 100 'strongest' (with the reference's strength
+    misalignment), describe."""
+    _ref()
+    vol = synth_volume(128, 128, 128)
+    want = parity.run_reference(vol, limit=100)
+    got = parity.run_product(vol, limit=100)
+    assert parity.cand_tuple_list(got["candidates"]) == parity.cand_tuple_list(want["candidates"])
+    assert len(got["keys"]) == len(want["keys"]) == 100
+    pairs = parity.match_keypoints(want["keys"], got["keys"])
+    assert len(pairs) >= 99
+    # same order after the sort, same (misaligned) strengths
+    same_slot = sum(1 for i, j in pairs if i == j)
+    assert same_slot >= 99
+    iw = [i for i, _ in pairs]
+    ig = [j for _, j in pairs]
+    np.testing.assert_array_equal(got["keys"]["strength"][ig], want["keys"]["strength"][iw])
+    cos = parity.cosine_rows(got["desc"][ig, 3:], want["desc"][iw, 3:])
+    assert cos.min() >= parity.DESC_COS_MIN
+
+
+def test_api_error_behaviour():
+    """Failure modes of the public API match the reference (SURVEY.md §8b 'Errors')."""
+    import sift3d_b200 as s3
+    d = s3.Detector()
+    assert d.set_peak_thresh(0.0) == -1 and d.set_peak_thresh(1.5) == -1 and d.set_peak_thresh(1.0) == 0
+    assert d.set_corner_thresh(-0.1) == -1 and d.set_corner_thresh(1.1) == -1 and d.set_corner_thresh(0.4) == 0
+    assert d.set_sigma_n(-1.0) == -1 and d.set_sigma0(-1.0) == -1
+    assert d.set_peak_thresh(0.1) == 0
+    # extract before any detect
+    kp = s3.KeypointStore()
+    with pytest.raises(s3.Sift3DError):
+        d.extract(kp)
+    # image smaller than 8 voxels in a dimension (sift.c:447-452)
+    with pytest.raises(s3.Sift3DError):
+        d.detect(s3.Image.from_array(np.ones((7, 16, 16), np.float32)))
+    # all-zero image: no keypoints, success; extract on an empty store fails (sift.c:1178)
+    kp = d.detect(s3.Image.from_array(np.zeros((16, 16, 16), np.float32)))
+    assert len(kp) == 0
+    assert kp.to_matrix().shape == (0, 3)
+    with pytest.raises(s3.Sift3DError):
+        d.extract(kp)
+    # multi-channel image rejected (sift.c:1221-1226)
+    with pytest.raises(s3.Sift3DError):
+        d.detect(s3.Image(16, 16, 16, 2))
+    d.close()
+
+
+def test_detector_reuse_and_replan():
+    """Same detector, second image with different dims re-plans; same dims does not."""
+    import sift3d_b200 as s3
+    _ref()
+    d = s3.Detector()
+    for dims, blobs in (((48, 48, 48), 27), ((40, 56, 32), 20), ((40, 56, 32), 21)):
+        vol = synth_volume(*dims, num_blobs=blobs, seed=1234 + blobs)
+        want = parity.run_reference(vol)
+        kp = d.detect(s3.Image.from_array(vol))
+        got = d.candidates()
+        assert parity.cand_tuple_list(got) == parity.cand_tuple_list(want["candidates"])
+        keys = kp.records()
+        assert len(parity.match_keypoints(want["keys"], keys)) >= 0.99 * len(want["keys"])
+    d.close()
