@@ -1,0 +1,7 @@
+/* sift.h -- source-compatibility shim: programs written against the reference's
+ * <sift.h> (fatimp/SIFT3D sift3d/sift.h) compile unchanged with -I<repo>/include/sift3d.
+ * All declarations live in ../sift3d.h. */
+#ifndef SIFT3D_B200_COMPAT_SIFT_H
+#define SIFT3D_B200_COMPAT_SIFT_H
+#include "../sift3d.h"
+#endif
