@@ -130,6 +130,11 @@ SIFT3D_EXPORT int sift3d_image_set_units(sift3d_image *, double ux, double uy, d
 SIFT3D_EXPORT void sift3d_image_get_units(const sift3d_image *, double *ux, double *uy, double *uz);
 SIFT3D_EXPORT void sift3d_image_dimensions(const sift3d_image *, int *nx, int *ny, int *nz, int *nc);
 
+/* Keep a copy of the image in the memory of CUDA device `device` (snapshot of the
+ * current host contents); detectors on that device then skip the upload. device < 0
+ * drops the copy. */
+SIFT3D_EXPORT int sift3d_image_make_resident(sift3d_image *, int device);
+
 /* Detector bound to a given CUDA device (sift3d_make_detector() uses
  * $SIFT3D_CUDA_DEVICE or device 0). */
 SIFT3D_EXPORT sift3d_detector *sift3d_make_detector_on_device(int device);

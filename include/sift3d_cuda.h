@@ -129,6 +129,24 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_get_timings(sift3d_cuda_ctx *ctx, sift3d_cuda
 SIFT3D_CUDA_EXPORT uint64_t sift3d_cuda_launch_count(sift3d_cuda_ctx *ctx);
 SIFT3D_CUDA_EXPORT int sift3d_cuda_synchronize(sift3d_cuda_ctx *ctx);
 
+/* Device-resident copies of image buffers (so a caller can keep inputs in HBM and
+ * skip the per-call upload). Returns NULL / -1 on failure. */
+SIFT3D_CUDA_EXPORT void *sift3d_cuda_device_upload(int device, const float *host, size_t count);
+SIFT3D_CUDA_EXPORT void sift3d_cuda_device_free(int device, void *dptr);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_ctx_device(sift3d_cuda_ctx *ctx);
+
+/* User timing marks on the context's stream (slots 0..7): record now / elapsed ms
+ * between two recorded marks (synchronises on `b`). */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_mark(sift3d_cuda_ctx *ctx, int slot);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_elapsed_ms(sift3d_cuda_ctx *ctx, int a, int b, float *ms);
+
+/* Per-blur profiling: when enabled, detect brackets every blur (all launches that
+ * produce one Gaussian level) with CUDA events. blur_ms returns the duration of the blur
+ * that produced level (o, s) in the last detect, and the number of launches it took. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_set_profiling(sift3d_cuda_ctx *ctx, int enabled);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_ms(sift3d_cuda_ctx *ctx, int o, int s, float *ms,
+                                           int *launches);
+
 #ifdef __cplusplus
 }
 #endif

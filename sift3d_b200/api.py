@@ -104,6 +104,12 @@ def libcuda():
     L.sift3d_cuda_launch_count.restype = C.c_uint64
     L.sift3d_cuda_launch_count.argtypes = [vp]
     L.sift3d_cuda_synchronize.argtypes = [vp]
+    L.sift3d_cuda_ctx_device.argtypes = [vp]
+    L.sift3d_cuda_mark.argtypes = [vp, C.c_int]
+    L.sift3d_cuda_elapsed_ms.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float)]
+    L.sift3d_cuda_set_profiling.argtypes = [vp, C.c_int]
+    L.sift3d_cuda_blur_ms.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float),
+                                      C.POINTER(C.c_int)]
     L._typed = True
     return L
 
@@ -150,6 +156,7 @@ def lib():
     L.sift3d_image_get_units.restype = None
     L.sift3d_image_dimensions.argtypes = [vp] + [C.POINTER(C.c_int)] * 4
     L.sift3d_image_dimensions.restype = None
+    L.sift3d_image_make_resident.argtypes = [vp, C.c_int]
     L.sift3d_keypoint_store_count.argtypes = [vp]
     L.sift3d_descriptor_store_count.argtypes = [vp]
     L.sift3d_keypoint_store_get.argtypes = [vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
@@ -201,6 +208,10 @@ class Image:
         im = cls(vol.shape[2], vol.shape[1], vol.shape[0], 1, units)
         im.array[...] = vol
         return im
+
+    def make_resident(self, device=0):
+        if self._L.sift3d_image_make_resident(self.handle, int(device)):
+            raise Sift3DError("sift3d_image_make_resident failed")
 
     def set_units(self, ux, uy, uz):
         if self._L.sift3d_image_set_units(self.handle, float(ux), float(uy), float(uz)):
@@ -329,13 +340,13 @@ class Detector:
     def set_sigma0(self, v): return int(self._L.sift3d_detector_set_sigma0(self.handle, float(v)))
 
     def detect(self, image: Image, store: KeypointStore | None = None) -> KeypointStore:
-        store = store or KeypointStore()
+        store = KeypointStore() if store is None else store
         if self._L.sift3d_detect_keypoints(self.handle, image.handle, store.handle):
             raise Sift3DError("sift3d_detect_keypoints failed")
         return store
 
     def extract(self, kp: KeypointStore, store: DescriptorStore | None = None) -> DescriptorStore:
-        store = store or DescriptorStore()
+        store = DescriptorStore() if store is None else store
         if self._L.sift3d_extract_descriptors(self.handle, kp.handle, store.handle):
             raise Sift3DError("sift3d_extract_descriptors failed")
         return store
@@ -383,6 +394,29 @@ class Detector:
         t = CudaTimings()
         self._C.sift3d_cuda_get_timings(self.ctx, C.byref(t))
         return t.as_dict()
+
+    def device(self) -> int:
+        return int(self._C.sift3d_cuda_ctx_device(self.ctx))
+
+    def mark(self, slot):
+        if self._C.sift3d_cuda_mark(self.ctx, int(slot)):
+            raise Sift3DError("sift3d_cuda_mark failed")
+
+    def elapsed_ms(self, a, b) -> float:
+        ms = C.c_float()
+        if self._C.sift3d_cuda_elapsed_ms(self.ctx, int(a), int(b), C.byref(ms)):
+            raise Sift3DError("sift3d_cuda_elapsed_ms failed")
+        return ms.value
+
+    def set_profiling(self, on=True):
+        self._C.sift3d_cuda_set_profiling(self.ctx, int(bool(on)))
+
+    def blur_ms(self, o, s):
+        """(milliseconds, launches) of the blur that produced level (o, s) in the last detect."""
+        ms, n = C.c_float(), C.c_int()
+        if self._C.sift3d_cuda_blur_ms(self.ctx, o, s, C.byref(ms), C.byref(n)):
+            raise Sift3DError("sift3d_cuda_blur_ms failed (profiling enabled?)")
+        return ms.value, n.value
 
     def launch_count(self) -> int:
         return int(self._C.sift3d_cuda_launch_count(self.ctx))

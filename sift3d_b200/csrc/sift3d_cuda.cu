@@ -66,6 +66,12 @@ struct sift3d_cuda_ctx {
     DevBuf desc_jobs, desc_out;
     sift3d_cuda_timings tm;
 
+    // user marks + per-blur profiling
+    cudaEvent_t marks[8] = {};
+    bool profiling = false;
+    std::vector<cudaEvent_t> blur_ev;    // 2 per level: [2 * (o * nlev + s + 1)] start, +1 stop
+    std::vector<int> blur_launches;      // launches per blur in the last detect
+
     Level &level(int o, int s) { return levels[(size_t) o * nlev + (s + 1)]; }
     float *d_taps(int filter /* -1 = first */) {
         return (float *) taps.p + (size_t) (filter + 1) * SIFT3D_CUDA_MAX_TAPS;
@@ -115,6 +121,7 @@ sift3d_cuda_ctx *sift3d_cuda_ctx_create(int device) {
         return nullptr;
     }
     for (int i = 0; i < EV_COUNT; i++) cudaEventCreate(&ctx->ev[i]);
+    for (int i = 0; i < 8; i++) cudaEventCreate(&ctx->marks[i]);
     for (int i = 0; i < DV_COUNT; i++) cudaEventCreate(&ctx->dv[i]);
     if (cudaMallocHost((void **) &ctx->h_counts, sizeof(int) * 64) != cudaSuccess ||
         upload_mesh() != 0) {
@@ -141,6 +148,9 @@ void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx) {
     ctx->kps.release();
     ctx->desc_jobs.release();
     ctx->desc_out.release();
+    for (int i = 0; i < 8; i++)
+        if (ctx->marks[i]) cudaEventDestroy(ctx->marks[i]);
+    for (cudaEvent_t e : ctx->blur_ev) cudaEventDestroy(e);
     if (ctx->h_counts) cudaFreeHost(ctx->h_counts);
     for (int i = 0; i < EV_COUNT; i++)
         if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -185,6 +195,10 @@ int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
 
     // level geometry: dims halve per octave (imutil.c:1545-1548)
     ctx->levels.assign((size_t) noct * nlev, Level());
+    for (cudaEvent_t e : ctx->blur_ev) cudaEventDestroy(e);
+    ctx->blur_ev.assign((size_t) 2 * noct * nlev, nullptr);
+    for (cudaEvent_t &e : ctx->blur_ev) S3D_CK(cudaEventCreate(&e));
+    ctx->blur_launches.assign((size_t) noct * nlev, 0);
     size_t total = 0;
     {
         int nx = d->nx, ny = d->ny, nz = d->nz;
@@ -304,9 +318,13 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     {
         Level &L = ctx->level(0, -1);
         const double u[3] = {L.ux, L.uy, L.uz};
+        const uint64_t l0 = ctx->launches;
+        if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[0], st));
         if (launch_blur(st, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
                         ctx->d_scalar(0), nullptr, nullptr, false, &ctx->launches))
             return -1;
+        if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[1], st));
+        ctx->blur_launches[0] = (int) (ctx->launches - l0);
     }
     for (int o = 0; o < noct; o++) {
         for (int s = 0; s < nlev - 1; s++) {
@@ -316,9 +334,14 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             // DoG level s-1 = G(s-1) - G(s); its max-abs is needed for keypoint levels only
             float *slot = nullptr;
             if (s - 1 >= 0 && s - 1 < kp) slot = ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (s - 1));
+            const size_t li = (size_t) o * nlev + (s + 1);
+            const uint64_t l0 = ctx->launches;
+            if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li], st));
             if (launch_blur(st, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
                             nullptr, slot, P.d, false, &ctx->launches))
                 return -1;
+            if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], st));
+            ctx->blur_launches[li] = (int) (ctx->launches - l0);
         }
         if (o != noct - 1) {
             const int ds = (nlev - 2) - 2 > -1 ? (nlev - 2) - 2 : -1;  // sift.c:696-697
@@ -541,6 +564,62 @@ int sift3d_cuda_get_timings(sift3d_cuda_ctx *ctx, sift3d_cuda_timings *t) {
 }
 
 uint64_t sift3d_cuda_launch_count(sift3d_cuda_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+void *sift3d_cuda_device_upload(int device, const float *host, size_t count) {
+    void *p = nullptr;
+    if (!host || count == 0 || cudaSetDevice(device) != cudaSuccess ||
+        cudaMalloc(&p, count * sizeof(float)) != cudaSuccess) {
+        S3D_ERR("sift3d_cuda_device_upload: %s\n", cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+    }
+    if (cudaMemcpy(p, host, count * sizeof(float), cudaMemcpyHostToDevice) != cudaSuccess) {
+        S3D_ERR("sift3d_cuda_device_upload: %s\n", cudaGetErrorString(cudaGetLastError()));
+        cudaFree(p);
+        return nullptr;
+    }
+    return p;
+}
+
+void sift3d_cuda_device_free(int device, void *dptr) {
+    if (!dptr) return;
+    cudaSetDevice(device);
+    cudaFree(dptr);
+}
+
+int sift3d_cuda_ctx_device(sift3d_cuda_ctx *ctx) { return ctx ? ctx->device : -1; }
+
+int sift3d_cuda_mark(sift3d_cuda_ctx *ctx, int slot) {
+    if (!ctx || slot < 0 || slot >= 8) return -1;
+    if (set_device(ctx)) return -1;
+    S3D_CK(cudaEventRecord(ctx->marks[slot], ctx->stream));
+    return 0;
+}
+
+int sift3d_cuda_elapsed_ms(sift3d_cuda_ctx *ctx, int a, int b, float *ms) {
+    if (!ctx || !ms || a < 0 || a >= 8 || b < 0 || b >= 8) return -1;
+    if (set_device(ctx)) return -1;
+    S3D_CK(cudaEventSynchronize(ctx->marks[b]));
+    S3D_CK(cudaEventElapsedTime(ms, ctx->marks[a], ctx->marks[b]));
+    return 0;
+}
+
+int sift3d_cuda_set_profiling(sift3d_cuda_ctx *ctx, int enabled) {
+    if (!ctx) return -1;
+    ctx->profiling = enabled != 0;
+    return 0;
+}
+
+int sift3d_cuda_blur_ms(sift3d_cuda_ctx *ctx, int o, int s, float *ms, int *launches) {
+    if (!ctx || !ctx->have_pyramid || !ctx->profiling || o < 0 || o >= ctx->desc.num_octaves ||
+        s < -1 || s > ctx->nlev - 2 || (s == -1 && o != 0))
+        return -1;
+    if (set_device(ctx)) return -1;
+    const size_t li = (size_t) o * ctx->nlev + (s + 1);
+    S3D_CK(cudaEventSynchronize(ctx->blur_ev[2 * li + 1]));
+    if (ms) S3D_CK(cudaEventElapsedTime(ms, ctx->blur_ev[2 * li], ctx->blur_ev[2 * li + 1]));
+    if (launches) *launches = ctx->blur_launches[li];
+    return 0;
+}
 
 int sift3d_cuda_synchronize(sift3d_cuda_ctx *ctx) {
     if (!ctx) return -1;

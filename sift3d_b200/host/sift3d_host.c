@@ -47,6 +47,8 @@ struct _sift3d_image {
     size_t size; /* voxels * channels */
     int nx, ny, nz, nc;
     double ux, uy, uz;
+    void *dev;   /* optional HBM-resident copy (sift3d_image_make_resident) */
+    int dev_id;
 };
 
 struct _sift3d_mat_rm {
@@ -258,8 +260,27 @@ sift3d_image *sift3d_make_image(const int nx, const int ny, const int nz, const 
 void sift3d_free_image(sift3d_image *im) {
     if (im == NULL)
         return;
+    if (im->dev != NULL)
+        sift3d_cuda_device_free(im->dev_id, im->dev);
     sift3d_cuda_host_free(im->data);
     free(im);
+}
+
+/* Extension: snapshot the current contents into device memory; later detects on a
+ * detector bound to the same device read that copy instead of uploading the host
+ * buffer. Call again after changing the host data. device < 0 drops the copy. */
+int sift3d_image_make_resident(sift3d_image *im, int device) {
+    if (im == NULL)
+        return SIFT3D_FAILURE;
+    if (im->dev != NULL) {
+        sift3d_cuda_device_free(im->dev_id, im->dev);
+        im->dev = NULL;
+    }
+    if (device < 0)
+        return SIFT3D_SUCCESS;
+    im->dev = sift3d_cuda_device_upload(device, im->data, im->size);
+    im->dev_id = device;
+    return im->dev != NULL ? SIFT3D_SUCCESS : SIFT3D_FAILURE;
 }
 
 sift3d_image *sift3d_read_image(const char *path) {
@@ -685,8 +706,12 @@ int sift3d_detect_keypoints(sift3d_detector *const d, const sift3d_image *const 
         d->plan_valid = 1;
     }
 
-    if (sift3d_cuda_detect(d->ctx, im->data, 0, units, d->peak_thresh, d->corner_thresh, &num_cand))
-        return SIFT3D_FAILURE;
+    {
+        const int resident = im->dev != NULL && im->dev_id == sift3d_cuda_ctx_device(d->ctx);
+        if (sift3d_cuda_detect(d->ctx, resident ? (const float *) im->dev : im->data, resident,
+                               units, d->peak_thresh, d->corner_thresh, &num_cand))
+            return SIFT3D_FAILURE;
+    }
 
     if ((size_t) num_cand > d->scratch_cap) {
         free(d->scratch);
