@@ -117,16 +117,37 @@ __device__ __forceinline__ bool face_hit(int f, float gx, float gy, float gz, fl
 }
 
 constexpr int kDescThreads = 256;
+constexpr float kFixScale = 1073741824.0f;          // 2^30 fixed-point units per 1.0
+constexpr double kFixInv = 1.0 / 1073741824.0;
+
+// Histogram accumulation in 64-bit fixed point held as two 32-bit words, so that the
+// only shared-memory atomic on the hot path is the native 32-bit integer add
+// (ATOMS.ADD); fp32 shared atomics compile to CAS spin loops (ATOMS.CAST.SPIN) and
+// serialise badly because neighbouring voxels hit the same bins. Integer adds commute,
+// so descriptors are bit-reproducible from run to run.
+__device__ __forceinline__ void fix_add(unsigned *lo, unsigned *hi, int i, float v) {
+    const long long q = __float2ll_rn(v * kFixScale);
+    const unsigned ql = (unsigned) q;
+    unsigned qh = (unsigned) ((unsigned long long) q >> 32);
+    const unsigned old = atomicAdd(lo + i, ql);
+    qh += (unsigned) (old + ql < old);  // carry out of the low word
+    if (qh) atomicAdd(hi + i, qh);
+}
 
 __global__ void __launch_bounds__(kDescThreads)
 descriptor_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ desc_out) {
+    __shared__ unsigned hlo[kDescNumel];
+    __shared__ unsigned hhi[kDescNumel];
     __shared__ float hist[kDescNumel];
     __shared__ double red[kDescThreads / 32];
     __shared__ double norm_sh;
     const int ki = blockIdx.x;
     if (ki >= n) return;
     const DescJob J = jobs[ki];
-    for (int i = threadIdx.x; i < kDescNumel; i += kDescThreads) hist[i] = 0.0f;
+    for (int i = threadIdx.x; i < kDescNumel; i += kDescThreads) {
+        hlo[i] = 0u;
+        hhi[i] = 0u;
+    }
     __syncthreads();
 
     const float *__restrict__ img = J.img;
@@ -151,8 +172,8 @@ descriptor_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ d
     const int y1 = (int) fminf(ceilf(__fadd_rn(cy, __fdiv_rn(rad, uyf))), (float) (ny - 2));
     const int z0 = (int) fmaxf(floorf(__fsub_rn(cz, __fdiv_rn(rad, uzf))), 1.0f);
     const int z1 = (int) fminf(ceilf(__fadd_rn(cz, __fdiv_rn(rad, uzf))), (float) (nz - 2));
-    const int wx = max(x1 - x0 + 1, 0), wy = max(y1 - y0 + 1, 0), wz = max(z1 - z0 + 1, 0);
-    const int total = wx * wy * wz;
+    const int wy = max(y1 - y0 + 1, 0), wz = max(z1 - z0 + 1, 0);
+    const int nrows = (x1 >= x0) ? wy * wz : 0;
     const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
 
     // Rt = R^T (sift.c:1462-1464): Rt[i][j] = R[j][i]
@@ -160,92 +181,125 @@ descriptor_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ d
     const float r10 = J.R[3], r11 = J.R[4], r12 = J.R[5];
     const float r20 = J.R[6], r21 = J.R[7], r22 = J.R[8];
 
-    for (int i = threadIdx.x; i < total; i += kDescThreads) {
-        const int lx = i % wx;
-        const int tq = i / wx;
-        const int ly = tq % wy;
-        const int lz = tq / wy;
-        const int x = x0 + lx, y = y0 + ly, z = z0 + lz;
-        const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
+    // One (y, z) row of the window per thread at a time; the thread walks the row in x.
+    // Consecutive voxels mostly fall into the same (spatial cell, icosahedron face), so
+    // their 8 x 3 weighted contributions are summed in registers and flushed to shared
+    // memory only when that key changes.
+    float acc[8][3];
+    int cur_key = -1;
+    int ci0 = 0, ci1 = 0, ci2 = 0, cbx = 0, cby = 0, cbz = 0;
+
+#define S3D_FLUSH()                                                                        \
+    if (cur_key >= 0) {                                                                    \
+        _Pragma("unroll") for (int c = 0; c < 8; c++) {                                    \
+            const int hx = cbx + (c >> 2), hy = cby + ((c >> 1) & 1), hz = cbz + (c & 1);  \
+            if (hx < kHistPerDim && hy < kHistPerDim && hz < kHistPerDim) {                \
+                const int hb = (hx + hy * kHistPerDim + hz * kHistPerDim * kHistPerDim) * kVerts; \
+                if (acc[c][0] != 0.0f) fix_add(hlo, hhi, hb + ci0, acc[c][0]);             \
+                if (acc[c][1] != 0.0f) fix_add(hlo, hhi, hb + ci1, acc[c][1]);             \
+                if (acc[c][2] != 0.0f) fix_add(hlo, hhi, hb + ci2, acc[c][2]);             \
+            }                                                                              \
+        }                                                                                  \
+    }
+
+    for (int r = threadIdx.x; r < nrows; r += kDescThreads) {
+        const int y = y0 + r % wy, z = z0 + r / wy;
         const float dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);
         const float dz = __fmul_rn(__fsub_rn((float) z, cz), uzf);
-        const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-        if (sq > rad2) continue;
+        // conservative chord of the sphere along this row; the exact test stays per voxel
+        const float rem = rad2 * 1.0001f - dy * dy - dz * dz;
+        if (rem < 0.0f) continue;
+        const float half = sqrtf(rem) * ixu + 1.0f;
+        const int xa = max(x0, (int) floorf(cx - half));
+        const int xb = min(x1, (int) ceilf(cx + half));
+        const float *__restrict__ row = img + (size_t) z * zs + (size_t) y * ys;
+        for (int x = xa; x <= xb; x++) {
+            const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
+            const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+            if (sq > rad2) continue;
+            // vkp = Rt * vim (SIFT3D_MUL_MAT_RM_CVEC, immacros.h:326-342)
+            const float kx = __fadd_rn(__fadd_rn(__fmul_rn(r00, dx), __fmul_rn(r10, dy)), __fmul_rn(r20, dz));
+            const float ky = __fadd_rn(__fadd_rn(__fmul_rn(r01, dx), __fmul_rn(r11, dy)), __fmul_rn(r21, dz));
+            const float kz = __fadd_rn(__fadd_rn(__fmul_rn(r02, dx), __fmul_rn(r12, dy)), __fmul_rn(r22, dz));
+            const float vbx = __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
+            const float vby = __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
+            const float vbz = __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
+            if (vbx < 0.0f || vby < 0.0f || vbz < 0.0f || vbx >= (float) kHistPerDim ||
+                vby >= (float) kHistPerDim || vbz >= (float) kHistPerDim)
+                continue;
 
-        // vkp = Rt * vim (SIFT3D_MUL_MAT_RM_CVEC, immacros.h:326-342)
-        const float kx = __fadd_rn(__fadd_rn(__fmul_rn(r00, dx), __fmul_rn(r10, dy)), __fmul_rn(r20, dz));
-        const float ky = __fadd_rn(__fadd_rn(__fmul_rn(r01, dx), __fmul_rn(r11, dy)), __fmul_rn(r21, dz));
-        const float kz = __fadd_rn(__fadd_rn(__fmul_rn(r02, dx), __fmul_rn(r12, dy)), __fmul_rn(r22, dz));
-        const float vbx = __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
-        const float vby = __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
-        const float vbz = __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
-        if (vbx < 0.0f || vby < 0.0f || vbz < 0.0f || vbx >= (float) kHistPerDim ||
-            vby >= (float) kHistPerDim || vbz >= (float) kHistPerDim)
-            continue;
+            float gx = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + 1], row[x - 1])), ixu);
+            float gy = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys])), iyu);
+            float gz = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + zs], row[(ptrdiff_t) x - (ptrdiff_t) zs])), izu);
+            const float w = expf(__fdiv_rn(__fmul_rn(-0.5f, sq), sig2));  // sift.c:1498
+            gx = __fmul_rn(gx, w);
+            gy = __fmul_rn(gy, w);
+            gz = __fmul_rn(gz, w);
+            const float rx = __fadd_rn(__fadd_rn(__fmul_rn(r00, gx), __fmul_rn(r10, gy)), __fmul_rn(r20, gz));
+            const float ry = __fadd_rn(__fadd_rn(__fmul_rn(r01, gx), __fmul_rn(r11, gy)), __fmul_rn(r21, gz));
+            const float rz = __fadd_rn(__fadd_rn(__fmul_rn(r02, gx), __fmul_rn(r12, gy)), __fmul_rn(r22, gz));
 
-        const size_t idx = (size_t) z * zs + (size_t) y * ys + x;
-        float gx = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(img[idx + 1], img[idx - 1])), ixu);
-        float gy = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(img[idx + ys], img[idx - ys])), iyu);
-        float gz = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(img[idx + zs], img[idx - zs])), izu);
-        const float w = expf(__fdiv_rn(__fmul_rn(-0.5f, sq), sig2));  // sift.c:1498
-        gx = __fmul_rn(gx, w);
-        gy = __fmul_rn(gy, w);
-        gz = __fmul_rn(gz, w);
-        const float rx = __fadd_rn(__fadd_rn(__fmul_rn(r00, gx), __fmul_rn(r10, gy)), __fmul_rn(r20, gz));
-        const float ry = __fadd_rn(__fadd_rn(__fmul_rn(r01, gx), __fmul_rn(r11, gy)), __fmul_rn(r21, gz));
-        const float rz = __fadd_rn(__fadd_rn(__fmul_rn(r02, gx), __fmul_rn(r12, gy)), __fmul_rn(r22, gz));
-
-        // icos_hist_bin (sift.c:1254-1291)
-        const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz));
-        if ((double) n2 < kBaryEps) continue;
-        // Fast selection: the face whose centre direction is closest to the ray. If the
-        // ray is comfortably inside that face no other face can pass the reference's
-        // (>= -bary_eps) test, so it is also the *first* passing face. Otherwise fall back
-        // to the literal first-hit scan so ties on edges/vertices resolve as in the reference.
-        int best = 0;
-        float bestd = -FLT_MAX;
+            // icos_hist_bin (sift.c:1254-1291)
+            const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz));
+            if ((double) n2 < kBaryEps) continue;
+            // Fast selection: the face whose centre direction is closest to the ray. If the
+            // ray is comfortably inside that face no other face can pass the reference's
+            // (>= -bary_eps) test, so it is also the *first* passing face. Otherwise fall
+            // back to the literal first-hit scan so ties on edges/vertices resolve as in
+            // the reference.
+            int best = 0;
+            float bestd = -FLT_MAX;
 #pragma unroll
-        for (int f = 0; f < kFaces; f++) {
-            const float d = fmaf(rx, c_mesh.ctr[f][0], fmaf(ry, c_mesh.ctr[f][1], rz * c_mesh.ctr[f][2]));
-            if (d > bestd) { bestd = d; best = f; }
-        }
-        float bx, by, bz;
-        int face = -1;
-        if (face_hit(best, rx, ry, rz, bx, by, bz) && bx > 1e-3f && by > 1e-3f && bz > 1e-3f) {
-            face = best;
-        } else {
             for (int f = 0; f < kFaces; f++) {
-                if (face_hit(f, rx, ry, rz, bx, by, bz)) { face = f; break; }
+                const float d = fmaf(rx, c_mesh.ctr[f][0], fmaf(ry, c_mesh.ctr[f][1], rz * c_mesh.ctr[f][2]));
+                if (d > bestd) { bestd = d; best = f; }
             }
-        }
-        if (face < 0) continue;  // "unreachable" in the reference (sift.c:1288-1290)
-        const float mag = sqrtf(n2);
-        const int i0 = c_mesh.idx[face][0], i1 = c_mesh.idx[face][1], i2 = c_mesh.idx[face][2];
-
-        // SIFT3D_desc_acc_interp (sift.c:1318-1397)
-        const float fx = __fsub_rn(vbx, floorf(vbx));
-        const float fy = __fsub_rn(vby, floorf(vby));
-        const float fz = __fsub_rn(vbz, floorf(vbz));
-        const int bxi = (int) vbx, byi = (int) vby, bzi = (int) vbz;
-#pragma unroll
-        for (int ddx = 0; ddx < 2; ddx++) {
-#pragma unroll
-            for (int ddy = 0; ddy < 2; ddy++) {
-#pragma unroll
-                for (int ddz = 0; ddz < 2; ddz++) {
-                    const int hx = bxi + ddx, hy = byi + ddy, hz = bzi + ddz;
-                    if (hx >= kHistPerDim || hy >= kHistPerDim || hz >= kHistPerDim) continue;
-                    const float wgt = __fmul_rn(
-                        __fmul_rn(ddx == 0 ? __fsub_rn(1.0f, fx) : fx, ddy == 0 ? __fsub_rn(1.0f, fy) : fy),
-                        ddz == 0 ? __fsub_rn(1.0f, fz) : fz);
-                    const float mw = __fmul_rn(mag, wgt);
-                    float *h = hist + (hx + hy * kHistPerDim + hz * kHistPerDim * kHistPerDim) * kVerts;
-                    atomicAdd(h + i0, __fmul_rn(mw, bx));
-                    atomicAdd(h + i1, __fmul_rn(mw, by));
-                    atomicAdd(h + i2, __fmul_rn(mw, bz));
+            float bx, by, bz;
+            int face = -1;
+            if (face_hit(best, rx, ry, rz, bx, by, bz) && bx > 1e-3f && by > 1e-3f && bz > 1e-3f) {
+                face = best;
+            } else {
+                for (int f = 0; f < kFaces; f++) {
+                    if (face_hit(f, rx, ry, rz, bx, by, bz)) { face = f; break; }
                 }
             }
+            if (face < 0) continue;  // "unreachable" in the reference (sift.c:1288-1290)
+            const float mag = sqrtf(n2);
+
+            // SIFT3D_desc_acc_interp (sift.c:1318-1397)
+            const int bxi = (int) vbx, byi = (int) vby, bzi = (int) vbz;
+            const int key = bxi | (byi << 2) | (bzi << 4) | (face << 6);
+            if (key != cur_key) {
+                S3D_FLUSH();
+                cur_key = key;
+                cbx = bxi; cby = byi; cbz = bzi;
+                ci0 = c_mesh.idx[face][0]; ci1 = c_mesh.idx[face][1]; ci2 = c_mesh.idx[face][2];
+#pragma unroll
+                for (int c = 0; c < 8; c++) acc[c][0] = acc[c][1] = acc[c][2] = 0.0f;
+            }
+            const float fx = __fsub_rn(vbx, floorf(vbx));
+            const float fy = __fsub_rn(vby, floorf(vby));
+            const float fz = __fsub_rn(vbz, floorf(vbz));
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                const int ddx = c >> 2, ddy = (c >> 1) & 1, ddz = c & 1;
+                const float wgt = __fmul_rn(
+                    __fmul_rn(ddx == 0 ? __fsub_rn(1.0f, fx) : fx, ddy == 0 ? __fsub_rn(1.0f, fy) : fy),
+                    ddz == 0 ? __fsub_rn(1.0f, fz) : fz);
+                const float mw = __fmul_rn(mag, wgt);
+                acc[c][0] = __fadd_rn(acc[c][0], __fmul_rn(mw, bx));
+                acc[c][1] = __fadd_rn(acc[c][1], __fmul_rn(mw, by));
+                acc[c][2] = __fadd_rn(acc[c][2], __fmul_rn(mw, bz));
+            }
         }
+        S3D_FLUSH();
+        cur_key = -1;
+    }
+#undef S3D_FLUSH
+    __syncthreads();
+    for (int i = threadIdx.x; i < kDescNumel; i += kDescThreads) {
+        const long long q = (long long) (((unsigned long long) hhi[i] << 32) | (unsigned long long) hlo[i]);
+        hist[i] = (float) ((double) q * kFixInv);
     }
     __syncthreads();
 

@@ -72,9 +72,9 @@ struct _sift3d_keypoint_store {
 };
 
 struct _sift3d_descriptor_store {
-    float *desc;  /* num * 768 */
+    float *desc;  /* num * 768, page-locked */
     double *xyzs; /* num * 4: base-octave x, y, z and scale */
-    size_t num;
+    size_t num, cap;
     int nx, ny, nz;
 };
 
@@ -443,8 +443,8 @@ sift3d_detector *sift3d_make_detector(void) { return sift3d_make_detector_on_dev
 void sift3d_free_detector(sift3d_detector *d) {
     if (d == NULL)
         return;
+    sift3d_cuda_host_free(d->scratch);
     sift3d_cuda_ctx_destroy(d->ctx);
-    free(d->scratch);
     free(d);
 }
 
@@ -627,7 +627,7 @@ sift3d_descriptor_store *sift3d_make_descriptor_store(void) {
 void sift3d_free_descriptor_store(sift3d_descriptor_store *ds) {
     if (ds == NULL)
         return;
-    free(ds->desc);
+    sift3d_cuda_host_free(ds->desc);
     free(ds->xyzs);
     free(ds);
 }
@@ -714,9 +714,11 @@ int sift3d_detect_keypoints(sift3d_detector *const d, const sift3d_image *const 
     }
 
     if ((size_t) num_cand > d->scratch_cap) {
-        free(d->scratch);
-        d->scratch_cap = (size_t) num_cand + 1024;
-        d->scratch = (sift3d_cuda_keypoint *) malloc(d->scratch_cap * sizeof(sift3d_cuda_keypoint));
+        /* page-locked, so the candidate download runs at PCIe speed */
+        sift3d_cuda_host_free(d->scratch);
+        d->scratch_cap = (size_t) num_cand * 2 + 1024;
+        d->scratch = (sift3d_cuda_keypoint *)
+            sift3d_cuda_host_alloc(d->scratch_cap * sizeof(sift3d_cuda_keypoint));
         if (d->scratch == NULL) {
             d->scratch_cap = 0;
             return SIFT3D_FAILURE;
@@ -803,9 +805,15 @@ int sift3d_extract_descriptors(sift3d_detector *const d, const sift3d_keypoint_s
     }
     num = (int) kp->num;
     keys = (sift3d_cuda_keypoint *) malloc((size_t) num * sizeof(*keys));
-    dbuf = (float *) realloc(desc->desc, (size_t) num * DESC_NUMEL * sizeof(float));
-    if (dbuf != NULL)
-        desc->desc = dbuf;
+    if ((size_t) num > desc->cap) {
+        /* page-locked, so the descriptor download runs at PCIe speed */
+        sift3d_cuda_host_free(desc->desc);
+        desc->cap = (size_t) num + (size_t) num / 2 + 64;
+        desc->desc = (float *) sift3d_cuda_host_alloc(desc->cap * DESC_NUMEL * sizeof(float));
+        if (desc->desc == NULL)
+            desc->cap = 0;
+    }
+    dbuf = desc->desc;
     xbuf = (double *) realloc(desc->xyzs, (size_t) num * 4 * sizeof(double));
     if (xbuf != NULL)
         desc->xyzs = xbuf;
