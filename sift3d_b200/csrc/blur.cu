@@ -13,6 +13,8 @@
 // Bit parity: the reference build (x86-64, no -mfma) rounds every multiply and every add
 // to fp32 separately and accumulates taps in ascending d. All arithmetic below uses
 // __fmul_rn/__fadd_rn/__fsub_rn/__fdiv_rn so nvcc can never contract it into FMAs.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace s3d {
@@ -144,6 +146,12 @@ absdiffmax_kernel(const float *__restrict__ a, const float *__restrict__ b, size
     block_atomic_max(m, out);
 }
 
+}  // namespace s3d
+
+#include "blur_fused.cuh"
+
+namespace s3d {
+
 // ---------------------------------------------------------------------------------------
 // Launchers
 // ---------------------------------------------------------------------------------------
@@ -155,17 +163,124 @@ static inline AxisSpec axis_spec(int n, double unit, int hw) {
     return a;
 }
 
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                  const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+                cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn) p;
+        else
+            cudaGetLastError();
+    }
+    return fn;
+}
+
+template <int HW, int TY>
+static int launch_fused_t(cudaStream_t st, const FusedParams &P, int nzc) {
+    using C = FusedCfg<HW>;
+    constexpr int TROWS = TY + 2 * HW;
+    constexpr int TILE_FLOATS = TROWS * C::BW;
+    constexpr int TILE_STRIDE = (TILE_FLOATS + 31) / 32 * 32;
+    constexpr size_t SMEM = (size_t) (2 * TILE_STRIDE + 2 * TROWS * kFTX) * 4 + 16;
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (enc == nullptr) return 1;
+    CUtensorMap tmap;
+    const cuuint64_t gdim[3] = {(cuuint64_t) P.nx, (cuuint64_t) P.ny, (cuuint64_t) P.nz};
+    const cuuint64_t gstr[2] = {(cuuint64_t) P.nx * 4, (cuuint64_t) P.nx * P.ny * 4};
+    const cuuint32_t box[3] = {(cuuint32_t) C::BW, (cuuint32_t) TROWS, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    if (enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *) P.src, gdim, gstr, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return 1;
+    static bool attr_set = false;
+    if (!attr_set) {
+        S3D_CK(cudaFuncSetAttribute(blur_fused_unit_kernel<HW, TY>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int) SMEM));
+        attr_set = true;
+    }
+    dim3 grid((unsigned) ((P.nx + kFTX - 1) / kFTX), (unsigned) ((P.ny + TY - 1) / TY), (unsigned) nzc);
+    blur_fused_unit_kernel<HW, TY><<<grid, 8 * TY, SMEM, st>>>(tmap, P);
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+// Returns 0 if launched, 1 if this blur is not eligible for the fused kernel, -1 on error.
+template <int TY>
+static int launch_fused(cudaStream_t st, FusedParams &P, int hw, int occ) {
+    const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
+    // one wave: as many z-chunks as fit 148 SMs x resident CTAs, each chunk long enough
+    // that the z halo (2*hw planes of x/y work per chunk) stays a small fraction
+    int nzc = (kNumSMs * occ) / tiles;
+    if (nzc < 1) nzc = 1;
+    while (nzc > 1 && (P.nz + nzc - 1) / nzc < 4 * hw + 4) nzc--;
+    int zc = (P.nz + nzc - 1) / nzc;
+    nzc = (P.nz + zc - 1) / zc;
+    // the last chunk must hold all right-boundary outputs (hw + 1 planes)
+    while (nzc > 1 && P.nz - (nzc - 1) * zc < hw + 1) {
+        zc++;
+        nzc = (P.nz + zc - 1) / zc;
+    }
+    P.zchunk = zc;
+    switch (hw) {
+    case 1: return launch_fused_t<1, TY>(st, P, nzc);
+    case 2: return launch_fused_t<2, TY>(st, P, nzc);
+    case 3: return launch_fused_t<3, TY>(st, P, nzc);
+    case 4: return launch_fused_t<4, TY>(st, P, nzc);
+    case 5: return launch_fused_t<5, TY>(st, P, nzc);
+    case 6: return launch_fused_t<6, TY>(st, P, nzc);
+    case 7: return launch_fused_t<7, TY>(st, P, nzc);
+    case 8: return launch_fused_t<8, TY>(st, P, nzc);
+    default: return 1;
+    }
+}
+
 int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, float *tmp_b,
                 int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
                 const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
-                const float *dog_prev, bool force_generic, uint64_t *launches) {
-    (void) force_generic;
+                const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches) {
     const int hw = f.width / 2;
     const size_t total = (size_t) nx * ny * nz;
     const unsigned blocks = (unsigned) ((total + 255) / 256);
     const AxisSpec ax = axis_spec(nx, units[0], hw);
     const AxisSpec ay = axis_spec(ny, units[1], hw);
     const AxisSpec az = axis_spec(nz, units[2], hw);
+
+    // Fused single-launch path: unit tap spacing on every axis, TMA-compatible rows.
+    static const int ty_env = getenv("SIFT3D_CUDA_TY") ? atoi(getenv("SIFT3D_CUDA_TY")) : 64;
+    const int ty = (ty_env == 32 || ny < 64) ? 32 : 64;
+    if (!force_generic && ax.uf == 1.0f && ay.uf == 1.0f && az.uf == 1.0f && hw >= 1 && hw <= 8 &&
+        f.width <= kMaxParamTaps && nx % 4 == 0 && nx >= kFTX && ny >= ty && nz >= 4 * hw + 4 &&
+        ((uintptr_t) src & 15) == 0 && ((uintptr_t) dst & 15) == 0 &&
+        (d_dogmax_slot == nullptr || dog_prev == src)) {
+        FusedParams P;
+        P.src = src;
+        P.dst = dst;
+        P.ds_dst = ds_dst;
+        P.dogmax = d_dogmax_slot;
+        P.divisor = d_divisor;
+        P.taps_g = d_taps;
+        P.nx = nx; P.ny = ny; P.nz = nz;
+        P.zchunk = nz;
+        for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];
+        for (int i = f.width; i < kMaxParamTaps; i++) P.taps.k[i] = 0.0f;
+        if (d_dogmax_slot != nullptr) S3D_CK(cudaMemsetAsync(d_dogmax_slot, 0, sizeof(float), st));
+        const int r = ty == 64 ? launch_fused<64>(st, P, hw, 1) : launch_fused<32>(st, P, hw, 2);
+        if (r < 0) return -1;
+        if (r == 0) {
+            if (launches) *launches += 1;
+            return 0;
+        }
+    }
 
     blur_axis_generic_kernel<0><<<blocks, 256, 0, st>>>(src, tmp_a, nx, ny, nz, d_taps, hw, ax.uf,
                                                         ax.uhw, d_divisor);
@@ -176,6 +291,9 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
     if (launches) *launches += 3;
     if (d_dogmax_slot != nullptr && dog_prev != nullptr) {
         if (launch_absdiffmax(st, dog_prev, dst, total, d_dogmax_slot, launches)) return -1;
+    }
+    if (ds_dst != nullptr) {
+        if (launch_downsample(st, dst, ds_dst, nx, ny, nz, launches)) return -1;
     }
     S3D_CK(cudaGetLastError());
     return 0;

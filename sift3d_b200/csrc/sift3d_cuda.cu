@@ -321,11 +321,12 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         const uint64_t l0 = ctx->launches;
         if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[0], st));
         if (launch_blur(st, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
-                        ctx->d_scalar(0), nullptr, nullptr, false, &ctx->launches))
+                        ctx->d_scalar(0), nullptr, nullptr, nullptr, false, &ctx->launches))
             return -1;
         if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[1], st));
         ctx->blur_launches[0] = (int) (ctx->launches - l0);
     }
+    const int ds_level = (nlev - 2) - 2 > -1 ? (nlev - 2) - 2 : -1;  // sift.c:696-697
     for (int o = 0; o < noct; o++) {
         for (int s = 0; s < nlev - 1; s++) {
             Level &P = ctx->level(o, s - 1);
@@ -337,17 +338,13 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             const size_t li = (size_t) o * nlev + (s + 1);
             const uint64_t l0 = ctx->launches;
             if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li], st));
+            // the level that seeds the next octave is decimated as it is produced
+            float *ds_dst = (o != noct - 1 && s == ds_level) ? ctx->level(o + 1, -1).d : nullptr;
             if (launch_blur(st, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
-                            nullptr, slot, P.d, false, &ctx->launches))
+                            nullptr, slot, P.d, ds_dst, false, &ctx->launches))
                 return -1;
             if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], st));
             ctx->blur_launches[li] = (int) (ctx->launches - l0);
-        }
-        if (o != noct - 1) {
-            const int ds = (nlev - 2) - 2 > -1 ? (nlev - 2) - 2 : -1;  // sift.c:696-697
-            Level &S = ctx->level(o, ds);
-            Level &T = ctx->level(o + 1, -1);
-            if (launch_downsample(st, S.d, T.d, S.nx, S.ny, S.nz, &ctx->launches)) return -1;
         }
     }
     S3D_CK(cudaEventRecord(ctx->ev[EV_PYR], st));
@@ -543,7 +540,7 @@ int sift3d_cuda_blur(sift3d_cuda_ctx *ctx, const float *host_src, float *host_ds
                         ctx->stream) != cudaSuccess)
         goto done;
     if (launch_blur(ctx->stream, (const float *) a.p, (float *) b.p, (float *) c.p, (float *) d.p,
-                    nx, ny, nz, units, *f, (const float *) t.p, nullptr, nullptr, nullptr,
+                    nx, ny, nz, units, *f, (const float *) t.p, nullptr, nullptr, nullptr, nullptr,
                     force_generic != 0, &ctx->launches))
         goto done;
     if (cudaMemcpyAsync(host_dst, b.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
