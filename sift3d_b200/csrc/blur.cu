@@ -190,7 +190,8 @@ static int launch_fused_t(cudaStream_t st, const FusedParams &P, int nzc) {
     constexpr int TROWS = TY + 2 * HW;
     constexpr int TILE_FLOATS = TROWS * C::BW;
     constexpr int TILE_STRIDE = (TILE_FLOATS + 31) / 32 * 32;
-    constexpr size_t SMEM = (size_t) (2 * TILE_STRIDE + 2 * TROWS * kFTX) * 4 + 16;
+    constexpr size_t SMEM = (size_t) (kNB * TILE_STRIDE + 2 * TROWS * kFTX) * 4 + kNB * 8 +
+                            2 * (HW + 1) * 4 + 16;
     EncodeTiledFn enc = encode_tiled_fn();
     if (enc == nullptr) return 1;
     CUtensorMap tmap;
@@ -218,14 +219,15 @@ static int launch_fused_t(cudaStream_t st, const FusedParams &P, int nzc) {
 template <int TY>
 static int launch_fused(cudaStream_t st, FusedParams &P, int hw, int occ) {
     const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
-    // one wave: as many z-chunks as fit 148 SMs x resident CTAs, each chunk long enough
-    // that the z halo (2*hw planes of x/y work per chunk) stays a small fraction
+    // One wave: as many z-chunks as fit 148 SMs x resident CTAs. Every chunk pays 2*hw halo
+    // planes of x/y work, so chunks are as long as one wave allows. Constraints: a chunk
+    // below the top must not reach plane nz-1 with its halo and a chunk above the bottom
+    // must not reach below plane 0: every chunk holds at least hw + 1 outputs.
     int nzc = (kNumSMs * occ) / tiles;
     if (nzc < 1) nzc = 1;
-    while (nzc > 1 && (P.nz + nzc - 1) / nzc < 4 * hw + 4) nzc--;
     int zc = (P.nz + nzc - 1) / nzc;
+    if (zc < hw + 1) zc = hw + 1;
     nzc = (P.nz + zc - 1) / zc;
-    // the last chunk must hold all right-boundary outputs (hw + 1 planes)
     while (nzc > 1 && P.nz - (nzc - 1) * zc < hw + 1) {
         zc++;
         nzc = (P.nz + zc - 1) / zc;
@@ -255,12 +257,15 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
     const AxisSpec ay = axis_spec(ny, units[1], hw);
     const AxisSpec az = axis_spec(nz, units[2], hw);
 
-    // Fused single-launch path: unit tap spacing on every axis, TMA-compatible rows.
+    // Fused single-launch path: unit tap spacing on every axis, TMA-compatible rows, taps
+    // symmetric bit for bit (the kernel shares the products of twin taps).
     static const int ty_env = getenv("SIFT3D_CUDA_TY") ? atoi(getenv("SIFT3D_CUDA_TY")) : 64;
     const int ty = (ty_env == 32 || ny < 64) ? 32 : 64;
-    if (!force_generic && ax.uf == 1.0f && ay.uf == 1.0f && az.uf == 1.0f && hw >= 1 && hw <= 8 &&
-        f.width <= kMaxParamTaps && nx % 4 == 0 && nx >= kFTX && ny >= ty && nz >= 4 * hw + 4 &&
-        ((uintptr_t) src & 15) == 0 && ((uintptr_t) dst & 15) == 0 &&
+    bool symmetric = true;
+    for (int i = 0; i < hw; i++) symmetric = symmetric && f.taps[i] == f.taps[f.width - 1 - i];
+    if (!force_generic && symmetric && ax.uf == 1.0f && ay.uf == 1.0f && az.uf == 1.0f && hw >= 1 &&
+        hw <= 8 && f.width <= kMaxParamTaps && nx % 4 == 0 && nx >= kFTX && ny >= ty &&
+        ny >= 2 * hw + 2 && nz >= 2 * hw + 2 && ((uintptr_t) src & 15) == 0 &&
         (d_dogmax_slot == nullptr || dog_prev == src)) {
         FusedParams P;
         P.src = src;
@@ -268,7 +273,6 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         P.ds_dst = ds_dst;
         P.dogmax = d_dogmax_slot;
         P.divisor = d_divisor;
-        P.taps_g = d_taps;
         P.nx = nx; P.ny = ny; P.nz = nz;
         P.zchunk = nz;
         for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];

@@ -2,22 +2,34 @@
 // previous one (x, y and z passes fused; 1 HBM read + 1 HBM write per voxel), for levels
 // whose tap spacing is exactly one voxel on every axis (octave 0 with units (1,1,1)).
 //
-//   * a CTA owns a TX x TY column of the volume and marches along z through a z-chunk;
+// Structure (v3):
+//   * a CTA owns a 32 x TY column of the volume and marches DOWN z through a z-chunk;
 //   * every input plane tile (with x/y halo) is staged in shared memory by TMA
-//     (cp.async.bulk.tensor.3d + mbarrier, double buffered, issued by one thread);
-//   * x pass: shared -> registers (LDS.128) -> shared; y pass: shared -> registers;
-//   * z pass: a (2*HW+1)-deep window of y-filtered values lives in registers; the window
-//     rotation is resolved at compile time by switching on the phase;
+//     (cp.async.bulk.tensor.3d + mbarrier, 3 buffers, issued by one thread; out-of-volume
+//     halo is zero filled by TMA and never used);
+//   * x pass: item = (tile row, 4-column group): LDS.128 -> registers -> STS.128 into a
+//     double-buffered x-filtered tile; the x pass of plane n+1 and the y/z pass of plane n
+//     run between the same pair of barriers (one __syncthreads per plane);
+//   * y pass: thread (x = lane, 4 consecutive rows) gathers 4 + 2*HW rows (LDS.32,
+//     conflict free) and produces 4 y-filtered values;
+//   * z pass in registers, scatter form: because the march is in DESCENDING z, plane p is
+//     tap t of output p - HW + t with t growing as the march proceeds, i.e. the partial sums
+//     receive their taps in ascending d exactly like convolve_sep_gen accumulates them.
+//     Each arriving value is multiplied by the HW + 1 distinct taps once (the Gaussian is
+//     symmetric bit for bit, checked on the host) and added into 2*HW + 1 running sums that
+//     shift by one slot per plane (the shift is free: A[t] = A[t-1] + p);
 //   * epilogue: max|G(s-1) - G(s)| (the DoG level's max-abs, sift.c:822-826) and the 2x
 //     decimation into the next octave (imutil.c:591-617) are fused into the store.
 //
 // Bit parity with convolve_sep_gen (imutil.c:742-861): taps are accumulated in ascending
-// d with separate fp32 multiply and add roundings. Interior samples have frac == 0, so
-// (1-frac)*lo + frac*hi is lo itself. The left boundary of a dyadic unit-spaced line is
-// an exact reflection (c = -c with integral c), which the z stream reproduces by
-// re-feeding planes HW..1; the right boundary's "- 0.1" lerp (imutil.c:846-849) becomes
-// HW+1 "virtual planes" built from the last real planes. x and y boundaries evaluate the
-// literal per-tap formula (from global memory / from the shared x-filtered rows).
+// d with separate fp32 multiply and add roundings. With unit spacing every sample has
+// frac == 0, so (1-frac)*lo + frac*hi is lo itself, and all three boundary rules reduce to
+// a plain FIR over an EXTENDED line: E[-i] = E[i] (mirror, c = -c with integral c) and
+// E[dim_end + m] = lerp(E[dim_end-m-1], E[dim_end-m], fr_m), m = 0..HW, the "- 0.1" right
+// mirror (imutil.c:846-849). Interior outputs never touch index dim_end, so giving index
+// dim_end the virtual value is consistent. The extension is built on the fly: in registers
+// for x (the edge tiles sit at static positions), by remapping / blending source rows in
+// the x pass for y, and by the plane stream for z.
 #pragma once
 
 #include <cuda.h>
@@ -26,7 +38,8 @@
 
 namespace s3d {
 
-constexpr int kFTX = 32;  // tile width (x): 8 float4 column groups
+constexpr int kFTX = 32;  // tile width (x): one warp lane per column in the y/z passes
+constexpr int kNB = 3;    // TMA tile buffers
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
     return (uint32_t) __cvta_generic_to_shared(p);
@@ -40,17 +53,18 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
                  : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra WAIT_DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "WAIT_DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    }
 }
 __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tmap, int x, int y, int z,
                                             uint64_t *bar) {
@@ -62,292 +76,322 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tmap, 
 }
 
 struct FusedParams {
-    const float *src;      // previous level (x/y boundary taps, DoG max)
+    const float *src;      // previous level (DoG max)
     float *dst;            // this level
     float *ds_dst;         // next octave's level -1 (2x decimation of dst) or nullptr
     float *dogmax;         // slot for max|src - dst| or nullptr
     const float *divisor;  // im_scale divisor applied to src on load, or nullptr
-    const float *taps_g;   // taps in global memory (boundary evaluation)
     int nx, ny, nz;
     int zchunk;            // outputs per z-chunk
-    TapsParam taps;        // taps in the parameter bank (interior evaluation)
+    TapsParam taps;        // taps in the parameter bank
 };
 
 template <int HW>
 struct FusedCfg {
-    static constexpr int NW = 2 * HW + 1;           // z window depth
-    static constexpr int HWP = (HW + 3) / 4 * 4;    // x halo rounded up for 16-byte alignment
+    static constexpr int NW = 2 * HW + 1;           // taps
+    static constexpr int HWP = (HW + 3) / 4 * 4;    // x halo rounded up to 4: TMA boxes whose start / width
+                                                    // are not 16-byte multiples fault ("illegal instruction")
     static constexpr int BW = kFTX + 2 * HWP;       // staged tile width
     static constexpr int NIN = 4 + 2 * HWP;         // inputs a 4-wide x item reads
+    static constexpr int NINY = 4 + 2 * HW;         // rows a 4-high y item reads
 };
 
-// One z step with the newest y-filtered value in window slot J (compile-time rotation).
-template <int HW, int J>
-__device__ __forceinline__ float4 zstep(float4 (&W)[2 * HW + 1], const float4 v, const TapsParam &k) {
-    constexpr int NW = 2 * HW + 1;
-    W[J] = v;
-    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-    for (int t = 0; t < NW; t++) {
-        const float4 s = W[(J - t + NW) % NW];  // tap d = t - HW samples plane z + HW - t
-        const float kt = k.k[t];
-        a.x = __fadd_rn(a.x, __fmul_rn(kt, s.x));
-        a.y = __fadd_rn(a.y, __fmul_rn(kt, s.y));
-        a.z = __fadd_rn(a.z, __fmul_rn(kt, s.z));
-        a.w = __fadd_rn(a.w, __fmul_rn(kt, s.w));
-    }
-    return a;
+__device__ __forceinline__ float lerp1(const float a, const float b, const float fr) {
+    return __fadd_rn(__fmul_rn(__fsub_rn(1.0f, fr), a), __fmul_rn(fr, b));
 }
 
-template <int HW, int J>
-struct ZDispatch {
-    static __device__ __forceinline__ float4 run(int phase, float4 (&W)[2 * HW + 1], const float4 v,
-                                                 const TapsParam &k) {
-        if (phase == J) return zstep<HW, J>(W, v, k);
-        return ZDispatch<HW, J - 1>::run(phase, W, v, k);
-    }
-};
+// Fraction of the right-boundary mirror for a tap landing m samples past dim_end:
+// c = dim_end + m -> 2*dim_end - c - 0.1f, frac = c - (int) c (imutil.c:846-853).
+__device__ __forceinline__ float right_frac(int dim_end, int m) {
+    const float c = (float) (dim_end + m);
+    const float cm = __fsub_rn(__fsub_rn(__fmul_rn(2.0f, (float) dim_end), c), 0.1f);
+    return __fsub_rn(cm, (float) (int) cm);
+}
+
+// tap index with the symmetric twin folded onto the lower half, so that the compiler sees
+// k[t] * v and k[2*HW - t] * v as the same product
 template <int HW>
-struct ZDispatch<HW, 0> {
-    static __device__ __forceinline__ float4 run(int, float4 (&W)[2 * HW + 1], const float4 v,
-                                                 const TapsParam &k) {
-        return zstep<HW, 0>(W, v, k);
-    }
-};
-
-__device__ __forceinline__ float4 lerp4(const float4 a, const float4 b, const float fr) {
-    const float om = __fsub_rn(1.0f, fr);
-    float4 r;
-    r.x = __fadd_rn(__fmul_rn(om, a.x), __fmul_rn(fr, b.x));
-    r.y = __fadd_rn(__fmul_rn(om, a.y), __fmul_rn(fr, b.y));
-    r.z = __fadd_rn(__fmul_rn(om, a.z), __fmul_rn(fr, b.z));
-    r.w = __fadd_rn(__fmul_rn(om, a.w), __fmul_rn(fr, b.w));
-    return r;
+__device__ __forceinline__ constexpr int fold(int t) {
+    return t <= HW ? t : 2 * HW - t;
 }
 
-// Literal per-tap evaluation on a line of x-filtered rows held in shared memory
-// (y boundaries). `rows` points at row y = row0; consecutive y are `pitch` floats apart.
-__device__ __forceinline__ float4 ypoint_generic(const float *rows, int pitch, int row0, int y,
-                                                 int ny, const TapsParam &k, int hw) {
-    const int dim_end = ny - 1;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int d = -hw; d <= hw; d++) {
-        const float tap = k.k[d + hw];
-        float c = __fsub_rn((float) y, (float) d);  // unit_factor == 1
-        if ((int) c < 0) {
-            c = -c;
-        } else if ((int) c >= dim_end) {
-            c = __fsub_rn(__fsub_rn(__fmul_rn(2.0f, (float) dim_end), c), 0.1f);
+// x pass of one tile row for one 4-column group: 4 x-filtered outputs.
+//   trow : tile row (column 0 <-> x0 - HWP)        gg : column group 0..7
+//   left / right : this tile sits at x0 == 0 / x0 == nx - 32 (static edge positions), so
+//                  the register indices of the edge fix-ups are static per column group
+//   frx[m] : right-mirror fractions
+template <int HW>
+__device__ __forceinline__ float4 xrow(const float *__restrict__ trow, const int gg, const bool left,
+                                       const bool right, const float *__restrict__ frx,
+                                       const bool scale, const float dv, const TapsParam &k) {
+    using C = FusedCfg<HW>;
+    constexpr int NW = C::NW, HWP = C::HWP, NIN = C::NIN;
+    float in[NIN];
+    const float4 *s4 = reinterpret_cast<const float4 *>(trow + 4 * gg);
+#pragma unroll
+    for (int q = 0; q < NIN / 4; q++) {
+        const float4 t4 = s4[q];
+        in[4 * q] = t4.x; in[4 * q + 1] = t4.y; in[4 * q + 2] = t4.z; in[4 * q + 3] = t4.w;
+    }
+    if (scale) {  // im_scale: v / max (imutil.c:710-712), first blur only
+#pragma unroll
+        for (int j = 0; j < NIN; j++) in[j] = __fdiv_rn(in[j], dv);
+    }
+    if (left) {  // E[-i] = E[i]: input j of group GG sits at x = 4*GG + j - HWP
+#pragma unroll
+        for (int GG = 0; GG < (HWP + 3) / 4; GG++) {
+            if (gg == GG) {
+#pragma unroll
+                for (int j = 0; j < HWP - 4 * GG; j++) in[j] = in[2 * (HWP - 4 * GG) - j];
+            }
         }
-        int lo = (int) c;
-        const float fr = __fsub_rn(c, (float) lo);
-        lo = max(0, min(lo, ny - 2));
-        const float4 a = *reinterpret_cast<const float4 *>(rows + (lo - row0) * pitch);
-        const float4 b = *reinterpret_cast<const float4 *>(rows + (lo + 1 - row0) * pitch);
-        const float4 v = lerp4(a, b, fr);
-        acc.x = __fadd_rn(acc.x, __fmul_rn(tap, v.x));
-        acc.y = __fadd_rn(acc.y, __fmul_rn(tap, v.y));
-        acc.z = __fadd_rn(acc.z, __fmul_rn(tap, v.z));
-        acc.w = __fadd_rn(acc.w, __fmul_rn(tap, v.w));
     }
-    return acc;
+    if (right) {  // E[dim_end + m] = lerp(E[dim_end-m-1], E[dim_end-m]); dim_end <-> input JD
+#pragma unroll
+        for (int GG = (kFTX - 4 - HWP + 3) / 4; GG < 8; GG++) {
+            if (gg == GG) {
+#pragma unroll
+                for (int m = HW; m >= 0; m--) {
+                    if (kFTX - 1 + HWP - 4 * GG + m <= NIN - 1)
+                        in[kFTX - 1 + HWP - 4 * GG + m] =
+                            lerp1(in[kFTX - 1 + HWP - 4 * GG - m - 1], in[kFTX - 1 + HWP - 4 * GG - m], frx[m]);
+                }
+            }
+        }
+    }
+    float o[4];
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        float a = 0.0f;
+#pragma unroll
+        for (int t = 0; t < NW; t++)  // tap d = t - HW samples x - d
+            a = __fadd_rn(a, __fmul_rn(k.k[fold<HW>(t)], in[c + HWP + HW - t]));
+        o[c] = a;
+    }
+    return make_float4(o[0], o[1], o[2], o[3]);
 }
 
-// Fused blur, unit tap spacing on all three axes. Block = 8 x TY threads; thread
-// (g, yy) owns the four columns x0 + 4g .. 4g+3 of row y0 + yy in the y and z passes.
+// z pass, scatter form: feed one y-filtered value; returns the output that is now complete.
+template <int HW>
+__device__ __forceinline__ float zfeed(float (&A)[2 * HW], const float v, const TapsParam &k) {
+    float P[HW + 1];
+#pragma unroll
+    for (int j = 0; j <= HW; j++) P[j] = __fmul_rn(k.k[j], v);
+    const float out = __fadd_rn(A[2 * HW - 1], P[0]);
+#pragma unroll
+    for (int t = 2 * HW - 1; t >= 1; t--) A[t] = __fadd_rn(A[t - 1], P[fold<HW>(t)]);
+    A[0] = __fadd_rn(0.0f, P[0]);
+    return out;
+}
+
+// Fused blur, unit tap spacing on all three axes. Block = 32 x TY/4 threads: thread
+// (lane, w) owns column x0 + lane, rows y0 + 4w .. 4w+3 in the y and z passes.
 template <int HW, int TY>
-__global__ void __launch_bounds__(8 * TY, 1)
+__global__ void __launch_bounds__(8 * TY, TY == 64 ? 1 : 2)
 blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedParams P) {
     using C = FusedCfg<HW>;
     constexpr int NT = 8 * TY;
-    constexpr int NW = C::NW, HWP = C::HWP, BW = C::BW, NIN = C::NIN;
+    constexpr int HWP = C::HWP, BW = C::BW, NINY = C::NINY;
     constexpr int TROWS = TY + 2 * HW;            // staged rows (y halo)
     constexpr int TILE_FLOATS = TROWS * BW;
     constexpr uint32_t TILE_BYTES = TILE_FLOATS * 4;
-    constexpr int TILE_STRIDE = (TILE_FLOATS + 31) / 32 * 32;  // keeps both TMA destinations 128-byte aligned
+    constexpr int TILE_STRIDE = (TILE_FLOATS + 31) / 32 * 32;  // 128-byte aligned TMA destinations
+    constexpr int XF_FLOATS = TROWS * kFTX;
+    constexpr int NITEMS = TROWS * 8;
+    constexpr int ROT = (TROWS - NT / 8 % TROWS) % TROWS;  // see the x-pass loop
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    float *tile = reinterpret_cast<float *>(smem_raw);                 // [2][TROWS][BW]
-    float *xf = tile + 2 * TILE_STRIDE;                                // [2][TROWS][kFTX]
-    uint64_t *mbar = reinterpret_cast<uint64_t *>(xf + 2 * TROWS * kFTX);  // [2]
+    float *tile = reinterpret_cast<float *>(smem_raw);                 // [kNB][TROWS][BW]
+    float *xf = tile + kNB * TILE_STRIDE;                              // [2][TROWS][32]
+    uint64_t *mbar = reinterpret_cast<uint64_t *>(xf + 2 * XF_FLOATS); // [kNB]
+    float *frx = reinterpret_cast<float *>(mbar + kNB);                // [HW + 1]
+    float *fry = frx + (HW + 1);                                       // [HW + 1]
     __shared__ float wmax_sh[NT / 32];
 
     const int tid = threadIdx.x;
-    const int g = tid & 7, yy = tid >> 3;
+    const int lane = tid & 31, w = tid >> 5;
     const int nx = P.nx, ny = P.ny, nz = P.nz;
-    // tiles are shifted inwards at the high edges so every tile is full (overlapping
-    // tiles write identical values)
+    // tiles are shifted inwards at the high edges so every tile is full
     const int x0 = min((int) blockIdx.x * kFTX, nx - kFTX);
     const int y0 = min((int) blockIdx.y * TY, ny - TY);
+    const bool xleft = x0 == 0, xright = x0 == nx - kFTX;
+    const bool ybot = y0 == 0, ytop = y0 == ny - TY;
+    const int dex = nx - 1, dey = ny - 1, dez = nz - 1;
     const int zb = blockIdx.z * P.zchunk;
     const int ze = min(zb + P.zchunk, nz);
-    const bool last = ze == nz;
-    const int dim_end = nz - 1;
-    // stream of plane indices i = zb-HW .. i_last; negative i reflect (plane -i)
-    const int i0 = zb - HW;
-    const int i_last = last ? dim_end - 1 : ze - 1 + HW;
-    const int nmain = i_last - i0 + 1;
-    const int nloads = nmain + (last ? 1 : 0);  // the last chunk also stages plane nz-1
+    const bool top = ze == nz;
+
+    // Stream of fed positions q (z_out = q + HW). Top chunk: a prologue walks planes
+    // dez-HW-1 .. dez upwards to build the virtual planes dez+HW .. dez (fed in that order),
+    // then the main stream feeds real planes dez-1 downwards. Other chunks: planes
+    // ze-1+HW downwards. Negative positions reflect (plane -q).
+    const int npro = top ? HW + 2 : 0;
+    const int qstart = top ? dez - 1 : ze - 1 + HW;
+    const int N = npro + (qstart - (zb - HW) + 1);
+    auto plane_of = [&](int n) -> int {
+        if (n < npro) return dez - HW - 1 + n;
+        const int q = qstart - (n - npro);
+        return q < 0 ? -q : q;
+    };
 
     float dv = 0.0f;
     if (P.divisor != nullptr) dv = *P.divisor;
     const bool scale = dv != 0.0f;
 
     if (tid == 0) {
-        mbar_init(&mbar[0], 1);
-        mbar_init(&mbar[1], 1);
+#pragma unroll
+        for (int b = 0; b < kNB; b++) mbar_init(&mbar[b], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    if (tid <= HW) {
+        frx[tid] = right_frac(dex, tid);
+        fry[tid] = right_frac(dey, tid);
+    }
     __syncthreads();
-    auto issue = [&](int n) {  // stage stream element n into buffer n & 1 (one thread)
-        const int i = i0 + n;
-        const int plane = n < nmain ? (i < 0 ? -i : i) : dim_end;
-        mbar_expect_tx(&mbar[n & 1], TILE_BYTES);
-        tma_load_3d(tile + (n & 1) * TILE_STRIDE, &tmap, x0 - HWP, y0 - HW, plane, &mbar[n & 1]);
+    auto issue = [&](int n) {  // stage stream element n into buffer n % kNB (one thread)
+        const int b = n % kNB;
+        mbar_expect_tx(&mbar[b], TILE_BYTES);
+        tma_load_3d(tile + b * TILE_STRIDE, &tmap, x0 - HWP, y0 - HW, plane_of(n), &mbar[b]);
     };
     if (tid == 0) {
-        issue(0);
-        if (nloads > 1) issue(1);
+        for (int n = 0; n < kNB && n < N; n++) issue(n);
     }
 
-    float4 W[NW];
+    float A[4][2 * HW];
 #pragma unroll
-    for (int j = 0; j < NW; j++) W[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-    int phase = last ? (NW - nmain % NW) % NW : 0;  // so that plane nz-2 lands in slot NW-1
+    for (int c = 0; c < 4; c++)
+#pragma unroll
+        for (int t = 0; t < 2 * HW; t++) A[c][t] = 0.0f;
+    float prev[4] = {0.f, 0.f, 0.f, 0.f};
     float vmax = 0.0f;
-    const int y = y0 + yy;
-    const bool y_interior = y >= HW && y <= ny - 2 - HW;
+
+    // which outputs this CTA stores: edge outputs belong to the tiles at the static edge
+    // positions (first / last), see xrow()
+    const int x = x0 + lane;
+    const bool xok = (xleft || x >= HW) && (xright || x + HW < dex);
+    const int ybase = y0 + 4 * w;
     const size_t plane_stride = (size_t) nx * ny;
 
-    // Stores one output row segment (+ fused DoG max and 2x decimation).
-    auto emit = [&](int z, const float4 o) {
-        const size_t idx = (size_t) z * plane_stride + (size_t) y * nx + (size_t) (x0 + 4 * g);
-        *reinterpret_cast<float4 *>(P.dst + idx) = o;
-        if (P.dogmax != nullptr) {
-            const float4 p = *reinterpret_cast<const float4 *>(P.src + idx);
-            vmax = fmaxf(vmax, fmaxf(fmaxf(fabsf(__fsub_rn(p.x, o.x)), fabsf(__fsub_rn(p.y, o.y))),
-                                     fmaxf(fabsf(__fsub_rn(p.z, o.z)), fabsf(__fsub_rn(p.w, o.w)))));
-        }
-        if (P.ds_dst != nullptr && !((z | y) & 1)) {
-            const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
-            const int hz = z >> 1, hy = y >> 1, hx = (x0 + 4 * g) >> 1;
-            if (hz < dnz && hy < dny) {
-                float *q = P.ds_dst + ((size_t) hz * dny + hy) * dnx + hx;
-                if (hx < dnx) q[0] = o.x;
-                if (hx + 1 < dnx) q[1] = o.z;
+    for (int n = -1; n < N; n++) {
+        // ---- x pass of stream element n + 1 into xf[(n + 1) & 1]
+        if (n + 1 < N) {
+            const int e = n + 1;
+            const int b = e % kNB;
+            const float *tb = tile + b * TILE_STRIDE;
+            float *xb = xf + (e & 1) * XF_FLOATS;
+            mbar_wait(&mbar[b], (uint32_t) ((e / kNB) & 1));
+            // Items are rotated so that the top tile's virtual rows (two source rows each)
+            // fall to threads that process a single item.
+            for (int it = tid; it < NITEMS; it += NT) {
+                int r = (it >> 3) + ROT;
+                if (r >= TROWS) r -= TROWS;
+                const int gg = it & 7;
+                const int gy = y0 - HW + r;
+                int ra = r, rb = -1;  // source tile rows: result = ra, or lerp(rb, ra, fr)
+                float fr = 0.0f;
+                if (gy < 0) {
+                    ra = r - 2 * gy;  // mirror: row -gy
+                } else if (gy >= dey) {
+                    // virtual row dey + m = lerp(row dey-m-1, row dey-m); only stored
+                    // outputs of the top tile use it
+                    const int m = gy - dey;
+                    if (ytop) {
+                        ra = r - 2 * m;
+                        rb = r - 2 * m - 1;
+                        fr = fry[m];
+                    } else {
+                        ra = -1;
+                    }
+                }
+                float4 o = make_float4(0.f, 0.f, 0.f, 0.f), a = o;
+                if (ra >= 0) {
+#pragma unroll 1
+                    for (int rep = rb >= 0 ? 1 : 0; rep >= 0; rep--) {
+                        const float4 v = xrow<HW>(tb + (rep ? rb : ra) * BW, gg, xleft, xright, frx,
+                                                  scale, dv, P.taps);
+                        if (rep) a = v; else o = v;
+                    }
+                    if (rb >= 0)
+                        o = make_float4(lerp1(a.x, o.x, fr), lerp1(a.y, o.y, fr), lerp1(a.z, o.z, fr),
+                                        lerp1(a.w, o.w, fr));
+                }
+                *reinterpret_cast<float4 *>(xb + r * kFTX + 4 * gg) = o;
             }
         }
-    };
-
-    // x pass + y pass of stream element n; returns this thread's y-filtered float4.
-    auto xy_pass = [&](int n, int plane) -> float4 {
-        float *tb = tile + (n & 1) * TILE_STRIDE;
-        float *xb = xf + (n & 1) * (TROWS * kFTX);
-        mbar_wait(&mbar[n & 1], (uint32_t) ((n >> 1) & 1));
-        if (scale) {  // im_scale: v / max on load (imutil.c:710-712), first blur only
-            for (int e = tid; e < TILE_FLOATS; e += NT) tb[e] = __fdiv_rn(tb[e], dv);
-            __syncthreads();
+        if (n >= 0) {
+        // ---- y pass: rows 4w .. 4w+3+2*HW of the x-filtered tile, column `lane`
+        const float *xb = xf + (n & 1) * XF_FLOATS + (4 * w) * kFTX + lane;
+        float in[NINY];
+#pragma unroll
+        for (int j = 0; j < NINY; j++) in[j] = xb[j * kFTX];
+        float yv[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            float a = 0.0f;
+#pragma unroll
+            for (int t = 0; t < 2 * HW + 1; t++)  // tap d = t - HW samples row y - d
+                a = __fadd_rn(a, __fmul_rn(P.taps.k[fold<HW>(t)], in[c + 2 * HW - t]));
+            yv[c] = a;
         }
-        // ---- x pass: items = (row, 4-column group)
-        for (int it = tid; it < TROWS * 8; it += NT) {
-            const int r = it >> 3, gg = it & 7;
-            const int gy = y0 - HW + r;
-            if (gy < 0 || gy >= ny) continue;
-            const int gx = x0 + 4 * gg;
-            float o[4];
-            if (gx >= HW && gx + 3 <= nx - 2 - HW) {
-                float in[NIN];
-                const float4 *src4 = reinterpret_cast<const float4 *>(tb + r * BW + 4 * gg);
-#pragma unroll
-                for (int q = 0; q < NIN / 4; q++) {
-                    const float4 t4 = src4[q];
-                    in[4 * q] = t4.x; in[4 * q + 1] = t4.y; in[4 * q + 2] = t4.z; in[4 * q + 3] = t4.w;
-                }
-#pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    float a = 0.0f;
-#pragma unroll
-                    for (int t = 0; t < NW; t++)  // d = t - HW samples x - d
-                        a = __fadd_rn(a, __fmul_rn(P.taps.k[t], in[c + HWP + HW - t]));
-                    o[c] = a;
-                }
+
+        // ---- z pass
+        int q;
+        bool feed = true;
+        if (n < npro) {
+            const int m = HW + 1 - n;  // plane dez - m
+            q = dez + m;
+            if (n == 0) {
+                feed = false;
             } else {
-                const float *line = P.src + (size_t) plane * plane_stride + (size_t) gy * nx;
+                const float fr = right_frac(dez, m);
 #pragma unroll
                 for (int c = 0; c < 4; c++) {
-                    const int x = gx + c;
-                    if (x >= HW && x <= nx - 2 - HW) {
-                        float a = 0.0f;
-                        for (int t = 0; t < NW; t++) {
-                            float s = line[x + HW - t];
-                            if (scale) s = __fdiv_rn(s, dv);
-                            a = __fadd_rn(a, __fmul_rn(P.taps.k[t], s));
-                        }
-                        o[c] = a;
-                    } else {
-                        o[c] = conv_point_generic(line, 1, x, nx, P.taps_g, HW, 1.0f, HW, scale, dv);
+                    const float cur = yv[c];
+                    yv[c] = lerp1(prev[c], cur, fr);
+                    prev[c] = cur;
+                }
+            }
+            if (n == 0) {
+#pragma unroll
+                for (int c = 0; c < 4; c++) prev[c] = yv[c];
+            }
+        } else {
+            q = qstart - (n - npro);
+        }
+        if (feed) {
+            float o[4];
+#pragma unroll
+            for (int c = 0; c < 4; c++) o[c] = zfeed<HW>(A[c], yv[c], P.taps);
+            const int z = q + HW;
+            if (z >= zb && z < ze && xok) {
+#pragma unroll
+                for (int c = 0; c < 4; c++) {
+                    const int y = ybase + c;
+                    const bool yok = (ybot || y >= HW) && (ytop || y + HW < dey);
+                    if (!yok) continue;
+                    const size_t idx = (size_t) z * plane_stride + (size_t) y * nx + (size_t) x;
+                    P.dst[idx] = o[c];
+                    if (P.dogmax != nullptr)
+                        vmax = fmaxf(vmax, fabsf(__fsub_rn(P.src[idx], o[c])));
+                    if (P.ds_dst != nullptr && !((z | y | x) & 1)) {
+                        const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
+                        const int hz = z >> 1, hy = y >> 1, hx = x >> 1;
+                        if (hz < dnz && hy < dny && hx < dnx)
+                            P.ds_dst[((size_t) hz * dny + hy) * dnx + hx] = o[c];
                     }
                 }
             }
-            *reinterpret_cast<float4 *>(xb + r * kFTX + 4 * gg) = make_float4(o[0], o[1], o[2], o[3]);
         }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }  // n >= 0
         __syncthreads();
-        // the staged tile is consumed: refill this buffer with stream element n + 2
-        if (tid == 0 && n + 2 < nloads) issue(n + 2);
-        // ---- y pass: thread (g, yy), rows yy .. yy + 2*HW of the x-filtered tile
-        float4 v;
-        if (y_interior) {
-            v = make_float4(0.f, 0.f, 0.f, 0.f);
-            const float *col = xb + yy * kFTX + 4 * g;
-#pragma unroll
-            for (int t = 0; t < NW; t++) {  // d = t - HW samples row y - d = yy + 2*HW - t
-                const float4 s = *reinterpret_cast<const float4 *>(col + (2 * HW - t) * kFTX);
-                const float kt = P.taps.k[t];
-                v.x = __fadd_rn(v.x, __fmul_rn(kt, s.x));
-                v.y = __fadd_rn(v.y, __fmul_rn(kt, s.y));
-                v.z = __fadd_rn(v.z, __fmul_rn(kt, s.z));
-                v.w = __fadd_rn(v.w, __fmul_rn(kt, s.w));
-            }
-        } else {
-            v = ypoint_generic(xb + 4 * g, kFTX, y0 - HW, y, ny, P.taps, HW);
-        }
-        return v;
-    };
-
-    // ---- main stream
-    for (int n = 0; n < nmain; n++) {
-        const int i = i0 + n;
-        const float4 v = xy_pass(n, i < 0 ? -i : i);
-        const float4 o = ZDispatch<HW, NW - 1>::run(phase, W, v, P.taps);
-        phase = phase + 1 == NW ? 0 : phase + 1;
-        const int z = i - HW;
-        if (z >= zb && z < ze) emit(z, o);
-    }
-
-    // ---- right boundary (last chunk): plane nz-1 and HW "virtual planes"
-    if (last) {
-        const float4 vreal = xy_pass(nmain, dim_end);
-#pragma unroll
-        for (int m = 0; m <= HW; m++) {
-            // tap position c = dim_end + m mirrors to 2*dim_end - c - 0.1 (imutil.c:846-849)
-            const float c = (float) (dim_end + m);
-            const float cm = __fsub_rn(__fsub_rn(__fmul_rn(2.0f, (float) dim_end), c), 0.1f);
-            const float fr = __fsub_rn(cm, (float) (int) cm);  // (int) cm == dim_end - m - 1
-            // plane dim_end-1-q sits in slot NW-1-q; slots 0..m-1 already hold virtual planes
-            const float4 a = W[NW - 1 - m];
-            const float4 b = m == 0 ? vreal : W[NW - m];
-            const float4 vm = lerp4(a, b, fr);
-            // slot m receives virtual plane m; the window rotation is static here
-            const float4 o = ZDispatch<HW, NW - 1>::run(m, W, vm, P.taps);
-            emit(dim_end + m - HW, o);
-        }
+        // tile buffer (n+1) % kNB was consumed by xpass(n+1): refill it
+        if (tid == 0 && n + 1 + kNB < N) issue(n + 1 + kNB);
     }
 
     // ---- DoG max-abs: block reduce, one atomic per CTA (non-negative floats order as ints)
     if (P.dogmax != nullptr) {
         for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
-        if ((tid & 31) == 0) wmax_sh[tid >> 5] = vmax;
+        if (lane == 0) wmax_sh[w] = vmax;
         __syncthreads();
         if (tid < 32) {
             float m2 = tid < NT / 32 ? wmax_sh[tid] : 0.0f;
