@@ -90,9 +90,13 @@ struct DescJob {
     float cx, cy, cz;
     float sigma;         // (float)(sd * desc_sig_fctr)  (sift.c:1453)
     float R[9];
+    int out_index;       // descriptor slot (jobs are launched largest window first)
+    int max_rows;        // upper bound of (y, z) rows of the window (host estimate)
 };
 int upload_mesh(void);
-int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, float *d_desc,
+// jobs may be reordered by the caller; max_rows = max over jobs of DescJob::max_rows
+int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_rows, float *d_desc,
                        uint64_t *launches);
+int desc_job_rows(const DescJob &J);  // host: upper bound of window rows of one job
 
 }  // namespace s3d

@@ -32,6 +32,9 @@ struct MeshConst {
     float e2q[kFaces];     // e2 . q
     float ctr[kFaces][3];  // v0 + v1 + v2 (direction of the face centre; selection only)
     int idx[kFaces][3];    // histogram bin of each barycentric weight
+    // face whose centre is nearest to a direction, by octant (bit 0: x < 0, bit 1: y < 0,
+    // bit 2: z < 0) and by which of the 4 candidate centres of that octant wins
+    unsigned char lut[8][4];
 };
 
 __constant__ MeshConst c_mesh;
@@ -86,6 +89,29 @@ int upload_mesh(void) {
         cross3(m.t[i], m.e1[i], m.q[i]);
         m.e2q[i] = dot3(m.e2[i], m.q[i]);
     }
+    // Nearest-centre lookup. By symmetry a direction in the octant with signs (sx, sy, sz)
+    // is nearest to one of 4 face centres: the octant's own face (1,1,1) and the three
+    // faces straddling the octant's coordinate planes, (phi,0,2phi+1), (0,2phi+1,phi),
+    // (2phi+1,phi,0) (all four of equal length). The table maps them onto the mesh's face
+    // numbering by matching the actual centre vectors, so it cannot disagree with `ctr`.
+    {
+        const float ph = (float) gr;
+        const float cand[4][3] = {{1 + ph, 1 + ph, 1 + ph}, {ph, 0, 2 * ph + 1}, {0, 2 * ph + 1, ph},
+                                  {2 * ph + 1, ph, 0}};
+        for (int oct = 0; oct < 8; oct++)
+            for (int c = 0; c < 4; c++) {
+                const float v[3] = {cand[c][0] * ((oct & 1) ? -1.f : 1.f),
+                                    cand[c][1] * ((oct & 2) ? -1.f : 1.f),
+                                    cand[c][2] * ((oct & 4) ? -1.f : 1.f)};
+                int best = 0;
+                float bd = -1e30f;
+                for (int f = 0; f < kFaces; f++) {
+                    const float d = dot3(v, m.ctr[f]);
+                    if (d > bd) { bd = d; best = f; }
+                }
+                m.lut[oct][c] = (unsigned char) best;
+            }
+    }
     S3D_CK(cudaMemcpyToSymbol(c_mesh, &m, sizeof(m)));
     return 0;
 }
@@ -135,7 +161,7 @@ __device__ __forceinline__ void fix_add(unsigned *lo, unsigned *hi, int i, float
 }
 
 __global__ void __launch_bounds__(kDescThreads)
-descriptor_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ desc_out) {
+descriptor_rows_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ desc_out) {
     __shared__ unsigned hlo[kDescNumel];
     __shared__ unsigned hhi[kDescNumel];
     __shared__ float hist[kDescNumel];
@@ -329,14 +355,396 @@ descriptor_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ d
         }
         __syncthreads();
     }
-    float *o = desc_out + (size_t) ki * kDescNumel;
+    float *o = desc_out + (size_t) J.out_index * kDescNumel;
     for (int i = threadIdx.x; i < kDescNumel; i += kDescThreads) o[i] = hist[i];
 }
 
-int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, float *d_desc,
+// ---------------------------------------------------------------------------------------
+// v3: flattened in-window work list.
+//
+// The window of a keypoint is the sphere of radius 2*sigma intersected with the rotated
+// cube of half-width rad/sqrt(2) (only voxels whose rotated coordinates fall into the
+// 4x4x4 cell grid contribute, sift.c:1488-1492) -- about a third of the bounding box the
+// reference loops over. Walking the bounding box (or one row per thread) leaves two thirds
+// of the lanes idle, so:
+//   phase 1  every (y, z) row of the bounding box gets a conservative x interval
+//            [xa, xa+len) covering sphere /\ cube (closed form: three slabs and a chord);
+//   phase 2  block-wide exclusive scan of len -> the flattened voxel list of T entries;
+//   phase 3  thread t walks entries [t*C, (t+1)*C), C = ceil(T/256): consecutive voxels of
+//            consecutive rows, so every lane runs the same trip count, and neighbouring
+//            voxels keep the (cell, face) key so the 8x3 contributions are summed in
+//            registers and flushed to shared memory only when the key changes.
+// The exact per-voxel tests of the reference are kept (the intervals are supersets), so
+// the set of contributing voxels is the reference's.
+//
+// Face lookup: nearest face centre out of the 4 candidates of the direction's octant
+// (icosahedral symmetry), confirmed by the reference's own Moller-Trumbore test with a
+// margin; anything near an edge falls back to the literal first-hit scan of
+// icos_hist_bin so that ties resolve exactly as in the reference.
+// ---------------------------------------------------------------------------------------
+
+// cart2bary on a face held in shared memory: fm = {e1[3], e2[3], t[3], q[3], e2q}
+__device__ __forceinline__ bool face_hit_s(const float *__restrict__ fm, float gx, float gy,
+                                           float gz, float &bx, float &by, float &bz) {
+    const float4 m0 = *reinterpret_cast<const float4 *>(fm);       // e1.x e1.y e1.z e2.x
+    const float4 m1 = *reinterpret_cast<const float4 *>(fm + 4);   // e2.y e2.z t.x  t.y
+    const float4 m2 = *reinterpret_cast<const float4 *>(fm + 8);   // t.z  q.x  q.y  q.z
+    const float e2q = fm[12];
+    const float e2x = m0.w, e2y = m1.x, e2z = m1.y;
+    const float px = __fsub_rn(__fmul_rn(gy, e2z), __fmul_rn(gz, e2y));
+    const float py = __fsub_rn(__fmul_rn(gz, e2x), __fmul_rn(gx, e2z));
+    const float pz = __fsub_rn(__fmul_rn(gx, e2y), __fmul_rn(gy, e2x));
+    const float det = __fadd_rn(__fadd_rn(__fmul_rn(m0.x, px), __fmul_rn(m0.y, py)), __fmul_rn(m0.z, pz));
+    if ((double) fabsf(det) < kBaryEps) return false;
+    const float det_inv = __fdiv_rn(1.0f, det);
+    const float tp = __fadd_rn(__fadd_rn(__fmul_rn(m1.z, px), __fmul_rn(m1.w, py)), __fmul_rn(m2.x, pz));
+    const float cq = __fadd_rn(__fadd_rn(__fmul_rn(gx, m2.y), __fmul_rn(gy, m2.z)), __fmul_rn(gz, m2.w));
+    by = __fmul_rn(det_inv, tp);
+    bz = __fmul_rn(det_inv, cq);
+    bx = __fsub_rn(__fsub_rn(1.0f, by), bz);
+    const float k = __fmul_rn(e2q, det_inv);
+    if ((double) bx < -kBaryEps || (double) by < -kBaryEps || (double) bz < -kBaryEps || k < 0.0f)
+        return false;
+    return true;
+}
+
+__global__ void __launch_bounds__(kDescThreads)
+descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ desc_out,
+                       int max_rows) {
+    extern __shared__ __align__(16) int dyn_smem[];
+    int *row_off = dyn_smem;                                            // [max_rows + 1]
+    short *row_xa = reinterpret_cast<short *>(dyn_smem + max_rows + 1);  // [max_rows]
+    __shared__ unsigned hlo[kDescNumel];
+    __shared__ unsigned hhi[kDescNumel];
+    __shared__ float hist[kDescNumel];
+    __shared__ __align__(16) float smesh[kFaces * 16];
+    __shared__ int sidx[kFaces * 3];
+    __shared__ unsigned char slut[32];
+    __shared__ int part[kDescThreads / 32];
+    __shared__ double red[kDescThreads / 32];
+    __shared__ double norm_sh;
+    const int ki = blockIdx.x;
+    if (ki >= n) return;
+    const DescJob J = jobs[ki];
+    const int tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < kDescNumel; i += kDescThreads) {
+        hlo[i] = 0u;
+        hhi[i] = 0u;
+    }
+    if (tid < kFaces) {
+        float *fm = smesh + tid * 16;
+        for (int k = 0; k < 3; k++) {
+            fm[k] = c_mesh.e1[tid][k];
+            fm[3 + k] = c_mesh.e2[tid][k];
+            fm[6 + k] = c_mesh.t[tid][k];
+            fm[9 + k] = c_mesh.q[tid][k];
+            sidx[tid * 3 + k] = c_mesh.idx[tid][k];
+        }
+        fm[12] = c_mesh.e2q[tid];
+        fm[13] = fm[14] = fm[15] = 0.0f;
+    }
+    if (tid < 32) slut[tid] = c_mesh.lut[tid >> 2][tid & 3];
+
+    const float *__restrict__ img = J.img;
+    const int nx = J.nx, ny = J.ny, nz = J.nz;
+    const float uxf = J.ux, uyf = J.uy, uzf = J.uz;
+    const float cx = J.cx, cy = J.cy, cz = J.cz;
+    // sift.c:1453-1458
+    const float sigma = J.sigma;
+    const float rad = (float) (kDescRadFctr * (double) sigma);
+    const float half_w = (float) ((double) rad / sqrt(2.0));
+    const float desc_w = __fmul_rn(2.0f, half_w);
+    const float hist_w = __fdiv_rn(desc_w, (float) kHistPerDim);
+    const float bin_fctr = __fdiv_rn(1.0f, hist_w);
+    const float rad2 = __fmul_rn(rad, rad);
+    const float sig2 = __fmul_rn(sigma, sigma);
+    const float ixu = __fdiv_rn(1.0f, uxf), iyu = __fdiv_rn(1.0f, uyf), izu = __fdiv_rn(1.0f, uzf);
+
+    // Window (sift.c:91-99), all-float here because win_radius is a float.
+    const int x0 = (int) fmaxf(floorf(__fsub_rn(cx, __fdiv_rn(rad, uxf))), 1.0f);
+    const int x1 = (int) fminf(ceilf(__fadd_rn(cx, __fdiv_rn(rad, uxf))), (float) (nx - 2));
+    const int y0 = (int) fmaxf(floorf(__fsub_rn(cy, __fdiv_rn(rad, uyf))), 1.0f);
+    const int y1 = (int) fminf(ceilf(__fadd_rn(cy, __fdiv_rn(rad, uyf))), (float) (ny - 2));
+    const int z0 = (int) fmaxf(floorf(__fsub_rn(cz, __fdiv_rn(rad, uzf))), 1.0f);
+    const int z1 = (int) fminf(ceilf(__fadd_rn(cz, __fdiv_rn(rad, uzf))), (float) (nz - 2));
+    const int wy = max(y1 - y0 + 1, 0), wz = max(z1 - z0 + 1, 0);
+    int nrows = (x1 >= x0) ? wy * wz : 0;
+    if (nrows > max_rows) nrows = max_rows;  // cannot happen: desc_job_rows() is an upper bound
+    const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
+
+    // Rt = R^T (sift.c:1462-1464): Rt[i][j] = R[j][i]
+    const float r00 = J.R[0], r01 = J.R[1], r02 = J.R[2];
+    const float r10 = J.R[3], r11 = J.R[4], r12 = J.R[5];
+    const float r20 = J.R[6], r21 = J.R[7], r22 = J.R[8];
+
+    // ---- phase 1: conservative x interval of every row
+    const int rpt = (nrows + kDescThreads - 1) / kDescThreads;
+    const int rbeg = min(tid * rpt, nrows), rend = min(rbeg + rpt, nrows);
+    const float hwm = half_w * 1.001f + 1e-6f;
+    int mysum = 0;
+    for (int r = rbeg; r < rend; r++) {
+        const int y = y0 + r % wy, z = z0 + r / wy;
+        const float dy = ((float) y - cy) * uyf, dz = ((float) z - cz) * uzf;
+        int len = 0, xa = x0;
+        const float rem = rad2 * 1.0001f - dy * dy - dz * dz;
+        if (rem >= 0.0f) {
+            const float half = sqrtf(rem) * ixu + 0.01f;
+            float lo = cx - half, hi = cx + half;
+            bool empty = false;
+            const float av[3] = {r00 * uxf, r01 * uxf, r02 * uxf};
+            const float bv[3] = {r10 * dy + r20 * dz, r11 * dy + r21 * dz, r12 * dy + r22 * dz};
+#pragma unroll
+            for (int i = 0; i < 3; i++) {
+                if (fabsf(av[i]) > 1e-6f) {
+                    const float inv = 1.0f / av[i];
+                    const float t1 = (-hwm - bv[i]) * inv, t2 = (hwm - bv[i]) * inv;
+                    lo = fmaxf(lo, cx + fminf(t1, t2) - 0.01f);
+                    hi = fminf(hi, cx + fmaxf(t1, t2) + 0.01f);
+                } else if (fabsf(bv[i]) > hwm) {
+                    empty = true;
+                }
+            }
+            if (!empty) {
+                xa = max(x0, (int) ceilf(lo));
+                const int xb = min(x1, (int) floorf(hi));
+                len = max(0, xb - xa + 1);
+            }
+        }
+        row_off[r] = len;
+        row_xa[r] = (short) xa;
+        mysum += len;
+    }
+    // ---- phase 2: exclusive scan over threads, then over each thread's rows
+    int incl = mysum;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) part[warp] = incl;
+    __syncthreads();
+    int base = incl - mysum;
+    int total = 0;
+    for (int wv = 0; wv < kDescThreads / 32; wv++) {
+        const int p = part[wv];
+        if (wv < warp) base += p;
+        total += p;
+    }
+    for (int r = rbeg; r < rend; r++) {
+        const int len = row_off[r];
+        row_off[r] = base;
+        base += len;
+    }
+    if (tid == 0) row_off[nrows] = total;
+    __syncthreads();
+    // ---- phase 3: walk my slice of the flattened list
+    const int chunk = (total + kDescThreads - 1) / kDescThreads;
+    const int t0 = min(tid * chunk, total), t1 = min(t0 + chunk, total);
+
+    float acc[8][3];
+    int cur_key = -1;
+    int ci0 = 0, ci1 = 0, ci2 = 0, cbx = 0, cby = 0, cbz = 0;
+
+#define S3D_FLUSH()                                                                        \
+    if (cur_key >= 0) {                                                                    \
+        _Pragma("unroll") for (int c = 0; c < 8; c++) {                                    \
+            const int hx = cbx + (c >> 2), hy = cby + ((c >> 1) & 1), hz = cbz + (c & 1);  \
+            if (hx < kHistPerDim && hy < kHistPerDim && hz < kHistPerDim) {                \
+                const int hb = (hx + hy * kHistPerDim + hz * kHistPerDim * kHistPerDim) * kVerts; \
+                if (acc[c][0] != 0.0f) fix_add(hlo, hhi, hb + ci0, acc[c][0]);             \
+                if (acc[c][1] != 0.0f) fix_add(hlo, hhi, hb + ci1, acc[c][1]);             \
+                if (acc[c][2] != 0.0f) fix_add(hlo, hhi, hb + ci2, acc[c][2]);             \
+            }                                                                              \
+        }                                                                                  \
+    }
+
+    if (t0 < t1) {
+        // row containing entry t0: the last r with row_off[r] <= t0 (its length is > 0)
+        int lo = 0, hi = nrows;  // invariant: row_off[lo] <= t0 < row_off[hi]
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (row_off[mid] <= t0) lo = mid; else hi = mid;
+        }
+        int r = lo;
+        int x = (int) row_xa[r] + (t0 - row_off[r]);
+        int xend = (int) row_xa[r] + (row_off[r + 1] - row_off[r]) - 1;
+        // per-row invariants
+        float dy, dz, dy2, dz2, bkx, bky, bkz, ckx, cky, ckz;
+        const float *__restrict__ row;
+#define S3D_ROW_SETUP()                                                                    \
+        {                                                                                  \
+            const int y = y0 + r % wy, z = z0 + r / wy;                                    \
+            dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);                                 \
+            dz = __fmul_rn(__fsub_rn((float) z, cz), uzf);                                 \
+            dy2 = __fmul_rn(dy, dy);                                                       \
+            dz2 = __fmul_rn(dz, dz);                                                       \
+            bkx = __fmul_rn(r10, dy); ckx = __fmul_rn(r20, dz);                            \
+            bky = __fmul_rn(r11, dy); cky = __fmul_rn(r21, dz);                            \
+            bkz = __fmul_rn(r12, dy); ckz = __fmul_rn(r22, dz);                            \
+            row = img + (size_t) z * zs + (size_t) y * ys;                                 \
+        }
+        S3D_ROW_SETUP();
+        for (int t = t0; t < t1; t++) {
+            do {  // one voxel; `break` = the reference's `continue`
+                const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
+                const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), dy2), dz2);
+                if (sq > rad2) break;
+                // vkp = Rt * vim (SIFT3D_MUL_MAT_RM_CVEC, immacros.h:326-342)
+                const float kx = __fadd_rn(__fadd_rn(__fmul_rn(r00, dx), bkx), ckx);
+                const float ky = __fadd_rn(__fadd_rn(__fmul_rn(r01, dx), bky), cky);
+                const float kz = __fadd_rn(__fadd_rn(__fmul_rn(r02, dx), bkz), ckz);
+                const float vbx = __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
+                const float vby = __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
+                const float vbz = __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
+                if (vbx < 0.0f || vby < 0.0f || vbz < 0.0f || vbx >= (float) kHistPerDim ||
+                    vby >= (float) kHistPerDim || vbz >= (float) kHistPerDim)
+                    break;
+
+                float gx = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + 1], row[x - 1])), ixu);
+                float gy = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys])), iyu);
+                float gz = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + zs], row[(ptrdiff_t) x - (ptrdiff_t) zs])), izu);
+                const float w = expf(__fdiv_rn(__fmul_rn(-0.5f, sq), sig2));  // sift.c:1498
+                gx = __fmul_rn(gx, w);
+                gy = __fmul_rn(gy, w);
+                gz = __fmul_rn(gz, w);
+                const float rx = __fadd_rn(__fadd_rn(__fmul_rn(r00, gx), __fmul_rn(r10, gy)), __fmul_rn(r20, gz));
+                const float ry = __fadd_rn(__fadd_rn(__fmul_rn(r01, gx), __fmul_rn(r11, gy)), __fmul_rn(r21, gz));
+                const float rz = __fadd_rn(__fadd_rn(__fmul_rn(r02, gx), __fmul_rn(r12, gy)), __fmul_rn(r22, gz));
+
+                // icos_hist_bin (sift.c:1254-1291)
+                const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz));
+                if ((double) n2 < kBaryEps) break;
+                // nearest face centre among the 4 candidates of this octant (selection only)
+                const float ax = fabsf(rx), ay = fabsf(ry), az = fabsf(rz);
+                const float kA = 2.6180339887f, kB = 1.6180339887f, kC = 4.2360679775f;  // 1+phi, phi, 2phi+1
+                const float d0 = kA * (ax + ay + az);
+                const float d1 = fmaf(kB, ax, kC * az);
+                const float d2 = fmaf(kC, ay, kB * az);
+                const float d3 = fmaf(kC, ax, kB * ay);
+                int which = 0;
+                float dbest = d0;
+                if (d1 > dbest) { dbest = d1; which = 1; }
+                if (d2 > dbest) { dbest = d2; which = 2; }
+                if (d3 > dbest) { dbest = d3; which = 3; }
+                const int oct = (rx < 0.0f ? 1 : 0) | (ry < 0.0f ? 2 : 0) | (rz < 0.0f ? 4 : 0);
+                const int best = slut[oct * 4 + which];
+                float bx, by, bz;
+                int face = -1;
+                if (face_hit_s(smesh + best * 16, rx, ry, rz, bx, by, bz) && bx > 1e-3f && by > 1e-3f &&
+                    bz > 1e-3f) {
+                    face = best;
+                } else {
+                    for (int f = 0; f < kFaces; f++) {
+                        if (face_hit_s(smesh + f * 16, rx, ry, rz, bx, by, bz)) { face = f; break; }
+                    }
+                }
+                if (face < 0) break;  // "unreachable" in the reference (sift.c:1288-1290)
+                const float mag = sqrtf(n2);
+
+                // SIFT3D_desc_acc_interp (sift.c:1318-1397)
+                const int bxi = (int) vbx, byi = (int) vby, bzi = (int) vbz;
+                const int key = bxi | (byi << 2) | (bzi << 4) | (face << 6);
+                if (key != cur_key) {
+                    S3D_FLUSH();
+                    cur_key = key;
+                    cbx = bxi; cby = byi; cbz = bzi;
+                    ci0 = sidx[face * 3]; ci1 = sidx[face * 3 + 1]; ci2 = sidx[face * 3 + 2];
+#pragma unroll
+                    for (int c = 0; c < 8; c++) acc[c][0] = acc[c][1] = acc[c][2] = 0.0f;
+                }
+                const float fx = __fsub_rn(vbx, floorf(vbx));
+                const float fy = __fsub_rn(vby, floorf(vby));
+                const float fz = __fsub_rn(vbz, floorf(vbz));
+#pragma unroll
+                for (int c = 0; c < 8; c++) {
+                    const int ddx = c >> 2, ddy = (c >> 1) & 1, ddz = c & 1;
+                    const float wgt = __fmul_rn(
+                        __fmul_rn(ddx == 0 ? __fsub_rn(1.0f, fx) : fx, ddy == 0 ? __fsub_rn(1.0f, fy) : fy),
+                        ddz == 0 ? __fsub_rn(1.0f, fz) : fz);
+                    const float mw = __fmul_rn(mag, wgt);
+                    acc[c][0] = __fadd_rn(acc[c][0], __fmul_rn(mw, bx));
+                    acc[c][1] = __fadd_rn(acc[c][1], __fmul_rn(mw, by));
+                    acc[c][2] = __fadd_rn(acc[c][2], __fmul_rn(mw, bz));
+                }
+            } while (0);
+            // next entry of the flattened list
+            if (++x > xend && t + 1 < t1) {
+                do { r++; } while (row_off[r + 1] == row_off[r]);
+                x = (int) row_xa[r];
+                xend = x + (row_off[r + 1] - row_off[r]) - 1;
+                S3D_ROW_SETUP();
+            }
+        }
+        S3D_FLUSH();
+#undef S3D_ROW_SETUP
+    }
+#undef S3D_FLUSH
+    __syncthreads();
+    for (int i = tid; i < kDescNumel; i += kDescThreads) {
+        const long long q = (long long) (((unsigned long long) hhi[i] << 32) | (unsigned long long) hlo[i]);
+        hist[i] = (float) ((double) q * kFixInv);
+    }
+    __syncthreads();
+
+    // normalise, clamp, normalise (sift.c:1513-1526)
+    const float trunc = __fdiv_rn(__fmul_rn(0.2f, 128.0f), (float) kDescNumel);  // sift.c:45
+    for (int pass = 0; pass < 2; pass++) {
+        double ssq = 0.0;
+        for (int i = tid; i < kDescNumel; i += kDescThreads) {
+            const float el = hist[i];
+            ssq += (double) el * (double) el;
+        }
+        for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
+        if (lane == 0) red[warp] = ssq;
+        __syncthreads();
+        if (tid == 0) {
+            double t = 0.0;
+            for (int wv = 0; wv < kDescThreads / 32; wv++) t += red[wv];
+            norm_sh = sqrt(t) + DBL_EPSILON;
+        }
+        __syncthreads();
+        const float norm_inv = (float) (1.0 / norm_sh);  // sift.c:1423
+        for (int i = tid; i < kDescNumel; i += kDescThreads) {
+            float el = __fmul_rn(hist[i], norm_inv);
+            if (pass == 0) el = fminf(el, trunc);
+            hist[i] = el;
+        }
+        __syncthreads();
+    }
+    float *o = desc_out + (size_t) J.out_index * kDescNumel;
+    for (int i = tid; i < kDescNumel; i += kDescThreads) o[i] = hist[i];
+}
+
+// Host: upper bound of the (y, z) rows of a job's window (the kernel clamps the window to
+// the volume, which only makes it smaller).
+int desc_job_rows(const DescJob &J) {
+    const double rad = 2.0 * (double) J.sigma * 1.001;
+    const double wy = 2.0 * ceil(rad / (double) J.uy) + 3.0, wz = 2.0 * ceil(rad / (double) J.uz) + 3.0;
+    const double wyc = wy < (double) J.ny ? wy : (double) J.ny;
+    const double wzc = wz < (double) J.nz ? wz : (double) J.nz;
+    const double rows = wyc * wzc;
+    return rows > 2.0e9 ? 2000000000 : (int) rows;
+}
+
+int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_rows, float *d_desc,
                        uint64_t *launches) {
     if (n <= 0) return 0;
-    descriptor_kernel<<<(unsigned) n, kDescThreads, 0, st>>>(d_jobs, n, d_desc);
+    // the flattened-list kernel keeps 6 bytes per window row in shared memory; windows too
+    // large for that (huge sigma / tiny units) take the row-walking kernel
+    static const bool force_rows = getenv("SIFT3D_CUDA_DESC_ROWS") != nullptr;
+    const size_t dyn = ((size_t) max_rows + 1) * 4 + (size_t) max_rows * 2 + 16;
+    const size_t kMaxDyn = 96 * 1024;
+    if (!force_rows && max_rows >= 1 && dyn <= kMaxDyn) {
+        static size_t attr = 0;
+        if (dyn > attr) {
+            S3D_CK(cudaFuncSetAttribute(descriptor_flat_kernel,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kMaxDyn));
+            attr = kMaxDyn;
+        }
+        descriptor_flat_kernel<<<(unsigned) n, kDescThreads, dyn, st>>>(d_jobs, n, d_desc, max_rows);
+    } else {
+        descriptor_rows_kernel<<<(unsigned) n, kDescThreads, 0, st>>>(d_jobs, n, d_desc);
+    }
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
     return 0;

@@ -6,6 +6,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <new>
 #include <vector>
 
@@ -461,7 +462,13 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
         J.cx = (float) k.x; J.cy = (float) k.y; J.cz = (float) k.z;  // sift.c:1474-1476
         J.sigma = (float) (k.sd * 7.071067812);                        // sift.c:43,1453
         for (int j = 0; j < 9; j++) J.R[j] = k.R[j];
+        J.out_index = i;
+        J.max_rows = desc_job_rows(J);
     }
+    // largest windows first: the grid drains in launch order, so the long CTAs start early
+    std::stable_sort(jobs.begin(), jobs.end(),
+                     [](const DescJob &a, const DescJob &b) { return a.max_rows > b.max_rows; });
+    const int max_rows = jobs[0].max_rows;
     if (ctx->desc_jobs.ensure(sizeof(DescJob) * (size_t) num)) return -1;
     float *d_out = desc;
     if (!desc_on_device) {
@@ -472,7 +479,7 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
     S3D_CK(cudaMemcpyAsync(ctx->desc_jobs.p, jobs.data(), sizeof(DescJob) * (size_t) num,
                            cudaMemcpyHostToDevice, st));
     S3D_CK(cudaEventRecord(ctx->dv[DV_H2D], st));
-    if (launch_descriptors(st, (const DescJob *) ctx->desc_jobs.p, num, d_out, &ctx->launches))
+    if (launch_descriptors(st, (const DescJob *) ctx->desc_jobs.p, num, max_rows, d_out, &ctx->launches))
         return -1;
     S3D_CK(cudaEventRecord(ctx->dv[DV_KERNEL], st));
     if (!desc_on_device)
