@@ -408,14 +408,32 @@ __device__ __forceinline__ bool face_hit_s(const float *__restrict__ fm, float g
     return true;
 }
 
+constexpr int kPadDim = kHistPerDim + 1;
+constexpr int kPadNumel = kPadDim * kPadDim * kPadDim * kVerts;
+constexpr int kFix2LoBits = 12;
+constexpr float kFix2Scale = 268435456.0f;  // 2^28 fixed-point units per 1.0
+constexpr double kFix2Inv = 1.0 / 268435456.0;
+
+// Carry-free two-word fixed point: q = v * 2^28 as int64, low 12 bits into an unsigned word
+// and the (signed) rest into a second word, both with the native 32-bit ATOMS.ADD. The low
+// word holds up to 2^20 additions, the high word sums of magnitude < 2^15; integer adds
+// commute, so descriptors stay bit-reproducible from run to run.
+__device__ __forceinline__ void fix_add2(unsigned *lo, int *hi, int i, float v) {
+    const long long q = __float2ll_rn(v * kFix2Scale);
+    atomicAdd(lo + i, (unsigned) q & ((1u << kFix2LoBits) - 1u));
+    atomicAdd(hi + i, (int) (q >> kFix2LoBits));
+}
+
 __global__ void __launch_bounds__(kDescThreads)
 descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ desc_out,
                        int max_rows) {
     extern __shared__ __align__(16) int dyn_smem[];
     int *row_off = dyn_smem;                                            // [max_rows + 1]
     short *row_xa = reinterpret_cast<short *>(dyn_smem + max_rows + 1);  // [max_rows]
-    __shared__ unsigned hlo[kDescNumel];
-    __shared__ unsigned hhi[kDescNumel];
+    // 5x5x5 cells: the 8 trilinear targets of any voxel exist, so the flush needs no range
+    // tests (cells with an index of 4 are never read back, sift.c:1346-1352 drops them)
+    __shared__ unsigned hlo[kPadNumel];
+    __shared__ int hhi[kPadNumel];
     __shared__ float hist[kDescNumel];
     __shared__ __align__(16) float smesh[kFaces * 16];
     __shared__ int sidx[kFaces * 3];
@@ -428,9 +446,9 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     const DescJob J = jobs[ki];
     const int tid = threadIdx.x;
     const int lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < kDescNumel; i += kDescThreads) {
+    for (int i = tid; i < kPadNumel; i += kDescThreads) {
         hlo[i] = 0u;
-        hhi[i] = 0u;
+        hhi[i] = 0;
     }
     if (tid < kFaces) {
         float *fm = smesh + tid * 16;
@@ -543,18 +561,17 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
 
     float acc[8][3];
     int cur_key = -1;
-    int ci0 = 0, ci1 = 0, ci2 = 0, cbx = 0, cby = 0, cbz = 0;
+    int ci0 = 0, ci1 = 0, ci2 = 0;
 
 #define S3D_FLUSH()                                                                        \
     if (cur_key >= 0) {                                                                    \
+        const int hb = ((cur_key & 3) + ((cur_key >> 2) & 3) * kPadDim +                   \
+                        ((cur_key >> 4) & 3) * kPadDim * kPadDim) * kVerts;                \
         _Pragma("unroll") for (int c = 0; c < 8; c++) {                                    \
-            const int hx = cbx + (c >> 2), hy = cby + ((c >> 1) & 1), hz = cbz + (c & 1);  \
-            if (hx < kHistPerDim && hy < kHistPerDim && hz < kHistPerDim) {                \
-                const int hb = (hx + hy * kHistPerDim + hz * kHistPerDim * kHistPerDim) * kVerts; \
-                if (acc[c][0] != 0.0f) fix_add(hlo, hhi, hb + ci0, acc[c][0]);             \
-                if (acc[c][1] != 0.0f) fix_add(hlo, hhi, hb + ci1, acc[c][1]);             \
-                if (acc[c][2] != 0.0f) fix_add(hlo, hhi, hb + ci2, acc[c][2]);             \
-            }                                                                              \
+            const int off = ((c >> 2) + ((c >> 1) & 1) * kPadDim + (c & 1) * kPadDim * kPadDim) * kVerts; \
+            fix_add2(hlo, hhi, hb + off + ci0, acc[c][0]);                                 \
+            fix_add2(hlo, hhi, hb + off + ci1, acc[c][1]);                                 \
+            fix_add2(hlo, hhi, hb + off + ci2, acc[c][2]);                                 \
         }                                                                                  \
     }
 
@@ -566,6 +583,7 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             if (row_off[mid] <= t0) lo = mid; else hi = mid;
         }
         int r = lo;
+        int y = y0 + r % wy, z = z0 + r / wy;
         int x = (int) row_xa[r] + (t0 - row_off[r]);
         int xend = (int) row_xa[r] + (row_off[r + 1] - row_off[r]) - 1;
         // per-row invariants
@@ -573,7 +591,6 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         const float *__restrict__ row;
 #define S3D_ROW_SETUP()                                                                    \
         {                                                                                  \
-            const int y = y0 + r % wy, z = z0 + r / wy;                                    \
             dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);                                 \
             dz = __fmul_rn(__fsub_rn((float) z, cz), uzf);                                 \
             dy2 = __fmul_rn(dy, dy);                                                       \
@@ -630,8 +647,8 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
                 const int best = slut[oct * 4 + which];
                 float bx, by, bz;
                 int face = -1;
-                if (face_hit_s(smesh + best * 16, rx, ry, rz, bx, by, bz) && bx > 1e-3f && by > 1e-3f &&
-                    bz > 1e-3f) {
+                if (face_hit_s(smesh + best * 16, rx, ry, rz, bx, by, bz) && bx > 1e-5f && by > 1e-5f &&
+                    bz > 1e-5f) {
                     face = best;
                 } else {
                     for (int f = 0; f < kFaces; f++) {
@@ -647,7 +664,6 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
                 if (key != cur_key) {
                     S3D_FLUSH();
                     cur_key = key;
-                    cbx = bxi; cby = byi; cbz = bzi;
                     ci0 = sidx[face * 3]; ci1 = sidx[face * 3 + 1]; ci2 = sidx[face * 3 + 2];
 #pragma unroll
                     for (int c = 0; c < 8; c++) acc[c][0] = acc[c][1] = acc[c][2] = 0.0f;
@@ -669,7 +685,10 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             } while (0);
             // next entry of the flattened list
             if (++x > xend && t + 1 < t1) {
-                do { r++; } while (row_off[r + 1] == row_off[r]);
+                do {
+                    r++;
+                    if (++y > y1) { y = y0; z++; }
+                } while (row_off[r + 1] == row_off[r]);
                 x = (int) row_xa[r];
                 xend = x + (row_off[r + 1] - row_off[r]) - 1;
                 S3D_ROW_SETUP();
@@ -681,8 +700,11 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
 #undef S3D_FLUSH
     __syncthreads();
     for (int i = tid; i < kDescNumel; i += kDescThreads) {
-        const long long q = (long long) (((unsigned long long) hhi[i] << 32) | (unsigned long long) hlo[i]);
-        hist[i] = (float) ((double) q * kFixInv);
+        const int bin = i % kVerts, cell = i / kVerts;
+        const int hx = cell & 3, hy = (cell >> 2) & 3, hz = cell >> 4;
+        const int j = (hx + hy * kPadDim + hz * kPadDim * kPadDim) * kVerts + bin;
+        const long long q = (long long) hhi[j] * (1ll << kFix2LoBits) + (long long) hlo[j];
+        hist[i] = (float) ((double) q * kFix2Inv);
     }
     __syncthreads();
 
