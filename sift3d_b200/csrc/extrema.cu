@@ -79,6 +79,86 @@ extrema_kernel(const ExtremaParams P, const float *__restrict__ dogmax, float pe
     (void) peak_thresh_f;
 }
 
+// Vectorised variant for rows that are float4 addressable (nx % 4 == 0): a thread owns 4
+// consecutive voxels, loads the kp+1 Gaussian levels that bound the keypoint DoG levels
+// once (independent LDG.128s in flight together), forms all DoG values in registers and
+// only touches neighbours for the few voxels that pass the contrast threshold.
+template <int KP>
+__global__ void __launch_bounds__(256)
+extrema_vec4_kernel(const ExtremaParams P, const float *__restrict__ dogmax, double peak_thresh,
+                    Cand *__restrict__ cand, int cap, int *__restrict__ count) {
+    const int nx = P.nx, ny = P.ny, nz = P.nz;
+    constexpr int kp = KP;
+    const int nx4 = nx >> 2;
+    const int x4 = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    const int z = blockIdx.z;
+    const bool row_ok = x4 < nx4 && y >= 1 && y <= ny - 2 && z >= 1 && z <= nz - 2;
+    const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
+    const size_t idx0 = (size_t) z * zs + (size_t) y * ys + (size_t) x4 * 4;
+    const unsigned lane = (threadIdx.y * blockDim.x + threadIdx.x) & 31u;
+
+    float4 g[KP + 1];  // levels 1 .. kp+1 of P.g (DoG s = g[s+1] - g[s+2])
+    if (row_ok) {
+#pragma unroll
+        for (int l = 0; l <= kp; l++) g[l] = *reinterpret_cast<const float4 *>(P.g[l + 1] + idx0);
+    }
+#pragma unroll
+    for (int s = 0; s < kp; s++) {
+        const float thr = (float) (peak_thresh * (double) dogmax[s]);
+        float v4[4] = {0.f, 0.f, 0.f, 0.f};
+        unsigned pass = 0;
+        if (row_ok) {
+            const float4 a = g[s], b = g[s + 1];
+            v4[0] = __fsub_rn(a.x, b.x); v4[1] = __fsub_rn(a.y, b.y);
+            v4[2] = __fsub_rn(a.z, b.z); v4[3] = __fsub_rn(a.w, b.w);
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const int x = x4 * 4 + c;
+                if ((v4[c] > thr || v4[c] < -thr) && x >= 1 && x <= nx - 2) pass |= 1u << c;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            bool hit = false;
+            const float v = v4[c];
+            if (pass & (1u << c)) {
+                const float *__restrict__ ga = P.g[s + 1];
+                const float *__restrict__ gb = P.g[s + 2];
+                const size_t idx = idx0 + c;
+                const float prev = __fsub_rn(P.g[s][idx], ga[idx]);
+                const float next = __fsub_rn(gb[idx], P.g[s + 3][idx]);
+                const float xp = __fsub_rn(ga[idx + 1], gb[idx + 1]), xm = __fsub_rn(ga[idx - 1], gb[idx - 1]);
+                const float yp = __fsub_rn(ga[idx + ys], gb[idx + ys]), ym = __fsub_rn(ga[idx - ys], gb[idx - ys]);
+                const float zp = __fsub_rn(ga[idx + zs], gb[idx + zs]), zm = __fsub_rn(ga[idx - zs], gb[idx - zs]);
+                const bool is_max = v > prev && v > xp && v > xm && v > yp && v > ym && v > zm &&
+                                    v > zp && v > next;
+                const bool is_min = v < prev && v < xp && v < xm && v < yp && v < ym && v < zm &&
+                                    v < zp && v < next;
+                hit = is_max || is_min;
+            }
+            const unsigned ballot = __ballot_sync(0xffffffffu, hit);
+            if (ballot) {
+                int base = 0;
+                const int leader = __ffs(ballot) - 1;
+                if ((int) lane == leader) base = atomicAdd(count, __popc(ballot));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (hit) {
+                    const int pos = base + __popc(ballot & ((1u << lane) - 1u));
+                    if (pos < cap) {
+                        Cand cd;
+                        cd.key = ((unsigned long long) s << 60) | ((unsigned long long) z << 40) |
+                                 ((unsigned long long) y << 20) | (unsigned long long) (x4 * 4 + c);
+                        cd.strength = fabsf(v);
+                        cd.pad = 0;
+                        cand[pos] = cd;
+                    }
+                }
+            }
+        }
+    }
+}
+
 // Rank sort: candidate i goes to slot #{j : key_j < key_i}. Keys are unique (one per
 // voxel and level) so the ranks are a permutation; the result is the reference's serial
 // scan order (s, z, y, x) regardless of the order the atomics appended them in.
@@ -114,9 +194,25 @@ int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, in
     P.ny = ny;
     P.nz = nz;
     S3D_CK(cudaMemsetAsync(d_count, 0, sizeof(int), st));
-    dim3 block(128, 1, 1);
-    dim3 grid((unsigned) ((nx + 127) / 128), (unsigned) ny, (unsigned) nz);
-    extrema_kernel<<<grid, block, 0, st>>>(P, d_dogmax, 0.f, peak_thresh, d_cand, cap, d_count);
+    bool aligned = nx % 4 == 0;
+    for (int i = 0; i < num_kp_levels + 3; i++) aligned = aligned && ((uintptr_t) g[i] & 15) == 0;
+    if (aligned && num_kp_levels >= 1 && num_kp_levels <= 4) {
+        const int nx4 = nx / 4;
+        int bx = 1;
+        while (bx < nx4 && bx < 64) bx <<= 1;  // power of two <= 64 so that warps stay row aligned
+        dim3 block((unsigned) bx, (unsigned) (256 / bx), 1);
+        dim3 grid((unsigned) ((nx4 + bx - 1) / bx), (unsigned) ((ny + block.y - 1) / block.y), (unsigned) nz);
+        switch (num_kp_levels) {
+        case 1: extrema_vec4_kernel<1><<<grid, block, 0, st>>>(P, d_dogmax, peak_thresh, d_cand, cap, d_count); break;
+        case 2: extrema_vec4_kernel<2><<<grid, block, 0, st>>>(P, d_dogmax, peak_thresh, d_cand, cap, d_count); break;
+        case 3: extrema_vec4_kernel<3><<<grid, block, 0, st>>>(P, d_dogmax, peak_thresh, d_cand, cap, d_count); break;
+        default: extrema_vec4_kernel<4><<<grid, block, 0, st>>>(P, d_dogmax, peak_thresh, d_cand, cap, d_count); break;
+        }
+    } else {
+        dim3 block(128, 1, 1);
+        dim3 grid((unsigned) ((nx + 127) / 128), (unsigned) ny, (unsigned) nz);
+        extrema_kernel<<<grid, block, 0, st>>>(P, d_dogmax, 0.f, peak_thresh, d_cand, cap, d_count);
+    }
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
     return 0;

@@ -128,38 +128,47 @@ orient_kernel(const Cand *__restrict__ cands, int n, const OctaveInfo info, doub
 
     double a00 = 0, a01 = 0, a02 = 0, a11 = 0, a12 = 0, a22 = 0;
     double gx = 0, gy = 0, gz = 0;  // window gradient, summed in double, narrowed at the end
-    for (int i = threadIdx.x; i < total; i += kOrientThreads) {
-        const int lx = i % wx;
-        const int t = i / wx;
-        const int ly = t % wy;
-        const int lz = t / wy;
-        const int x = x0 + lx, y = y0 + ly, z = z0 + lz;
-        const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
+    // One (y, z) row of the window per thread at a time; within a row only the chord that
+    // can pass the sphere test is walked (the exact test stays per voxel).
+    (void) total;
+    const float rad2f_hi = (float) rad2 * 1.0001f;
+    const int nrows = wx > 0 ? wy * wz : 0;
+    for (int r = threadIdx.x; r < nrows; r += kOrientThreads) {
+        const int y = y0 + r % wy, z = z0 + r / wy;
         const float dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);
         const float dz = __fmul_rn(__fsub_rn((float) z, cz), uzf);
-        const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-        if ((double) sq > rad2) continue;
-        // weight = expf(-0.5 * sq_dist / (sigma * sigma)): double argument narrowed to float
-        // (sift.c:972). exp() in double then one rounding is a correctly rounded expf.
-        const float arg = (float) (-0.5 * (double) sq / sig2);
-        const float w = (float) exp((double) arg);
-        const size_t idx = (size_t) z * zs + (size_t) y * ys + x;
-        float vx = __fmul_rn(0.5f, __fsub_rn(img[idx + 1], img[idx - 1]));
-        float vy = __fmul_rn(0.5f, __fsub_rn(img[idx + ys], img[idx - ys]));
-        float vz = __fmul_rn(0.5f, __fsub_rn(img[idx + zs], img[idx - zs]));
-        vx = __fmul_rn(vx, ixu);
-        vy = __fmul_rn(vy, iyu);
-        vz = __fmul_rn(vz, izu);
-        const double wd = (double) w;
-        a00 += (double) vx * (double) vx * wd;
-        a01 += (double) vx * (double) vy * wd;
-        a02 += (double) vx * (double) vz * wd;
-        a11 += (double) vy * (double) vy * wd;
-        a12 += (double) vy * (double) vz * wd;
-        a22 += (double) vz * (double) vz * wd;
-        gx += (double) __fmul_rn(vx, w);
-        gy += (double) __fmul_rn(vy, w);
-        gz += (double) __fmul_rn(vz, w);
+        const float dy2 = __fmul_rn(dy, dy), dz2 = __fmul_rn(dz, dz);
+        const float rem = rad2f_hi - dy2 - dz2;
+        if (rem < 0.0f) continue;
+        const float half = sqrtf(rem) * ixu + 0.01f;
+        const int xa = max(x0, (int) ceilf(cx - half)), xb = min(x1, (int) floorf(cx + half));
+        const float *__restrict__ row = img + (size_t) z * zs + (size_t) y * ys;
+        for (int x = xa; x <= xb; x++) {
+            const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
+            const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), dy2), dz2);
+            if ((double) sq > rad2) continue;
+            // weight = expf(-0.5 * sq_dist / (sigma * sigma)): the argument is evaluated in
+            // double and narrowed to float (sift.c:972); expf itself in fp32 (<= 2 ulp)
+            const float arg = (float) (-0.5 * (double) sq / sig2);
+            const float w = expf(arg);
+            float vx = __fmul_rn(0.5f, __fsub_rn(row[x + 1], row[x - 1]));
+            float vy = __fmul_rn(0.5f, __fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys]));
+            float vz = __fmul_rn(0.5f, __fsub_rn(row[x + zs], row[(ptrdiff_t) x - (ptrdiff_t) zs]));
+            vx = __fmul_rn(vx, ixu);
+            vy = __fmul_rn(vy, iyu);
+            vz = __fmul_rn(vz, izu);
+            const double wd = (double) w;
+            const double dvx = (double) vx, dvy = (double) vy, dvz = (double) vz;
+            a00 += dvx * dvx * wd;
+            a01 += dvx * dvy * wd;
+            a02 += dvx * dvz * wd;
+            a11 += dvy * dvy * wd;
+            a12 += dvy * dvz * wd;
+            a22 += dvz * dvz * wd;
+            gx += (double) __fmul_rn(vx, w);
+            gy += (double) __fmul_rn(vy, w);
+            gz += (double) __fmul_rn(vz, w);
+        }
     }
 
     __shared__ double red[kOrientThreads / 32][9];
