@@ -49,8 +49,27 @@ __device__ __forceinline__ float conv_point_generic(const float *__restrict__ li
     float acc = 0.0f;
     if (p >= start && p <= end) {
         // interior pass: the coordinate is carried across taps (imutil.c:803-818)
+        // The coordinate chain does not depend on the samples, so the taps are evaluated in
+        // batches of 4: coordinates first, then the 8 loads together, then the in-order
+        // accumulation (the loads of one voxel would otherwise serialise on L2 latency).
         float c = (float) p;
-        for (int d = -hw; d <= hw; d++) {
+        int d = -hw;
+        for (; d + 3 <= hw; d += 4) {
+            float cs[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float step = __fmul_rn((float) (d + j), uf);
+                c = __fsub_rn(c, step);
+                cs[j] = c;
+                c = __fadd_rn(c, step);
+            }
+            float sv[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) sv[j] = samp(line, stride, cs[j], n, scale, dv);
+#pragma unroll
+            for (int j = 0; j < 4; j++) acc = __fadd_rn(acc, __fmul_rn(taps[d + j + hw], sv[j]));
+        }
+        for (; d <= hw; d++) {
             const float tap = taps[d + hw];
             const float step = __fmul_rn((float) d, uf);
             c = __fsub_rn(c, step);
@@ -74,25 +93,46 @@ __device__ __forceinline__ float conv_point_generic(const float *__restrict__ li
     return acc;
 }
 
-template <int AXIS>
+// forward: cross-block max reduction, defined with the max-abs kernels below
+__device__ __forceinline__ void block_atomic_max(float m, float *out);
+
+// One axis of the generic 3-pass blur, one thread per voxel. The z pass (EPI) also carries
+// the epilogue of a level: max|prev - out| (DoG max-abs) and the 2x decimation.
+template <int AXIS, bool EPI>
 __global__ void __launch_bounds__(256)
 blur_axis_generic_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny,
                          int nz, const float *__restrict__ taps, int hw, float uf, int uhw,
-                         const float *__restrict__ divisor) {
-    const size_t total = (size_t) nx * ny * nz;
-    const size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= total) return;
-    const int x = (int) (idx % nx);
-    const int y = (int) ((idx / nx) % ny);
-    const int z = (int) (idx / ((size_t) nx * ny));
-    const int p = AXIS == 0 ? x : (AXIS == 1 ? y : z);
-    const int n = AXIS == 0 ? nx : (AXIS == 1 ? ny : nz);
-    const size_t stride = AXIS == 0 ? 1 : (AXIS == 1 ? (size_t) nx : (size_t) nx * ny);
-    float dv = 0.0f;
-    if (divisor != nullptr) dv = *divisor;
-    const bool scale = dv != 0.0f;  // im_scale leaves an all-zero image alone (imutil.c:706)
-    dst[idx] = conv_point_generic(src + (idx - (size_t) p * stride), stride, p, n, taps, hw, uf,
-                                  uhw, scale, dv);
+                         const float *__restrict__ divisor, const float *__restrict__ dog_prev,
+                         float *__restrict__ dogmax, float *__restrict__ ds_dst) {
+    // 3-D launch (x in the block, rows and planes in the grid): no 64-bit div/mod per thread
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    const int z = blockIdx.z;
+    const size_t idx = ((size_t) z * ny + (size_t) y) * nx + (size_t) x;
+    float vmax = 0.0f;
+    if (x < nx && y < ny) {
+        const int p = AXIS == 0 ? x : (AXIS == 1 ? y : z);
+        const int n = AXIS == 0 ? nx : (AXIS == 1 ? ny : nz);
+        const size_t stride = AXIS == 0 ? 1 : (AXIS == 1 ? (size_t) nx : (size_t) nx * ny);
+        float dv = 0.0f;
+        if (divisor != nullptr) dv = *divisor;
+        const bool scale = dv != 0.0f;  // im_scale leaves an all-zero image alone (imutil.c:706)
+        const float o = conv_point_generic(src + (idx - (size_t) p * stride), stride, p, n, taps, hw,
+                                           uf, uhw, scale, dv);
+        dst[idx] = o;
+        if (EPI) {
+            if (dogmax != nullptr) vmax = fabsf(__fsub_rn(dog_prev[idx], o));
+            if (ds_dst != nullptr && !((x | y | z) & 1)) {
+                const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
+                const int qx = x >> 1, qy = y >> 1, qz = z >> 1;
+                if (qx < dnx && qy < dny && qz < dnz)
+                    ds_dst[((size_t) qz * dny + qy) * dnx + qx] = o;
+            }
+        }
+    }
+    if (EPI) {
+        if (dogmax != nullptr) block_atomic_max(vmax, dogmax);
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -117,11 +157,12 @@ downsample_kernel(const float *__restrict__ src, float *__restrict__ dst, int sn
 __device__ __forceinline__ void block_atomic_max(float m, float *out) {
     for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     __shared__ float wmax[32];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tid = threadIdx.y * blockDim.x + threadIdx.x;  // 1-D and 2-D blocks
+    const int lane = tid & 31, warp = tid >> 5;
     if (lane == 0) wmax[warp] = m;
     __syncthreads();
     if (warp == 0) {
-        m = lane < (int) (blockDim.x >> 5) ? wmax[lane] : 0.0f;
+        m = lane < (int) ((blockDim.x * blockDim.y) >> 5) ? wmax[lane] : 0.0f;
         for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
         if (lane == 0) atomicMax(reinterpret_cast<int *>(out), __float_as_int(m));
     }
@@ -286,19 +327,20 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         }
     }
 
-    blur_axis_generic_kernel<0><<<blocks, 256, 0, st>>>(src, tmp_a, nx, ny, nz, d_taps, hw, ax.uf,
-                                                        ax.uhw, d_divisor);
-    blur_axis_generic_kernel<1><<<blocks, 256, 0, st>>>(tmp_a, tmp_b, nx, ny, nz, d_taps, hw,
-                                                        ay.uf, ay.uhw, nullptr);
-    blur_axis_generic_kernel<2><<<blocks, 256, 0, st>>>(tmp_b, dst, nx, ny, nz, d_taps, hw, az.uf,
-                                                        az.uhw, nullptr);
+    const bool want_max = d_dogmax_slot != nullptr && dog_prev != nullptr;
+    if (want_max) S3D_CK(cudaMemsetAsync(d_dogmax_slot, 0, sizeof(float), st));
+    int bx = 32;
+    while (bx < nx && bx < 256) bx <<= 1;
+    const dim3 gblock((unsigned) bx, (unsigned) (256 / bx), 1);
+    const dim3 ggrid((unsigned) ((nx + bx - 1) / bx), (unsigned) ((ny + gblock.y - 1) / gblock.y), (unsigned) nz);
+    blur_axis_generic_kernel<0, false><<<ggrid, gblock, 0, st>>>(
+        src, tmp_a, nx, ny, nz, d_taps, hw, ax.uf, ax.uhw, d_divisor, nullptr, nullptr, nullptr);
+    blur_axis_generic_kernel<1, false><<<ggrid, gblock, 0, st>>>(
+        tmp_a, tmp_b, nx, ny, nz, d_taps, hw, ay.uf, ay.uhw, nullptr, nullptr, nullptr, nullptr);
+    blur_axis_generic_kernel<2, true><<<ggrid, gblock, 0, st>>>(
+        tmp_b, dst, nx, ny, nz, d_taps, hw, az.uf, az.uhw, nullptr, dog_prev,
+        want_max ? d_dogmax_slot : nullptr, ds_dst);
     if (launches) *launches += 3;
-    if (d_dogmax_slot != nullptr && dog_prev != nullptr) {
-        if (launch_absdiffmax(st, dog_prev, dst, total, d_dogmax_slot, launches)) return -1;
-    }
-    if (ds_dst != nullptr) {
-        if (launch_downsample(st, dst, ds_dst, nx, ny, nz, launches)) return -1;
-    }
     S3D_CK(cudaGetLastError());
     return 0;
 }

@@ -69,7 +69,9 @@ int launch_absdiffmax(cudaStream_t st, const float *a, const float *b, size_t n,
 int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, int nx, int ny,
                    int nz, const float *d_dogmax, double peak_thresh, Cand *d_cand, int cap,
                    int *d_count, uint64_t *launches);
-int launch_order(cudaStream_t st, const Cand *d_in, int n, Cand *d_out, uint64_t *launches);
+// all octaves in one launch; counts stay on the device
+int launch_order_all(cudaStream_t st, const Cand *d_raw, Cand *d_sorted, const int *base,
+                     const int *cap, int noct, const int *d_counts, uint64_t *launches);
 
 // orient.cu
 struct OctaveInfo {  // what the per-candidate kernels need to know about one octave
@@ -79,8 +81,19 @@ struct OctaveInfo {  // what the per-candidate kernels need to know about one oc
     int nx, ny, nz;
     float ux, uy, uz;  // level units narrowed to float (sift.c:88-90)
 };
-int launch_orient(cudaStream_t st, const Cand *d_cands, int n, const OctaveInfo &info,
-                  double corner_thresh, sift3d_cuda_keypoint *d_out, uint64_t *launches);
+// Everything the orientation kernel needs to walk the candidate regions of all octaves.
+struct OrientPlan {
+    OctaveInfo oct[SIFT3D_CUDA_MAX_OCTAVES];
+    int base[SIFT3D_CUDA_MAX_OCTAVES];  // first slot of the octave's candidate region
+    int cap[SIFT3D_CUDA_MAX_OCTAVES];
+    int noct;
+};
+// One persistent launch over the candidates of every octave (counts read on the device,
+// work handed out through *d_work, which must be zero). Output slot = rank of the
+// candidate in the concatenated (o, s, z, y, x) order.
+int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d_plan,
+                      const int *d_counts, int *d_work, double corner_thresh,
+                      sift3d_cuda_keypoint *d_out, uint64_t *launches);
 
 // descriptor.cu
 struct DescJob {

@@ -162,26 +162,39 @@ extrema_vec4_kernel(const ExtremaParams P, const float *__restrict__ dogmax, dou
 // Rank sort: candidate i goes to slot #{j : key_j < key_i}. Keys are unique (one per
 // voxel and level) so the ranks are a permutation; the result is the reference's serial
 // scan order (s, z, y, x) regardless of the order the atomics appended them in.
+// One launch orders every octave: blockIdx.y = octave, counts are read on the device.
+struct OrderParams {
+    int base[SIFT3D_CUDA_MAX_OCTAVES];  // first slot of the octave's candidate region
+    int cap[SIFT3D_CUDA_MAX_OCTAVES];
+};
+
 __global__ void __launch_bounds__(256)
-order_kernel(const Cand *__restrict__ in, int n, Cand *__restrict__ out) {
+order_all_kernel(const Cand *__restrict__ raw, Cand *__restrict__ sorted, const OrderParams P,
+                 const int *__restrict__ counts) {
     __shared__ unsigned long long tile[256];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    Cand mine;
-    mine.key = ~0ull;
-    mine.strength = 0.f;
-    mine.pad = 0;
-    if (i < n) mine = in[i];
-    int rank = 0;
-    for (int base = 0; base < n; base += 256) {
-        const int j = base + threadIdx.x;
-        tile[threadIdx.x] = j < n ? in[j].key : ~0ull;
-        __syncthreads();
-        const int lim = min(256, n - base);
+    const int o = blockIdx.y;
+    const int n = min(counts[o], P.cap[o]);
+    const Cand *__restrict__ in = raw + P.base[o];
+    Cand *__restrict__ out = sorted + P.base[o];
+    for (int first = blockIdx.x * 256; first < n; first += gridDim.x * 256) {
+        const int i = first + threadIdx.x;
+        Cand mine;
+        mine.key = ~0ull;
+        mine.strength = 0.f;
+        mine.pad = 0;
+        if (i < n) mine = in[i];
+        int rank = 0;
+        for (int base = 0; base < n; base += 256) {
+            const int j = base + threadIdx.x;
+            __syncthreads();
+            tile[threadIdx.x] = j < n ? in[j].key : ~0ull;
+            __syncthreads();
+            const int lim = min(256, n - base);
 #pragma unroll 8
-        for (int k = 0; k < lim; k++) rank += tile[k] < mine.key ? 1 : 0;
-        __syncthreads();
+            for (int k = 0; k < lim; k++) rank += tile[k] < mine.key ? 1 : 0;
+        }
+        if (i < n) out[rank] = mine;
     }
-    if (i < n) out[rank] = mine;
 }
 
 int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, int nx, int ny,
@@ -193,7 +206,6 @@ int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, in
     P.nx = nx;
     P.ny = ny;
     P.nz = nz;
-    S3D_CK(cudaMemsetAsync(d_count, 0, sizeof(int), st));
     bool aligned = nx % 4 == 0;
     for (int i = 0; i < num_kp_levels + 3; i++) aligned = aligned && ((uintptr_t) g[i] & 15) == 0;
     if (aligned && num_kp_levels >= 1 && num_kp_levels <= 4) {
@@ -218,9 +230,14 @@ int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, in
     return 0;
 }
 
-int launch_order(cudaStream_t st, const Cand *d_in, int n, Cand *d_out, uint64_t *launches) {
-    if (n <= 0) return 0;
-    order_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>(d_in, n, d_out);
+int launch_order_all(cudaStream_t st, const Cand *d_raw, Cand *d_sorted, const int *base,
+                     const int *cap, int noct, const int *d_counts, uint64_t *launches) {
+    OrderParams P;
+    for (int o = 0; o < SIFT3D_CUDA_MAX_OCTAVES; o++) {
+        P.base[o] = o < noct ? base[o] : 0;
+        P.cap[o] = o < noct ? cap[o] : 0;
+    }
+    order_all_kernel<<<dim3(32, (unsigned) noct), 256, 0, st>>>(d_raw, d_sorted, P, d_counts);
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
     return 0;

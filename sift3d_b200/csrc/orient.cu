@@ -94,11 +94,34 @@ __device__ __forceinline__ T warp_sum(T v) {
 constexpr int kOrientThreads = 128;
 
 __global__ void __launch_bounds__(kOrientThreads)
-orient_kernel(const Cand *__restrict__ cands, int n, const OctaveInfo info, double corner_thresh,
-              sift3d_cuda_keypoint *__restrict__ out) {
-    const int ci = blockIdx.x;
-    if (ci >= n) return;
-    const Cand cd = cands[ci];
+orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict__ plan,
+                  const int *__restrict__ counts, int *__restrict__ work, double corner_thresh,
+                  sift3d_cuda_keypoint *__restrict__ out) {
+    __shared__ int s_first[SIFT3D_CUDA_MAX_OCTAVES + 1];  // rank of each octave's first candidate
+    __shared__ int s_ci;
+    __shared__ double red[kOrientThreads / 32][9];
+    const int noct = plan->noct;
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        for (int o = 0; o < noct; o++) {
+            s_first[o] = acc;
+            acc += min(counts[o], plan->cap[o]);
+        }
+        s_first[noct] = acc;
+    }
+    __syncthreads();
+    const int total = s_first[noct];
+  for (;;) {
+    // dynamic hand-out: windows differ 4x in size between keypoint levels
+    __syncthreads();
+    if (threadIdx.x == 0) s_ci = atomicAdd(work, 1);
+    __syncthreads();
+    const int ci = s_ci;
+    if (ci >= total) break;
+    int oi = 0;
+    while (ci >= s_first[oi + 1]) oi++;
+    const OctaveInfo &info = plan->oct[oi];
+    const Cand cd = sorted[plan->base[oi] + (ci - s_first[oi])];
     const int s = (int) (cd.key >> 60);
     const int kz = (int) ((cd.key >> 40) & 0xFFFFF);
     const int ky = (int) ((cd.key >> 20) & 0xFFFFF);
@@ -171,7 +194,6 @@ orient_kernel(const Cand *__restrict__ cands, int n, const OctaveInfo info, doub
         }
     }
 
-    __shared__ double red[kOrientThreads / 32][9];
     double vals[9] = {a00, a01, a02, a11, a12, a22, gx, gy, gz};
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -180,7 +202,7 @@ orient_kernel(const Cand *__restrict__ cands, int n, const OctaveInfo info, doub
         if (lane == 0) red[warp][k] = r;
     }
     __syncthreads();
-    if (threadIdx.x != 0) return;
+    if (threadIdx.x != 0) continue;
 #pragma unroll
     for (int k = 0; k < 9; k++) {
         double r = 0;
@@ -239,12 +261,15 @@ orient_kernel(const Cand *__restrict__ cands, int n, const OctaveInfo info, doub
     }
     kp.valid = ok ? 1 : 0;
     out[ci] = kp;
+  }  // candidates
 }
 
-int launch_orient(cudaStream_t st, const Cand *d_cands, int n, const OctaveInfo &info,
-                  double corner_thresh, sift3d_cuda_keypoint *d_out, uint64_t *launches) {
-    if (n <= 0) return 0;
-    orient_kernel<<<(unsigned) n, kOrientThreads, 0, st>>>(d_cands, n, info, corner_thresh, d_out);
+int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d_plan,
+                      const int *d_counts, int *d_work, double corner_thresh,
+                      sift3d_cuda_keypoint *d_out, uint64_t *launches) {
+    // persistent grid: 148 SMs x the CTAs that fit (94 registers x 128 threads -> 5 per SM)
+    orient_all_kernel<<<kNumSMs * 5, kOrientThreads, 0, st>>>(d_sorted, d_plan, d_counts, d_work,
+                                                          corner_thresh, d_out);
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
     return 0;

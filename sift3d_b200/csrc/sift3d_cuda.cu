@@ -52,7 +52,18 @@ struct sift3d_cuda_ctx {
     sift3d_cuda_plan_desc desc;
     int nlev = 0;  // Gaussian levels per octave = num_kp_levels + 3
     std::vector<Level> levels;          // [o * nlev + (s + 1)]
-    DevBuf pyr, input, tmp_a, tmp_b;    // arena
+    DevBuf pyr, input, tmp_a, tmp_b;    // arena (tmp_*: scratch of the 3-pass blur, octave 0)
+    DevBuf tmp_side;                    // scratch of octaves >= 1 (they run on their own streams)
+    std::vector<size_t> side_off;       // [o]: offset of octave o's two scratch volumes in tmp_side
+    // octave o >= 1 runs on oct_stream[o] as soon as its seed level exists (sift.c:694-705);
+    // ev_seed[o] = level (o+1, -1) written, ev_done[o] = octave o finished (levels + extrema)
+    cudaStream_t oct_stream[SIFT3D_CUDA_MAX_OCTAVES] = {};
+    cudaEvent_t ev_seed[SIFT3D_CUDA_MAX_OCTAVES] = {};
+    cudaEvent_t ev_done[SIFT3D_CUDA_MAX_OCTAVES] = {};
+    bool serial = false;                // $SIFT3D_CUDA_SERIAL: everything on one stream
+    DevBuf orient_plan;                 // OrientPlan on the device
+    OrientPlan *h_plan = nullptr;       // pinned staging copy
+    DevBuf work;                        // work counter of the persistent orientation kernel
     DevBuf taps;                        // (1 + filters) * SIFT3D_CUDA_MAX_TAPS floats
     DevBuf scalars;                     // [0] image max-abs; [1 + o*MAX_FILTERS + s] DoG max
     DevBuf cand_raw, cand_sorted;       // Cand regions, one per octave
@@ -122,9 +133,15 @@ sift3d_cuda_ctx *sift3d_cuda_ctx_create(int device) {
         return nullptr;
     }
     for (int i = 0; i < EV_COUNT; i++) cudaEventCreate(&ctx->ev[i]);
+    ctx->serial = getenv("SIFT3D_CUDA_SERIAL") != nullptr;
+    for (int o = 0; o < SIFT3D_CUDA_MAX_OCTAVES; o++) {
+        cudaEventCreateWithFlags(&ctx->ev_seed[o], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&ctx->ev_done[o], cudaEventDisableTiming);
+    }
     for (int i = 0; i < 8; i++) cudaEventCreate(&ctx->marks[i]);
     for (int i = 0; i < DV_COUNT; i++) cudaEventCreate(&ctx->dv[i]);
     if (cudaMallocHost((void **) &ctx->h_counts, sizeof(int) * 64) != cudaSuccess ||
+        cudaMallocHost((void **) &ctx->h_plan, sizeof(OrientPlan)) != cudaSuccess ||
         upload_mesh() != 0) {
         S3D_ERR("sift3d_cuda: context setup failed\n");
         sift3d_cuda_ctx_destroy(ctx);
@@ -141,6 +158,18 @@ void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx) {
     ctx->input.release();
     ctx->tmp_a.release();
     ctx->tmp_b.release();
+    ctx->tmp_side.release();
+    ctx->orient_plan.release();
+    ctx->work.release();
+    for (int o = 0; o < SIFT3D_CUDA_MAX_OCTAVES; o++) {
+        if (ctx->oct_stream[o]) {
+            cudaStreamSynchronize(ctx->oct_stream[o]);
+            cudaStreamDestroy(ctx->oct_stream[o]);
+        }
+        if (ctx->ev_seed[o]) cudaEventDestroy(ctx->ev_seed[o]);
+        if (ctx->ev_done[o]) cudaEventDestroy(ctx->ev_done[o]);
+    }
+    if (ctx->h_plan) cudaFreeHost(ctx->h_plan);
     ctx->taps.release();
     ctx->scalars.release();
     ctx->cand_raw.release();
@@ -232,6 +261,24 @@ int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
         ctx->tmp_b.ensure(n0 * sizeof(float)))
         return -1;
 
+    // octaves >= 1: own stream and own 3-pass scratch each
+    {
+        ctx->side_off.assign(noct, 0);
+        size_t side_total = 0;
+        for (int o = 1; o < noct; o++) {
+            ctx->side_off[o] = side_total;
+            side_total += 2 * ((ctx->level(o, 0).nvox() + 63) & ~(size_t) 63);
+            if (!ctx->oct_stream[o] &&
+                cudaStreamCreateWithFlags(&ctx->oct_stream[o], cudaStreamNonBlocking) != cudaSuccess) {
+                S3D_ERR("sift3d_cuda_plan: cannot create a stream\n");
+                return -1;
+            }
+        }
+        if (ctx->tmp_side.ensure((side_total + 64) * sizeof(float)) ||
+            ctx->orient_plan.ensure(sizeof(OrientPlan)) || ctx->work.ensure(sizeof(int) * 4))
+            return -1;
+    }
+
     // filters
     const int nfilt = d->num_kp_levels + 2;
     if (ctx->taps.ensure((size_t) (nfilt + 1) * SIFT3D_CUDA_MAX_TAPS * sizeof(float))) return -1;
@@ -312,59 +359,101 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
 
     // im_scale: max |v| (imutil.c:681-695); the division is applied on load by the first blur.
     if (launch_absmax(st, d_in, n0, ctx->d_scalar(0), &ctx->launches)) return -1;
+    S3D_CK(cudaMemsetAsync(ctx->counts.p, 0, sizeof(int) * 64, st));
+    S3D_CK(cudaMemsetAsync(ctx->work.p, 0, sizeof(int) * 4, st));
     S3D_CK(cudaEventRecord(ctx->ev[EV_SCALE], st));
 
-    // build_gpyr (sift.c:662-711)
-    float *ta = (float *) ctx->tmp_a.p, *tb = (float *) ctx->tmp_b.p;
-    {
-        Level &L = ctx->level(0, -1);
-        const double u[3] = {L.ux, L.uy, L.uz};
-        const uint64_t l0 = ctx->launches;
-        if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[0], st));
-        if (launch_blur(st, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
-                        ctx->d_scalar(0), nullptr, nullptr, nullptr, false, &ctx->launches))
-            return -1;
-        if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[1], st));
-        ctx->blur_launches[0] = (int) (ctx->launches - l0);
-    }
+    // build_gpyr (sift.c:662-711) + detect_extrema (sift.c:735-871), one octave per stream:
+    // octave o + 1 starts as soon as its seed level (2x decimation of level ds_level of octave
+    // o, fused into that blur's epilogue) exists, while octave o finishes its upper levels.
     const int ds_level = (nlev - 2) - 2 > -1 ? (nlev - 2) - 2 : -1;  // sift.c:696-697
     for (int o = 0; o < noct; o++) {
-        for (int s = 0; s < nlev - 1; s++) {
-            Level &P = ctx->level(o, s - 1);
+        cudaStream_t so = (o == 0 || ctx->serial) ? st : ctx->oct_stream[o];
+        float *ta, *tb;
+        if (o == 0) {
+            ta = (float *) ctx->tmp_a.p;
+            tb = (float *) ctx->tmp_b.p;
+        } else {
+            ta = (float *) ctx->tmp_side.p + ctx->side_off[o];
+            tb = ta + ((ctx->level(o, 0).nvox() + 63) & ~(size_t) 63);
+            if (so != st) S3D_CK(cudaStreamWaitEvent(so, ctx->ev_seed[o - 1], 0));
+        }
+        for (int s = (o == 0 ? -1 : 0); s < nlev - 1; s++) {
             Level &L = ctx->level(o, s);
-            const double u[3] = {P.ux, P.uy, P.uz};
-            // DoG level s-1 = G(s-1) - G(s); its max-abs is needed for keypoint levels only
-            float *slot = nullptr;
-            if (s - 1 >= 0 && s - 1 < kp) slot = ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (s - 1));
             const size_t li = (size_t) o * nlev + (s + 1);
             const uint64_t l0 = ctx->launches;
-            if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li], st));
+            if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li], so));
             // the level that seeds the next octave is decimated as it is produced
             float *ds_dst = (o != noct - 1 && s == ds_level) ? ctx->level(o + 1, -1).d : nullptr;
-            if (launch_blur(st, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
-                            nullptr, slot, P.d, ds_dst, false, &ctx->launches))
-                return -1;
-            if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], st));
+            int rc;
+            if (s == -1) {
+                const double u[3] = {L.ux, L.uy, L.uz};
+                rc = launch_blur(so, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
+                                 ctx->d_scalar(0), nullptr, nullptr, ds_dst, false, &ctx->launches);
+            } else {
+                Level &P = ctx->level(o, s - 1);
+                const double u[3] = {P.ux, P.uy, P.uz};
+                // DoG level s-1 = G(s-1) - G(s); its max-abs is needed for keypoint levels only
+                float *slot = nullptr;
+                if (s - 1 >= 0 && s - 1 < kp)
+                    slot = ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (s - 1));
+                rc = launch_blur(so, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
+                                 nullptr, slot, P.d, ds_dst, false, &ctx->launches);
+            }
+            if (rc) return -1;
+            if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], so));
             ctx->blur_launches[li] = (int) (ctx->launches - l0);
+            if (ds_dst != nullptr && so != st) S3D_CK(cudaEventRecord(ctx->ev_seed[o], so));
+            if (ds_dst != nullptr && so == st && !ctx->serial) S3D_CK(cudaEventRecord(ctx->ev_seed[o], st));
         }
-    }
-    S3D_CK(cudaEventRecord(ctx->ev[EV_PYR], st));
-
-    // detect_extrema (sift.c:735-871)
-    S3D_CK(cudaMemsetAsync(ctx->counts.p, 0, sizeof(int) * 64, st));
-    for (int o = 0; o < noct; o++) {
+        if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_PYR], st));
         const float *g[SIFT3D_CUDA_MAX_FILTERS + 1];
         for (int s = -1; s < nlev - 1; s++) g[s + 1] = ctx->level(o, s).d;
         Level &L = ctx->level(o, 0);
-        if (launch_extrema(st, g, kp, L.nx, L.ny, L.nz,
+        if (launch_extrema(so, g, kp, L.nx, L.ny, L.nz,
                            ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS), peak_thresh,
                            (Cand *) ctx->cand_raw.p + ctx->cand_base[o], ctx->cand_cap[o],
                            (int *) ctx->counts.p + o, &ctx->launches))
             return -1;
+        if (so != st) S3D_CK(cudaEventRecord(ctx->ev_done[o], so));
     }
+    if (!ctx->serial)
+        for (int o = 1; o < noct; o++) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_done[o], 0));
+    S3D_CK(cudaEventRecord(ctx->ev[EV_EXTREMA], st));
+
+    // scan order (o, s, z, y, x) and assign_orientations (sift.c:1109-1143): one launch each
+    // over all octaves, candidate counts read on the device
+    if (launch_order_all(st, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
+                         ctx->cand_base.data(), ctx->cand_cap.data(), noct,
+                         (const int *) ctx->counts.p, &ctx->launches))
+        return -1;
+    S3D_CK(cudaEventRecord(ctx->ev[EV_ORDER], st));
+    {
+        OrientPlan &H = *ctx->h_plan;
+        memset(&H, 0, sizeof(H));
+        H.noct = noct;
+        for (int o = 0; o < noct; o++) {
+            OctaveInfo &info = H.oct[o];
+            for (int s = 0; s < kp; s++) {
+                info.lvl[s] = ctx->level(o, s).d;
+                info.sd[s] = ctx->level(o, s).scale;
+            }
+            Level &L = ctx->level(o, 0);
+            info.o = o;
+            info.nx = L.nx; info.ny = L.ny; info.nz = L.nz;
+            info.ux = (float) L.ux; info.uy = (float) L.uy; info.uz = (float) L.uz;
+            H.base[o] = ctx->cand_base[o];
+            H.cap[o] = ctx->cand_cap[o];
+        }
+        S3D_CK(cudaMemcpyAsync(ctx->orient_plan.p, &H, sizeof(H), cudaMemcpyHostToDevice, st));
+    }
+    if (launch_orient_all(st, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
+                          (const int *) ctx->counts.p, (int *) ctx->work.p, corner_thresh,
+                          (sift3d_cuda_keypoint *) ctx->kps.p, &ctx->launches))
+        return -1;
     S3D_CK(cudaMemcpyAsync(ctx->h_counts, ctx->counts.p, sizeof(int) * noct,
                            cudaMemcpyDeviceToHost, st));
-    S3D_CK(cudaEventRecord(ctx->ev[EV_EXTREMA], st));
+    S3D_CK(cudaEventRecord(ctx->ev[EV_ORIENT], st));
     S3D_CK(cudaStreamSynchronize(st));
     int total = 0;
     for (int o = 0; o < noct; o++) {
@@ -375,34 +464,6 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         }
         total += ctx->h_counts[o];
     }
-
-    // scan order (o, s, z, y, x)
-    for (int o = 0; o < noct; o++)
-        if (launch_order(st, (Cand *) ctx->cand_raw.p + ctx->cand_base[o], ctx->h_counts[o],
-                         (Cand *) ctx->cand_sorted.p + ctx->cand_base[o], &ctx->launches))
-            return -1;
-    S3D_CK(cudaEventRecord(ctx->ev[EV_ORDER], st));
-
-    // assign_orientations (sift.c:1109-1143), compact output across octaves
-    int out_base = 0;
-    for (int o = 0; o < noct; o++) {
-        OctaveInfo info;
-        memset(&info, 0, sizeof(info));
-        for (int s = 0; s < kp; s++) {
-            info.lvl[s] = ctx->level(o, s).d;
-            info.sd[s] = ctx->level(o, s).scale;
-        }
-        Level &L = ctx->level(o, 0);
-        info.o = o;
-        info.nx = L.nx; info.ny = L.ny; info.nz = L.nz;
-        info.ux = (float) L.ux; info.uy = (float) L.uy; info.uz = (float) L.uz;
-        if (launch_orient(st, (Cand *) ctx->cand_sorted.p + ctx->cand_base[o], ctx->h_counts[o],
-                          info, corner_thresh, (sift3d_cuda_keypoint *) ctx->kps.p + out_base,
-                          &ctx->launches))
-            return -1;
-        out_base += ctx->h_counts[o];
-    }
-    S3D_CK(cudaEventRecord(ctx->ev[EV_ORIENT], st));
     ctx->total_candidates = total;
     ctx->have_pyramid = true;
     if (num_candidates) *num_candidates = total;
