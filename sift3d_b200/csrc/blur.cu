@@ -42,12 +42,35 @@ __device__ __forceinline__ float samp(const float *__restrict__ line, size_t str
 __device__ __forceinline__ float conv_point_generic(const float *__restrict__ line,
                                                     size_t stride, int p, int n,
                                                     const float *__restrict__ taps, int hw,
-                                                    float uf, int uhw, bool scale, float dv) {
+                                                    float uf, int uhw, bool scale, float dv,
+                                                    int sh = -1) {
     const int start = uhw;
     const int end = n - 2 - uhw;
     const int dim_end = n - 1;
     float acc = 0.0f;
-    if (p >= start && p <= end) {
+    if (sh >= 0 && p >= start && p <= end) {
+        // Interior pass with a dyadic unit factor 2^-sh: p - d*uf and the way back are exact,
+        // so tap d samples position p + (-d >> sh) with fraction ((-d) mod 2^sh) * 2^-sh --
+        // the same values the carried-coordinate loop below produces, without the
+        // float <-> int round trips. frac == 0 taps are the sample itself: 1*a + 0*b == a.
+        const float *__restrict__ q = line + (size_t) p * stride;
+        const ptrdiff_t st = (ptrdiff_t) stride;
+        for (int d = -hw; d <= hw; d++) {
+            const float tap = taps[d + hw];
+            const int off = (-d) >> sh;
+            const int fi = (-d) & ((1 << sh) - 1);
+            float a = q[(ptrdiff_t) off * st];
+            if (scale) a = __fdiv_rn(a, dv);
+            float sv = a;
+            if (fi != 0) {  // uniform across the block
+                float b = q[(ptrdiff_t) (off + 1) * st];
+                if (scale) b = __fdiv_rn(b, dv);
+                const float fr = __fmul_rn((float) fi, uf);
+                sv = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, fr), a), __fmul_rn(fr, b));
+            }
+            acc = __fadd_rn(acc, __fmul_rn(tap, sv));
+        }
+    } else if (p >= start && p <= end) {
         // interior pass: the coordinate is carried across taps (imutil.c:803-818)
         // The coordinate chain does not depend on the samples, so the taps are evaluated in
         // batches of 4: coordinates first, then the 8 loads together, then the in-order
@@ -103,7 +126,7 @@ __global__ void __launch_bounds__(256)
 blur_axis_generic_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny,
                          int nz, const float *__restrict__ taps, int hw, float uf, int uhw,
                          const float *__restrict__ divisor, const float *__restrict__ dog_prev,
-                         float *__restrict__ dogmax, float *__restrict__ ds_dst) {
+                         float *__restrict__ dogmax, float *__restrict__ ds_dst, int sh) {
     // 3-D launch (x in the block, rows and planes in the grid): no 64-bit div/mod per thread
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     const int y = blockIdx.y * blockDim.y + threadIdx.y;
@@ -118,7 +141,7 @@ blur_axis_generic_kernel(const float *__restrict__ src, float *__restrict__ dst,
         if (divisor != nullptr) dv = *divisor;
         const bool scale = dv != 0.0f;  // im_scale leaves an all-zero image alone (imutil.c:706)
         const float o = conv_point_generic(src + (idx - (size_t) p * stride), stride, p, n, taps, hw,
-                                           uf, uhw, scale, dv);
+                                           uf, uhw, scale, dv, sh);
         dst[idx] = o;
         if (EPI) {
             if (dogmax != nullptr) vmax = fabsf(__fsub_rn(dog_prev[idx], o));
@@ -190,6 +213,7 @@ absdiffmax_kernel(const float *__restrict__ a, const float *__restrict__ b, size
 }  // namespace s3d
 
 #include "blur_fused.cuh"
+#include "blur_fused_half.cuh"
 
 namespace s3d {
 
@@ -201,6 +225,10 @@ static inline AxisSpec axis_spec(int n, double unit, int hw) {
     a.n = n;
     a.uf = (float) (1.0 / unit);                 // imutil.c:754-755 (unit argument is 1.0)
     a.uhw = (int) ceilf((float) hw * a.uf);      // imutil.c:756-757
+    // dyadic unit factor 2^-sh on a line short enough that every coordinate is exact
+    a.sh = -1;
+    for (int k = 0; k <= 8; k++)
+        if (a.uf == ldexpf(1.0f, -k) && n < (1 << 20)) a.sh = k;
     return a;
 }
 
@@ -287,6 +315,67 @@ static int launch_fused(cudaStream_t st, FusedParams &P, int hw, int occ) {
     }
 }
 
+template <int HW, int TY>
+static int launch_half_t(cudaStream_t st, const FusedParams &P, int nzc) {
+    using C = HalfCfg<HW>;
+    constexpr int TROWS = TY + 2 * C::YH;
+    constexpr int TILE_FLOATS = TROWS * C::BW;
+    constexpr int TILE_STRIDE = (TILE_FLOATS + 31) / 32 * 32;
+    constexpr int NUR = 2 * TY + 2 * HW - 1;
+    constexpr size_t SMEM = (size_t) (kNB * TILE_STRIDE + 2 * TROWS * kFTX + 2 * NUR * kFTX) * 4 +
+                            kNB * 8 + (HW + 1) * 4 + 16;
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (enc == nullptr) return 1;
+    CUtensorMap tmap;
+    const cuuint64_t gdim[3] = {(cuuint64_t) P.nx, (cuuint64_t) P.ny, (cuuint64_t) P.nz};
+    const cuuint64_t gstr[2] = {(cuuint64_t) P.nx * 4, (cuuint64_t) P.nx * P.ny * 4};
+    const cuuint32_t box[3] = {(cuuint32_t) C::BW, (cuuint32_t) TROWS, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    if (enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *) P.src, gdim, gstr, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return 1;
+    static bool attr_set = false;
+    if (!attr_set) {
+        S3D_CK(cudaFuncSetAttribute(blur_fused_half_kernel<HW, TY>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int) SMEM));
+        attr_set = true;
+    }
+    dim3 grid((unsigned) ((P.nx + kFTX - 1) / kFTX), (unsigned) ((P.ny + TY - 1) / TY), (unsigned) nzc);
+    blur_fused_half_kernel<HW, TY><<<grid, 8 * TY, SMEM, st>>>(tmap, P);
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+// Spacing-1/2 fused kernel; same return convention and chunking rules as launch_fused, with
+// the z footprint uhw = ceil(hw / 2).
+template <int TY>
+static int launch_half(cudaStream_t st, FusedParams &P, int hw, int occ) {
+    const int uhw = (hw + 1) / 2;
+    const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
+    int nzc = (kNumSMs * occ) / tiles;
+    if (nzc < 1) nzc = 1;
+    int zc = (P.nz + nzc - 1) / nzc;
+    if (zc < uhw + 1) zc = uhw + 1;
+    nzc = (P.nz + zc - 1) / zc;
+    while (nzc > 1 && P.nz - (nzc - 1) * zc < uhw + 1) {
+        zc++;
+        nzc = (P.nz + zc - 1) / zc;
+    }
+    P.zchunk = zc;
+    switch (hw) {
+    case 1: return launch_half_t<1, TY>(st, P, nzc);
+    case 2: return launch_half_t<2, TY>(st, P, nzc);
+    case 3: return launch_half_t<3, TY>(st, P, nzc);
+    case 4: return launch_half_t<4, TY>(st, P, nzc);
+    case 5: return launch_half_t<5, TY>(st, P, nzc);
+    case 6: return launch_half_t<6, TY>(st, P, nzc);
+    case 7: return launch_half_t<7, TY>(st, P, nzc);
+    case 8: return launch_half_t<8, TY>(st, P, nzc);
+    default: return 1;
+    }
+}
+
 int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, float *tmp_b,
                 int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
                 const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
@@ -327,6 +416,30 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         }
     }
 
+    // Fused single-launch path for tap spacing 1/2 on every axis (octave 1).
+    if (!force_generic && symmetric && ax.uf == 0.5f && ay.uf == 0.5f && az.uf == 0.5f && hw >= 1 &&
+        hw <= 8 && d_divisor == nullptr && nx % 4 == 0 && nx >= kFTX && ny >= ty && nx < (1 << 20) &&
+        ny < (1 << 20) && nz < (1 << 20) && ny >= hw + 3 && nz >= hw + 3 &&
+        ((uintptr_t) src & 15) == 0 && (d_dogmax_slot == nullptr || dog_prev == src)) {
+        FusedParams P;
+        P.src = src;
+        P.dst = dst;
+        P.ds_dst = ds_dst;
+        P.dogmax = d_dogmax_slot;
+        P.divisor = nullptr;
+        P.nx = nx; P.ny = ny; P.nz = nz;
+        P.zchunk = nz;
+        for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];
+        for (int i = f.width; i < kMaxParamTaps; i++) P.taps.k[i] = 0.0f;
+        if (d_dogmax_slot != nullptr) S3D_CK(cudaMemsetAsync(d_dogmax_slot, 0, sizeof(float), st));
+        const int r = ty == 64 ? launch_half<64>(st, P, hw, 1) : launch_half<32>(st, P, hw, 2);
+        if (r < 0) return -1;
+        if (r == 0) {
+            if (launches) *launches += 1;
+            return 0;
+        }
+    }
+
     const bool want_max = d_dogmax_slot != nullptr && dog_prev != nullptr;
     if (want_max) S3D_CK(cudaMemsetAsync(d_dogmax_slot, 0, sizeof(float), st));
     int bx = 32;
@@ -334,12 +447,12 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
     const dim3 gblock((unsigned) bx, (unsigned) (256 / bx), 1);
     const dim3 ggrid((unsigned) ((nx + bx - 1) / bx), (unsigned) ((ny + gblock.y - 1) / gblock.y), (unsigned) nz);
     blur_axis_generic_kernel<0, false><<<ggrid, gblock, 0, st>>>(
-        src, tmp_a, nx, ny, nz, d_taps, hw, ax.uf, ax.uhw, d_divisor, nullptr, nullptr, nullptr);
+        src, tmp_a, nx, ny, nz, d_taps, hw, ax.uf, ax.uhw, d_divisor, nullptr, nullptr, nullptr, ax.sh);
     blur_axis_generic_kernel<1, false><<<ggrid, gblock, 0, st>>>(
-        tmp_a, tmp_b, nx, ny, nz, d_taps, hw, ay.uf, ay.uhw, nullptr, nullptr, nullptr, nullptr);
+        tmp_a, tmp_b, nx, ny, nz, d_taps, hw, ay.uf, ay.uhw, nullptr, nullptr, nullptr, nullptr, ay.sh);
     blur_axis_generic_kernel<2, true><<<ggrid, gblock, 0, st>>>(
         tmp_b, dst, nx, ny, nz, d_taps, hw, az.uf, az.uhw, nullptr, dog_prev,
-        want_max ? d_dogmax_slot : nullptr, ds_dst);
+        want_max ? d_dogmax_slot : nullptr, ds_dst, az.sh);
     if (launches) *launches += 3;
     S3D_CK(cudaGetLastError());
     return 0;

@@ -43,6 +43,7 @@ struct AxisSpec {
     int n;        // samples along the axis
     float uf;     // unit_factor = (float)(unit / units[dim])
     int uhw;      // (int) ceilf(half_width * unit_factor)
+    int sh;       // unit_factor == 2^-sh exactly (dyadic fast path), else -1
 };
 
 // Candidate extremum as written by the extrema kernel.

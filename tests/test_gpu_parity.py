@@ -70,6 +70,26 @@ def test_fused_blur_bit_exact(det, dims, sigma):
     assert parity.level_error(gen, want)[1] == 0
 
 
+@pytest.mark.parametrize("dims", [(64, 64, 40), (96, 70, 45), (36, 33, 50), (128, 64, 37),
+                                  (32, 32, 36), (128, 128, 128)])
+@pytest.mark.parametrize("sigma", [0.3, 0.5387, 0.9733, 1.2263, 1.5450, 1.9466, 2.2, 2.4525])
+def test_fused_half_blur_bit_exact(det, dims, sigma):
+    """The fused kernel for tap spacing 1/2 (octave 1: units (2,2,2), unit 1) ==
+    apply_Sep_FIR_filter bit for bit: half-widths 1..8 (odd and even), the -1/2 extrapolated
+    sample, mirrored and "-0.1" virtual samples on all six faces, shifted tiles, z chunks."""
+    ref = _ref()
+    nx, ny, nz = dims
+    rng = np.random.default_rng(int(sigma * 1000) + nx + 7)
+    vol = rng.standard_normal((nz, ny, nx)).astype(np.float32)
+    taps = _gauss_taps(sigma)
+    want = ref.ref_blur(vol, (2, 2, 2), taps)
+    got = det.blur(vol, (2, 2, 2), taps)
+    rel, nbits = parity.level_error(got, want)
+    assert nbits == 0, f"{nbits} voxels differ (max rel err {rel:.3g})"
+    gen = det.blur(vol, (2, 2, 2), taps, force_generic=True)
+    assert parity.level_error(gen, want)[1] == 0
+
+
 CASES = [
     # name, dims (nx, ny, nz), units, blobs, flags
     ("blobs_64", (64, 64, 64), (1.0, 1.0, 1.0), 64, 0),
