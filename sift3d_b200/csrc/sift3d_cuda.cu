@@ -268,8 +268,13 @@ int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
         for (int o = 1; o < noct; o++) {
             ctx->side_off[o] = side_total;
             side_total += 2 * ((ctx->level(o, 0).nvox() + 63) & ~(size_t) 63);
+            // higher priority than the octave-0 stream: the small octaves are the tail of the
+            // dependency chain, so their kernels go first whenever SMs free up
+            int prio_lo = 0, prio_hi = 0;
+            cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
             if (!ctx->oct_stream[o] &&
-                cudaStreamCreateWithFlags(&ctx->oct_stream[o], cudaStreamNonBlocking) != cudaSuccess) {
+                cudaStreamCreateWithPriority(&ctx->oct_stream[o], cudaStreamNonBlocking, prio_hi) !=
+                    cudaSuccess) {
                 S3D_ERR("sift3d_cuda_plan: cannot create a stream\n");
                 return -1;
             }
