@@ -265,12 +265,65 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
     float prev[4] = {0.f, 0.f, 0.f, 0.f};
     float vmax = 0.0f;
 
-    // which outputs this CTA stores: edge outputs belong to the tiles at the static edge
-    // positions (first / last), see xrow()
+    // ---- plane-invariant x-pass work of this thread: up to 2 items (tile row, 4-column
+    // group). Item k covers tile row ((tid + k*NT) >> 3) + ROT: the rotation hands the top
+    // tile's virtual rows (two source rows each) to threads that own a single item.
+    // offA = float offset of the source row in the tile, offB >= 0: result is
+    // lerp(row offB, row offA, frI) (the "- 0.1" right mirror, imutil.c:846-849).
+    constexpr int kItems = (NITEMS + NT - 1) / NT;
+    static_assert(kItems <= 2, "tile has at most 2 x-pass items per thread");
+    int offA[kItems], offB[kItems], offD[kItems];
+    float frI[kItems];
+    const int gg = tid & 7;
+#pragma unroll
+    for (int k = 0; k < kItems; k++) {
+        const int it = tid + k * NT;
+        int r = (it >> 3) + ROT;
+        if (r >= TROWS) r -= TROWS;
+        const int gy = y0 - HW + r;
+        int ra = r, rb = -1;
+        float fr = 0.0f;
+        if (gy < 0) {
+            ra = r - 2 * gy;  // mirror: row -gy
+        } else if (gy >= dey) {
+            const int m = gy - dey;  // virtual row dey + m; only the top tile's outputs use it
+            if (ytop) {
+                ra = r - 2 * m;
+                rb = r - 2 * m - 1;
+                fr = fry[m];
+            } else {
+                ra = -1;
+            }
+        }
+        if (it >= NITEMS) ra = -1;
+        offA[k] = ra >= 0 ? ra * BW : -1;
+        offB[k] = rb >= 0 ? rb * BW : -1;
+        offD[k] = r * kFTX + 4 * gg;
+        frI[k] = fr;
+    }
+
+    // ---- which outputs this thread stores: edge outputs belong to the tiles at the static
+    // edge positions (first / last), see xrow()
     const int x = x0 + lane;
     const bool xok = (xleft || x >= HW) && (xright || x + HW < dex);
     const int ybase = y0 + 4 * w;
+    unsigned smask = 0;
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const int y = ybase + c;
+        if (xok && (ybot || y >= HW) && (ytop || y + HW < dey)) smask |= 1u << c;
+    }
     const size_t plane_stride = (size_t) nx * ny;
+    const size_t col_off = (size_t) ybase * nx + (size_t) x;  // row c adds c * nx
+    // decimation targets: even z, even rows, even x
+    const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
+    unsigned dmask = 0;
+    if (P.ds_dst != nullptr && !(x & 1) && (x >> 1) < dnx) {
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+            if ((smask & (1u << c)) && !((ybase + c) & 1) && ((ybase + c) >> 1) < dny) dmask |= 1u << c;
+    }
+    const size_t ds_col = (size_t) (ybase >> 1) * dnx + (size_t) (x >> 1);
 
     for (int n = -1; n < N; n++) {
         // ---- x pass of stream element n + 1 into xf[(n + 1) & 1]
@@ -280,108 +333,87 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
             const float *tb = tile + b * TILE_STRIDE;
             float *xb = xf + (e & 1) * XF_FLOATS;
             mbar_wait(&mbar[b], (uint32_t) ((e / kNB) & 1));
-            // Items are rotated so that the top tile's virtual rows (two source rows each)
-            // fall to threads that process a single item.
-            for (int it = tid; it < NITEMS; it += NT) {
-                int r = (it >> 3) + ROT;
-                if (r >= TROWS) r -= TROWS;
-                const int gg = it & 7;
-                const int gy = y0 - HW + r;
-                int ra = r, rb = -1;  // source tile rows: result = ra, or lerp(rb, ra, fr)
-                float fr = 0.0f;
-                if (gy < 0) {
-                    ra = r - 2 * gy;  // mirror: row -gy
-                } else if (gy >= dey) {
-                    // virtual row dey + m = lerp(row dey-m-1, row dey-m); only stored
-                    // outputs of the top tile use it
-                    const int m = gy - dey;
-                    if (ytop) {
-                        ra = r - 2 * m;
-                        rb = r - 2 * m - 1;
-                        fr = fry[m];
-                    } else {
-                        ra = -1;
-                    }
+#pragma unroll
+            for (int k = 0; k < kItems; k++) {
+                if (offA[k] < 0) {
+                    if (tid + k * NT < NITEMS)
+                        *reinterpret_cast<float4 *>(xb + offD[k]) = make_float4(0.f, 0.f, 0.f, 0.f);
+                    continue;
                 }
-                float4 o = make_float4(0.f, 0.f, 0.f, 0.f), a = o;
-                if (ra >= 0) {
-#pragma unroll 1
-                    for (int rep = rb >= 0 ? 1 : 0; rep >= 0; rep--) {
-                        const float4 v = xrow<HW>(tb + (rep ? rb : ra) * BW, gg, xleft, xright, frx,
-                                                  scale, dv, P.taps);
-                        if (rep) a = v; else o = v;
-                    }
-                    if (rb >= 0)
-                        o = make_float4(lerp1(a.x, o.x, fr), lerp1(a.y, o.y, fr), lerp1(a.z, o.z, fr),
-                                        lerp1(a.w, o.w, fr));
+                float4 o = xrow<HW>(tb + offA[k], gg, xleft, xright, frx, scale, dv, P.taps);
+                if (offB[k] >= 0) {
+                    const float4 a = xrow<HW>(tb + offB[k], gg, xleft, xright, frx, scale, dv, P.taps);
+                    const float fr = frI[k];
+                    o = make_float4(lerp1(a.x, o.x, fr), lerp1(a.y, o.y, fr), lerp1(a.z, o.z, fr),
+                                    lerp1(a.w, o.w, fr));
                 }
-                *reinterpret_cast<float4 *>(xb + r * kFTX + 4 * gg) = o;
+                *reinterpret_cast<float4 *>(xb + offD[k]) = o;
             }
         }
         if (n >= 0) {
-        // ---- y pass: rows 4w .. 4w+3+2*HW of the x-filtered tile, column `lane`
-        const float *xb = xf + (n & 1) * XF_FLOATS + (4 * w) * kFTX + lane;
-        float in[NINY];
+            // ---- y pass: rows 4w .. 4w+3+2*HW of the x-filtered tile, column `lane`
+            const float *xb = xf + (n & 1) * XF_FLOATS + (4 * w) * kFTX + lane;
+            float in[NINY];
 #pragma unroll
-        for (int j = 0; j < NINY; j++) in[j] = xb[j * kFTX];
-        float yv[4];
+            for (int j = 0; j < NINY; j++) in[j] = xb[j * kFTX];
+            float yv[4];
 #pragma unroll
-        for (int c = 0; c < 4; c++) {
-            float a = 0.0f;
+            for (int c = 0; c < 4; c++) {
+                float a = 0.0f;
 #pragma unroll
-            for (int t = 0; t < 2 * HW + 1; t++)  // tap d = t - HW samples row y - d
-                a = __fadd_rn(a, __fmul_rn(P.taps.k[fold<HW>(t)], in[c + 2 * HW - t]));
-            yv[c] = a;
-        }
+                for (int t = 0; t < 2 * HW + 1; t++)  // tap d = t - HW samples row y - d
+                    a = __fadd_rn(a, __fmul_rn(P.taps.k[fold<HW>(t)], in[c + 2 * HW - t]));
+                yv[c] = a;
+            }
 
-        // ---- z pass
-        int q;
-        bool feed = true;
-        if (n < npro) {
-            const int m = HW + 1 - n;  // plane dez - m
-            q = dez + m;
-            if (n == 0) {
-                feed = false;
-            } else {
-                const float fr = right_frac(dez, m);
+            // ---- z pass
+            int q;
+            bool feed = true;
+            if (n < npro) {
+                const int m = HW + 1 - n;  // plane dez - m
+                q = dez + m;
+                if (n == 0) {
+                    feed = false;
 #pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    const float cur = yv[c];
-                    yv[c] = lerp1(prev[c], cur, fr);
-                    prev[c] = cur;
+                    for (int c = 0; c < 4; c++) prev[c] = yv[c];
+                } else {
+                    const float fr = right_frac(dez, m);
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        const float cur = yv[c];
+                        yv[c] = lerp1(prev[c], cur, fr);
+                        prev[c] = cur;
+                    }
                 }
+            } else {
+                q = qstart - (n - npro);
             }
-            if (n == 0) {
+            if (feed) {
+                float o[4];
 #pragma unroll
-                for (int c = 0; c < 4; c++) prev[c] = yv[c];
-            }
-        } else {
-            q = qstart - (n - npro);
-        }
-        if (feed) {
-            float o[4];
+                for (int c = 0; c < 4; c++) o[c] = zfeed<HW>(A[c], yv[c], P.taps);
+                const int z = q + HW;
+                if (z >= zb && z < ze) {
+                    float *dp = P.dst + ((size_t) z * plane_stride + col_off);
 #pragma unroll
-            for (int c = 0; c < 4; c++) o[c] = zfeed<HW>(A[c], yv[c], P.taps);
-            const int z = q + HW;
-            if (z >= zb && z < ze && xok) {
+                    for (int c = 0; c < 4; c++)
+                        if (smask & (1u << c)) dp[(size_t) c * nx] = o[c];
+                    if (P.dogmax != nullptr) {
+                        const float *sp = P.src + ((size_t) z * plane_stride + col_off);
 #pragma unroll
-                for (int c = 0; c < 4; c++) {
-                    const int y = ybase + c;
-                    const bool yok = (ybot || y >= HW) && (ytop || y + HW < dey);
-                    if (!yok) continue;
-                    const size_t idx = (size_t) z * plane_stride + (size_t) y * nx + (size_t) x;
-                    P.dst[idx] = o[c];
-                    if (P.dogmax != nullptr)
-                        vmax = fmaxf(vmax, fabsf(__fsub_rn(P.src[idx], o[c])));
-                    if (P.ds_dst != nullptr && !((z | y | x) & 1)) {
-                        const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
-                        const int hz = z >> 1, hy = y >> 1, hx = x >> 1;
-                        if (hz < dnz && hy < dny && hx < dnx)
-                            P.ds_dst[((size_t) hz * dny + hy) * dnx + hx] = o[c];
+                        for (int c = 0; c < 4; c++)
+                            if (smask & (1u << c))
+                                vmax = fmaxf(vmax, fabsf(__fsub_rn(sp[(size_t) c * nx], o[c])));
+                    }
+                    if (dmask != 0 && !(z & 1) && (z >> 1) < dnz) {
+                        float *qd = P.ds_dst + ((size_t) (z >> 1) * dny * dnx + ds_col);
+#pragma unroll
+                        for (int c = 0; c < 4; c++)
+                            if (dmask & (1u << c))
+                                qd[(size_t) (((ybase + c) >> 1) - (ybase >> 1)) * dnx] = o[c];
                     }
                 }
             }
-        }
         }  // n >= 0
         __syncthreads();
         // tile buffer (n+1) % kNB was consumed by xpass(n+1): refill it
