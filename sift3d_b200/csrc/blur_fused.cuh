@@ -325,14 +325,19 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
     }
     const size_t ds_col = (size_t) (ybase >> 1) * dnx + (size_t) (x >> 1);
 
+    int xb_buf = 0;          // tile buffer of the element the x pass consumes next
+    uint32_t xb_par = 0;     // and its mbarrier phase parity
     for (int n = -1; n < N; n++) {
         // ---- x pass of stream element n + 1 into xf[(n + 1) & 1]
         if (n + 1 < N) {
             const int e = n + 1;
-            const int b = e % kNB;
-            const float *tb = tile + b * TILE_STRIDE;
+            const float *tb = tile + xb_buf * TILE_STRIDE;
             float *xb = xf + (e & 1) * XF_FLOATS;
-            mbar_wait(&mbar[b], (uint32_t) ((e / kNB) & 1));
+            mbar_wait(&mbar[xb_buf], xb_par);
+            if (++xb_buf == kNB) {
+                xb_buf = 0;
+                xb_par ^= 1u;
+            }
 #pragma unroll
             for (int k = 0; k < kItems; k++) {
                 if (offA[k] < 0) {
@@ -394,23 +399,25 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
                 for (int c = 0; c < 4; c++) o[c] = zfeed<HW>(A[c], yv[c], P.taps);
                 const int z = q + HW;
                 if (z >= zb && z < ze) {
-                    float *dp = P.dst + ((size_t) z * plane_stride + col_off);
+                    // element offset of (z, ybase, x): 32-bit row steps keep the address math short
+                    const size_t base = (size_t) z * plane_stride + col_off;
+                    float *dp = P.dst + base;
 #pragma unroll
                     for (int c = 0; c < 4; c++)
-                        if (smask & (1u << c)) dp[(size_t) c * nx] = o[c];
+                        if (smask & (1u << c)) dp[c * nx] = o[c];
                     if (P.dogmax != nullptr) {
-                        const float *sp = P.src + ((size_t) z * plane_stride + col_off);
+                        const float *sp = P.src + base;
 #pragma unroll
                         for (int c = 0; c < 4; c++)
                             if (smask & (1u << c))
-                                vmax = fmaxf(vmax, fabsf(__fsub_rn(sp[(size_t) c * nx], o[c])));
+                                vmax = fmaxf(vmax, fabsf(__fsub_rn(sp[c * nx], o[c])));
                     }
                     if (dmask != 0 && !(z & 1) && (z >> 1) < dnz) {
                         float *qd = P.ds_dst + ((size_t) (z >> 1) * dny * dnx + ds_col);
 #pragma unroll
                         for (int c = 0; c < 4; c++)
                             if (dmask & (1u << c))
-                                qd[(size_t) (((ybase + c) >> 1) - (ybase >> 1)) * dnx] = o[c];
+                                qd[(((ybase + c) >> 1) - (ybase >> 1)) * dnx] = o[c];
                     }
                 }
             }

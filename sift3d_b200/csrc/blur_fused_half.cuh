@@ -225,21 +225,62 @@ blur_fused_half_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
     const bool xok = (xleft || x >= UHW) && (xright || x + UHW < dex);
     const int ybase = y0 + 4 * w;
     const size_t plane_stride = (size_t) nx * ny;
+    const size_t col_off = (size_t) ybase * nx + (size_t) x;
+    const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
+    unsigned dmask = 0;  // decimation targets: even z, even rows, even x
+    if (P.ds_dst != nullptr && xok && !(x & 1) && (x >> 1) < dnx) {
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+            if (!((ybase + c) & 1) && ((ybase + c) >> 1) < dny) dmask |= 1u << c;
+    }
+    const size_t ds_col = (size_t) (ybase >> 1) * dnx + (size_t) (x >> 1);
 
+    // ---- plane-invariant work descriptors of this thread
+    // x pass: items (tile row, 4-column group), rows inside the volume only
+    constexpr int kXItems = (TROWS * 8 + NT - 1) / NT;
+    int xoff[kXItems];  // float offset of the row in the tile, -1: nothing to do
+    const int gg = tid & 7;
+#pragma unroll
+    for (int k = 0; k < kXItems; k++) {
+        const int it = tid + k * NT;
+        const int r = it >> 3;
+        const int gy = y0 - YH + r;
+        xoff[k] = (it < TROWS * 8 && gy >= 0 && gy <= dey) ? r : -1;
+    }
+    // U build: items (U row, 4-column group): U[ur] = lerp(xf[lo], xf[lo + 1], fr) by the literal rule
+    constexpr int kUItems = (NUR * 8 + NT - 1) / NT;
+    int usrc[kUItems];  // float offset of row lo in xf (+ column group), -1: nothing to do
+    float ufr[kUItems];
+#pragma unroll
+    for (int k = 0; k < kUItems; k++) {
+        const int it = tid + k * NT;
+        const int ur = it >> 3;
+        int lo;
+        float fr;
+        half_rule(2 * y0 - HW + ur, dey, ny, lo, fr);
+        const int r = lo - (y0 - YH);  // tile row of sample lo
+        usrc[k] = (it < NUR * 8 && r >= 0 && r + 1 < TROWS) ? r * kFTX + 4 * gg : -1;
+        ufr[k] = fr;
+    }
+
+    int xb_buf = 0;
+    uint32_t xb_par = 0;
     for (int n = -2; n < N; n++) {
         // ---- stage 1: x pass of element n + 2 into xf[(n + 2) & 1] (rows inside the volume)
         if (n + 2 < N) {
             const int e = n + 2;
-            const int b = e % kNB;
-            const float *tb = tile + b * TILE_STRIDE;
+            const float *tb = tile + xb_buf * TILE_STRIDE;
             float *xb = xf + (e & 1) * XF_FLOATS;
-            mbar_wait(&mbar[b], (uint32_t) ((e / kNB) & 1));
-            for (int it = tid; it < TROWS * 8; it += NT) {
-                const int r = it >> 3, gg = it & 7;
-                const int gy = y0 - YH + r;
-                if (gy < 0 || gy > dey) continue;
-                const float4 o = xrow_half<HW>(tb + r * BW, gg, xleft, xright, frx, P.taps);
-                *reinterpret_cast<float4 *>(xb + r * kFTX + 4 * gg) = o;
+            mbar_wait(&mbar[xb_buf], xb_par);
+            if (++xb_buf == kNB) {
+                xb_buf = 0;
+                xb_par ^= 1u;
+            }
+#pragma unroll
+            for (int k = 0; k < kXItems; k++) {
+                if (xoff[k] < 0) continue;
+                const float4 o = xrow_half<HW>(tb + xoff[k] * BW, gg, xleft, xright, frx, P.taps);
+                *reinterpret_cast<float4 *>(xb + xoff[k] * kFTX + 4 * gg) = o;
             }
         }
         // ---- stage 2: U rows of element n + 1: U[ur] = S_y(u / 2), u = 2*y0 - HW + ur
@@ -247,20 +288,19 @@ blur_fused_half_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
             const int e = n + 1;
             const float *xb = xf + (e & 1) * XF_FLOATS;
             float *ub = ut + (e & 1) * U_FLOATS;
-            for (int it = tid; it < NUR * 8; it += NT) {
-                const int ur = it >> 3, gg = it & 7;
-                int lo;
-                float fr;
-                half_rule(2 * y0 - HW + ur, dey, ny, lo, fr);
-                const int r = lo - (y0 - YH);  // tile row of sample lo
+#pragma unroll
+            for (int k = 0; k < kUItems; k++) {
+                const int it = tid + k * NT;
+                if (it >= NUR * 8) continue;
                 float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (r >= 0 && r + 1 < TROWS) {
-                    const float4 a = *reinterpret_cast<const float4 *>(xb + r * kFTX + 4 * gg);
-                    const float4 c = *reinterpret_cast<const float4 *>(xb + (r + 1) * kFTX + 4 * gg);
+                if (usrc[k] >= 0) {
+                    const float4 a = *reinterpret_cast<const float4 *>(xb + usrc[k]);
+                    const float4 c = *reinterpret_cast<const float4 *>(xb + usrc[k] + kFTX);
+                    const float fr = ufr[k];
                     o = make_float4(lerp1(a.x, c.x, fr), lerp1(a.y, c.y, fr), lerp1(a.z, c.z, fr),
                                     lerp1(a.w, c.w, fr));
                 }
-                *reinterpret_cast<float4 *>(ub + ur * kFTX + 4 * gg) = o;
+                *reinterpret_cast<float4 *>(ub + (it >> 3) * kFTX + 4 * gg) = o;
             }
         }
         // ---- stage 3: y pass + z step of element n
@@ -312,19 +352,22 @@ blur_fused_half_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
                 }
                 const int z = p + C::JMAX;
                 if (z >= zb && z < ze && xok) {
+                    const size_t base = (size_t) z * plane_stride + col_off;
+                    float *dp = P.dst + base;
 #pragma unroll
-                    for (int c = 0; c < 4; c++) {
-                        const int y = ybase + c;
-                        const size_t idx = (size_t) z * plane_stride + (size_t) y * nx + (size_t) x;
-                        P.dst[idx] = o[c];
-                        if (P.dogmax != nullptr)
-                            vmax = fmaxf(vmax, fabsf(__fsub_rn(P.src[idx], o[c])));
-                        if (P.ds_dst != nullptr && !((z | y | x) & 1)) {
-                            const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
-                            const int hz = z >> 1, hy = y >> 1, hx = x >> 1;
-                            if (hz < dnz && hy < dny && hx < dnx)
-                                P.ds_dst[((size_t) hz * dny + hy) * dnx + hx] = o[c];
-                        }
+                    for (int c = 0; c < 4; c++) dp[c * nx] = o[c];
+                    if (P.dogmax != nullptr) {
+                        const float *sp = P.src + base;
+#pragma unroll
+                        for (int c = 0; c < 4; c++)
+                            vmax = fmaxf(vmax, fabsf(__fsub_rn(sp[c * nx], o[c])));
+                    }
+                    if (dmask != 0 && !(z & 1) && (z >> 1) < dnz) {
+                        float *qd = P.ds_dst + ((size_t) (z >> 1) * dny * dnx + ds_col);
+#pragma unroll
+                        for (int c = 0; c < 4; c++)
+                            if (dmask & (1u << c))
+                                qd[(((ybase + c) >> 1) - (ybase >> 1)) * dnx] = o[c];
                     }
                 }
             }
