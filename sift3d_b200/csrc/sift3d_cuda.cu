@@ -272,8 +272,10 @@ int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
             // dependency chain, so their kernels go first whenever SMs free up
             int prio_lo = 0, prio_hi = 0;
             cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+            // (numerically lower = higher priority) octave 1 above octave 0, the rest above both
+            const int prio = o == 1 ? (prio_hi + prio_lo) / 2 : prio_hi;
             if (!ctx->oct_stream[o] &&
-                cudaStreamCreateWithPriority(&ctx->oct_stream[o], cudaStreamNonBlocking, prio_hi) !=
+                cudaStreamCreateWithPriority(&ctx->oct_stream[o], cudaStreamNonBlocking, prio) !=
                     cudaSuccess) {
                 S3D_ERR("sift3d_cuda_plan: cannot create a stream\n");
                 return -1;
@@ -372,8 +374,9 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     // octave o + 1 starts as soon as its seed level (2x decimation of level ds_level of octave
     // o, fused into that blur's epilogue) exists, while octave o finishes its upper levels.
     const int ds_level = (nlev - 2) - 2 > -1 ? (nlev - 2) - 2 : -1;  // sift.c:696-697
-    for (int o = 0; o < noct; o++) {
-        cudaStream_t so = (o == 0 || ctx->serial) ? st : ctx->oct_stream[o];
+    auto stream_of = [&](int o) { return (o == 0 || ctx->serial) ? st : ctx->oct_stream[o]; };
+    auto run_level = [&](int o, int s) -> int {  // blur that produces level (o, s)
+        cudaStream_t so = stream_of(o);
         float *ta, *tb;
         if (o == 0) {
             ta = (float *) ctx->tmp_a.p;
@@ -381,36 +384,47 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         } else {
             ta = (float *) ctx->tmp_side.p + ctx->side_off[o];
             tb = ta + ((ctx->level(o, 0).nvox() + 63) & ~(size_t) 63);
-            if (so != st) S3D_CK(cudaStreamWaitEvent(so, ctx->ev_seed[o - 1], 0));
         }
-        for (int s = (o == 0 ? -1 : 0); s < nlev - 1; s++) {
-            Level &L = ctx->level(o, s);
-            const size_t li = (size_t) o * nlev + (s + 1);
-            const uint64_t l0 = ctx->launches;
-            if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li], so));
-            // the level that seeds the next octave is decimated as it is produced
-            float *ds_dst = (o != noct - 1 && s == ds_level) ? ctx->level(o + 1, -1).d : nullptr;
-            int rc;
-            if (s == -1) {
-                const double u[3] = {L.ux, L.uy, L.uz};
-                rc = launch_blur(so, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
-                                 ctx->d_scalar(0), nullptr, nullptr, ds_dst, false, &ctx->launches);
-            } else {
-                Level &P = ctx->level(o, s - 1);
-                const double u[3] = {P.ux, P.uy, P.uz};
-                // DoG level s-1 = G(s-1) - G(s); its max-abs is needed for keypoint levels only
-                float *slot = nullptr;
-                if (s - 1 >= 0 && s - 1 < kp)
-                    slot = ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (s - 1));
-                rc = launch_blur(so, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
-                                 nullptr, slot, P.d, ds_dst, false, &ctx->launches);
-            }
-            if (rc) return -1;
-            if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], so));
-            ctx->blur_launches[li] = (int) (ctx->launches - l0);
-            if (ds_dst != nullptr && so != st) S3D_CK(cudaEventRecord(ctx->ev_seed[o], so));
-            if (ds_dst != nullptr && so == st && !ctx->serial) S3D_CK(cudaEventRecord(ctx->ev_seed[o], st));
+        Level &L = ctx->level(o, s);
+        const size_t li = (size_t) o * nlev + (s + 1);
+        const uint64_t l0 = ctx->launches;
+        if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li], so));
+        // the level that seeds the next octave is decimated as it is produced
+        float *ds_dst = (o != noct - 1 && s == ds_level) ? ctx->level(o + 1, -1).d : nullptr;
+        int rc;
+        if (s == -1) {
+            const double u[3] = {L.ux, L.uy, L.uz};
+            rc = launch_blur(so, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
+                             ctx->d_scalar(0), nullptr, nullptr, ds_dst, false, &ctx->launches);
+        } else {
+            Level &P = ctx->level(o, s - 1);
+            const double u[3] = {P.ux, P.uy, P.uz};
+            // DoG level s-1 = G(s-1) - G(s); its max-abs is needed for keypoint levels only
+            float *slot = nullptr;
+            if (s - 1 >= 0 && s - 1 < kp) slot = ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (s - 1));
+            rc = launch_blur(so, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
+                             nullptr, slot, P.d, ds_dst, false, &ctx->launches);
         }
+        if (rc) return -1;
+        if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], so));
+        ctx->blur_launches[li] = (int) (ctx->launches - l0);
+        if (ds_dst != nullptr && !ctx->serial) S3D_CK(cudaEventRecord(ctx->ev_seed[o], so));
+        return 0;
+    };
+    // Phase A, the critical chain: every octave up to the level that seeds the next one.
+    for (int o = 0; o < noct; o++) {
+        if (o > 0 && !ctx->serial) S3D_CK(cudaStreamWaitEvent(stream_of(o), ctx->ev_seed[o - 1], 0));
+        for (int s = (o == 0 ? -1 : 0); s <= ds_level && s < nlev - 1; s++)
+            if (run_level(o, s)) return -1;
+    }
+    // Phase B, the bulk: remaining levels and the extrema scan of each octave. Octave 0's
+    // one-wave kernels would otherwise occupy every SM while octave 1 still has to produce
+    // the seed of octave 2, so octave 0 resumes only after octave 1's seed level.
+    if (noct > 1 && !ctx->serial) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_seed[noct > 2 ? 1 : 0], 0));
+    for (int o = 0; o < noct; o++) {
+        cudaStream_t so = stream_of(o);
+        for (int s = (ds_level + 1 > (o == 0 ? -1 : 0) ? ds_level + 1 : (o == 0 ? -1 : 0)); s < nlev - 1; s++)
+            if (run_level(o, s)) return -1;
         if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_PYR], st));
         const float *g[SIFT3D_CUDA_MAX_FILTERS + 1];
         for (int s = -1; s < nlev - 1; s++) g[s + 1] = ctx->level(o, s).d;
