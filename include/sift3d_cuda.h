@@ -104,6 +104,56 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *ima
                                           double peak_thresh, double corner_thresh,
                                           int *num_candidates);
 
+/* ---- one tall volume over several GPUs (z-slabs) -----------------------------------
+ * The reference has no multi-device path; this is the decomposition of the same
+ * build_gpyr / detect_extrema loops (sift.c:662-871) over z. Each rank plans a context
+ * for its slab of planes plus halo planes on the cut faces, and owns a contiguous plane
+ * range of every sharded octave. A blur only writes the owned planes of a level; the
+ * halo planes are then filled from the neighbours through `exchange`, so every rank holds
+ * exactly the values a single device would hold there. Octaves too small to shard are
+ * run as a separate small context fed by sift3d_cuda_detect_from_seed. */
+typedef struct {
+    int num_sharded_octaves;            /* octaves 0 .. K-1 of the plan run on this slab */
+    int own0[SIFT3D_CUDA_MAX_OCTAVES];  /* owned planes [own0[o], own1[o]) of octave o,  */
+    int own1[SIFT3D_CUDA_MAX_OCTAVES];  /* in slab-array coordinates; entry K describes  */
+                                        /* the seed level (K, -1) when the plan has it   */
+} sift3d_cuda_slab_desc;
+
+typedef struct {
+    void *user;
+    /* element-wise max of `count` device floats over all ranks, in place */
+    int (*reduce_max)(void *user, float *d_vals, int count);
+    /* level (o, s) (s = -1: the seed) now holds its owned planes [own0, own1): fill the
+     * other planes of the nx*ny*nz device array from the ranks that own them. Called
+     * with the context's stream drained. */
+    int (*exchange)(void *user, int o, int s, float *d_level, int nx, int ny, int nz,
+                    int own0, int own1);
+} sift3d_cuda_slab_callbacks;
+
+/* As sift3d_cuda_detect for a z-slab. Candidates are those of the owned planes, with
+ * slab-array coordinates; the caller offsets z and merges ranks in (o, s, rank) order. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_detect_slab(sift3d_cuda_ctx *ctx, const float *image,
+                                               int image_on_device, const double units[3],
+                                               double peak_thresh, double corner_thresh,
+                                               const sift3d_cuda_slab_desc *slab,
+                                               const sift3d_cuda_slab_callbacks *cb,
+                                               int *num_candidates);
+
+/* As sift3d_cuda_detect, but `seed` already is level -1 of this context's octave 0 (the
+ * 2x decimation sift.c:699-705 made in a larger pyramid): no im_scale, no first blur. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_detect_from_seed(sift3d_cuda_ctx *ctx, const float *seed,
+                                                    int seed_on_device, const double units[3],
+                                                    double peak_thresh, double corner_thresh,
+                                                    int *num_candidates);
+
+/* Octave number this context's octave 0 has in the pyramid it is a part of: reported in
+ * keypoint.o by detect and subtracted from it by describe. Default 0. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_set_base_octave(sift3d_cuda_ctx *ctx, int base_octave);
+
+/* Device address of level (o, s), s = -1 .. num_kp_levels + 1 (for the exchange
+ * callbacks and for feeding a seed to another context). NULL if out of range. */
+SIFT3D_CUDA_EXPORT float *sift3d_cuda_level_ptr(sift3d_cuda_ctx *ctx, int o, int s);
+
 /* All candidates in the reference's scan order (o, s, z, y, x), each with its
  * orientation result (valid flag + R). out has room for max entries. */
 SIFT3D_CUDA_EXPORT int sift3d_cuda_fetch_candidates(sift3d_cuda_ctx *ctx,

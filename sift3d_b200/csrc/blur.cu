@@ -126,11 +126,11 @@ __global__ void __launch_bounds__(256)
 blur_axis_generic_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny,
                          int nz, const float *__restrict__ taps, int hw, float uf, int uhw,
                          const float *__restrict__ divisor, const float *__restrict__ dog_prev,
-                         float *__restrict__ dogmax, float *__restrict__ ds_dst, int sh) {
+                         float *__restrict__ dogmax, float *__restrict__ ds_dst, int sh, int zoff) {
     // 3-D launch (x in the block, rows and planes in the grid): no 64-bit div/mod per thread
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     const int y = blockIdx.y * blockDim.y + threadIdx.y;
-    const int z = blockIdx.z;
+    const int z = blockIdx.z + zoff;
     const size_t idx = ((size_t) z * ny + (size_t) y) * nx + (size_t) x;
     float vmax = 0.0f;
     if (x < nx && y < ny) {
@@ -294,12 +294,13 @@ static int launch_fused(cudaStream_t st, FusedParams &P, int hw, int occ) {
     // must not reach below plane 0: every chunk holds at least hw + 1 outputs.
     int nzc = (kNumSMs * occ) / tiles;
     if (nzc < 1) nzc = 1;
-    int zc = (P.nz + nzc - 1) / nzc;
+    const int nzr = P.z1 - P.z0;  // planes to produce
+    int zc = (nzr + nzc - 1) / nzc;
     if (zc < hw + 1) zc = hw + 1;
-    nzc = (P.nz + zc - 1) / zc;
-    while (nzc > 1 && P.nz - (nzc - 1) * zc < hw + 1) {
+    nzc = (nzr + zc - 1) / zc;
+    while (nzc > 1 && nzr - (nzc - 1) * zc < hw + 1) {
         zc++;
-        nzc = (P.nz + zc - 1) / zc;
+        nzc = (nzr + zc - 1) / zc;
     }
     P.zchunk = zc;
     switch (hw) {
@@ -355,12 +356,13 @@ static int launch_half(cudaStream_t st, FusedParams &P, int hw, int occ) {
     const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
     int nzc = (kNumSMs * occ) / tiles;
     if (nzc < 1) nzc = 1;
-    int zc = (P.nz + nzc - 1) / nzc;
+    const int nzr = P.z1 - P.z0;  // planes to produce
+    int zc = (nzr + nzc - 1) / nzc;
     if (zc < uhw + 1) zc = uhw + 1;
-    nzc = (P.nz + zc - 1) / zc;
-    while (nzc > 1 && P.nz - (nzc - 1) * zc < uhw + 1) {
+    nzc = (nzr + zc - 1) / zc;
+    while (nzc > 1 && nzr - (nzc - 1) * zc < uhw + 1) {
         zc++;
-        nzc = (P.nz + zc - 1) / zc;
+        nzc = (nzr + zc - 1) / zc;
     }
     P.zchunk = zc;
     switch (hw) {
@@ -379,8 +381,20 @@ static int launch_half(cudaStream_t st, FusedParams &P, int hw, int occ) {
 int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, float *tmp_b,
                 int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
                 const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
-                const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches) {
+                const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches,
+                int z0, int z1) {
     const int hw = f.width / 2;
+    if (z1 < 0) {  // whole volume
+        z0 = 0;
+        z1 = nz;
+    }
+    // A cut face (z-slab mode) must keep the filter footprint inside the array: the planes
+    // beyond it are halo filled by the neighbouring rank, not a volume boundary.
+    if ((z0 > 0 && z0 < 2 * hw + 2) || (z1 < nz && nz - z1 < 2 * hw + 2) || z0 < 0 || z1 > nz || z0 >= z1) {
+        S3D_ERR("sift3d_cuda: z range [%d, %d) of %d planes leaves no room for a %d-tap halo\n", z0, z1,
+                nz, f.width);
+        return -1;
+    }
     const size_t total = (size_t) nx * ny * nz;
     const unsigned blocks = (unsigned) ((total + 255) / 256);
     const AxisSpec ax = axis_spec(nx, units[0], hw);
@@ -404,6 +418,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         P.dogmax = d_dogmax_slot;
         P.divisor = d_divisor;
         P.nx = nx; P.ny = ny; P.nz = nz;
+        P.z0 = z0; P.z1 = z1;
         P.zchunk = nz;
         for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];
         for (int i = f.width; i < kMaxParamTaps; i++) P.taps.k[i] = 0.0f;
@@ -428,6 +443,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         P.dogmax = d_dogmax_slot;
         P.divisor = nullptr;
         P.nx = nx; P.ny = ny; P.nz = nz;
+        P.z0 = z0; P.z1 = z1;
         P.zchunk = nz;
         for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];
         for (int i = f.width; i < kMaxParamTaps; i++) P.taps.k[i] = 0.0f;
@@ -445,14 +461,19 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
     int bx = 32;
     while (bx < nx && bx < 256) bx <<= 1;
     const dim3 gblock((unsigned) bx, (unsigned) (256 / bx), 1);
-    const dim3 ggrid((unsigned) ((nx + bx - 1) / bx), (unsigned) ((ny + gblock.y - 1) / gblock.y), (unsigned) nz);
-    blur_axis_generic_kernel<0, false><<<ggrid, gblock, 0, st>>>(
-        src, tmp_a, nx, ny, nz, d_taps, hw, ax.uf, ax.uhw, d_divisor, nullptr, nullptr, nullptr, ax.sh);
-    blur_axis_generic_kernel<1, false><<<ggrid, gblock, 0, st>>>(
-        tmp_a, tmp_b, nx, ny, nz, d_taps, hw, ay.uf, ay.uhw, nullptr, nullptr, nullptr, nullptr, ay.sh);
-    blur_axis_generic_kernel<2, true><<<ggrid, gblock, 0, st>>>(
+    // x and y passes cover the z range plus the z footprint of the last pass
+    const int zlo = z0 - az.uhw - 1 > 0 ? z0 - az.uhw - 1 : 0;
+    const int zhi = z1 + az.uhw + 1 < nz ? z1 + az.uhw + 1 : nz;
+    const dim3 ggrid_xy((unsigned) ((nx + bx - 1) / bx), (unsigned) ((ny + gblock.y - 1) / gblock.y),
+                        (unsigned) (zhi - zlo));
+    const dim3 ggrid_z(ggrid_xy.x, ggrid_xy.y, (unsigned) (z1 - z0));
+    blur_axis_generic_kernel<0, false><<<ggrid_xy, gblock, 0, st>>>(
+        src, tmp_a, nx, ny, nz, d_taps, hw, ax.uf, ax.uhw, d_divisor, nullptr, nullptr, nullptr, ax.sh, zlo);
+    blur_axis_generic_kernel<1, false><<<ggrid_xy, gblock, 0, st>>>(
+        tmp_a, tmp_b, nx, ny, nz, d_taps, hw, ay.uf, ay.uhw, nullptr, nullptr, nullptr, nullptr, ay.sh, zlo);
+    blur_axis_generic_kernel<2, true><<<ggrid_z, gblock, 0, st>>>(
         tmp_b, dst, nx, ny, nz, d_taps, hw, az.uf, az.uhw, nullptr, dog_prev,
-        want_max ? d_dogmax_slot : nullptr, ds_dst, az.sh);
+        want_max ? d_dogmax_slot : nullptr, ds_dst, az.sh, z0);
     if (launches) *launches += 3;
     S3D_CK(cudaGetLastError());
     return 0;

@@ -82,6 +82,7 @@ struct FusedParams {
     float *dogmax;         // slot for max|src - dst| or nullptr
     const float *divisor;  // im_scale divisor applied to src on load, or nullptr
     int nx, ny, nz;
+    int z0, z1;            // output planes [z0, z1)
     int zchunk;            // outputs per z-chunk
     TapsParam taps;        // taps in the parameter bank
 };
@@ -217,8 +218,8 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
     const bool xleft = x0 == 0, xright = x0 == nx - kFTX;
     const bool ybot = y0 == 0, ytop = y0 == ny - TY;
     const int dex = nx - 1, dey = ny - 1, dez = nz - 1;
-    const int zb = blockIdx.z * P.zchunk;
-    const int ze = min(zb + P.zchunk, nz);
+    const int zb = P.z0 + blockIdx.z * P.zchunk;  // outputs [P.z0, P.z1): the whole volume, or the
+    const int ze = min(zb + P.zchunk, P.z1);       // planes this rank owns in z-slab mode
     const bool top = ze == nz;
 
     // Stream of fed positions q (z_out = q + HW). Top chunk: a prologue walks planes

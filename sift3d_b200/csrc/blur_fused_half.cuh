@@ -173,8 +173,8 @@ blur_fused_half_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
     const int y0 = min((int) blockIdx.y * TY, ny - TY);
     const bool xleft = x0 == 0, xright = x0 == nx - kFTX;
     const int dex = nx - 1, dey = ny - 1, dez = nz - 1;
-    const int zb = blockIdx.z * P.zchunk;
-    const int ze = min(zb + P.zchunk, nz);
+    const int zb = P.z0 + blockIdx.z * P.zchunk;  // outputs [P.z0, P.z1): the whole volume, or the
+    const int ze = min(zb + P.zchunk, P.z1);       // planes this rank owns in z-slab mode
     const bool top = ze == nz;
 
     // Stream of plane loads, each followed by one plane step p (feeds U[2p+1], U[2p]):

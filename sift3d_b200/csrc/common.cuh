@@ -59,7 +59,8 @@ struct Cand {
 int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, float *tmp_b,
                 int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
                 const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
-                const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches);
+                const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches,
+                int z0 = 0, int z1 = -1);  // output planes [z0, z1); z1 < 0: the whole volume
 int launch_downsample(cudaStream_t st, const float *src, float *dst, int snx, int sny, int snz,
                       uint64_t *launches);
 int launch_absmax(cudaStream_t st, const float *src, size_t n, float *d_out, uint64_t *launches);
@@ -69,7 +70,7 @@ int launch_absdiffmax(cudaStream_t st, const float *a, const float *b, size_t n,
 // extrema.cu
 int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, int nx, int ny,
                    int nz, const float *d_dogmax, double peak_thresh, Cand *d_cand, int cap,
-                   int *d_count, uint64_t *launches);
+                   int *d_count, uint64_t *launches, int z0 = 0, int z1 = -1);  // planes [z0, z1)
 // all octaves in one launch; counts stay on the device
 int launch_order_all(cudaStream_t st, const Cand *d_raw, Cand *d_sorted, const int *base,
                      const int *cap, int noct, const int *d_counts, uint64_t *launches);

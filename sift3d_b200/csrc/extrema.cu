@@ -17,6 +17,7 @@ struct ExtremaParams {
     float thresh[SIFT3D_CUDA_MAX_FILTERS];        // per keypoint level
     int num_kp_levels;
     int nx, ny, nz;
+    int z0, z1;  // planes [z0, z1) are scanned (z-slab mode: the planes this rank owns)
 };
 
 __global__ void __launch_bounds__(256)
@@ -25,8 +26,8 @@ extrema_kernel(const ExtremaParams P, const float *__restrict__ dogmax, float pe
     const int nx = P.nx, ny = P.ny, nz = P.nz;
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     const int y = blockIdx.y;
-    const int z = blockIdx.z;
-    const bool inside = x >= 1 && x <= nx - 2 && y >= 1 && y <= ny - 2 && z >= 1 && z <= nz - 2;
+    const int z = blockIdx.z + P.z0;
+    const bool inside = x >= 1 && x <= nx - 2 && y >= 1 && y <= ny - 2 && z >= 1 && z <= nz - 2 && z < P.z1;
     const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
     const size_t idx = (size_t) z * zs + (size_t) y * ys + x;
     const unsigned lane = threadIdx.x & 31u;
@@ -92,8 +93,8 @@ extrema_vec4_kernel(const ExtremaParams P, const float *__restrict__ dogmax, dou
     const int nx4 = nx >> 2;
     const int x4 = blockIdx.x * blockDim.x + threadIdx.x;
     const int y = blockIdx.y * blockDim.y + threadIdx.y;
-    const int z = blockIdx.z;
-    const bool row_ok = x4 < nx4 && y >= 1 && y <= ny - 2 && z >= 1 && z <= nz - 2;
+    const int z = blockIdx.z + P.z0;
+    const bool row_ok = x4 < nx4 && y >= 1 && y <= ny - 2 && z >= 1 && z <= nz - 2 && z < P.z1;
     const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
     const size_t idx0 = (size_t) z * zs + (size_t) y * ys + (size_t) x4 * 4;
     const unsigned lane = (threadIdx.y * blockDim.x + threadIdx.x) & 31u;
@@ -199,13 +200,19 @@ order_all_kernel(const Cand *__restrict__ raw, Cand *__restrict__ sorted, const 
 
 int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, int nx, int ny,
                    int nz, const float *d_dogmax, double peak_thresh, Cand *d_cand, int cap,
-                   int *d_count, uint64_t *launches) {
+                   int *d_count, uint64_t *launches, int z0, int z1) {
+    if (z1 < 0) {
+        z0 = 0;
+        z1 = nz;
+    }
     ExtremaParams P;
     for (int i = 0; i < num_kp_levels + 3; i++) P.g[i] = g[i];
     P.num_kp_levels = num_kp_levels;
     P.nx = nx;
     P.ny = ny;
     P.nz = nz;
+    P.z0 = z0;
+    P.z1 = z1;
     bool aligned = nx % 4 == 0;
     for (int i = 0; i < num_kp_levels + 3; i++) aligned = aligned && ((uintptr_t) g[i] & 15) == 0;
     if (aligned && num_kp_levels >= 1 && num_kp_levels <= 4) {
@@ -213,7 +220,7 @@ int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, in
         int bx = 1;
         while (bx < nx4 && bx < 64) bx <<= 1;  // power of two <= 64 so that warps stay row aligned
         dim3 block((unsigned) bx, (unsigned) (256 / bx), 1);
-        dim3 grid((unsigned) ((nx4 + bx - 1) / bx), (unsigned) ((ny + block.y - 1) / block.y), (unsigned) nz);
+        dim3 grid((unsigned) ((nx4 + bx - 1) / bx), (unsigned) ((ny + block.y - 1) / block.y), (unsigned) (z1 - z0));
         switch (num_kp_levels) {
         case 1: extrema_vec4_kernel<1><<<grid, block, 0, st>>>(P, d_dogmax, peak_thresh, d_cand, cap, d_count); break;
         case 2: extrema_vec4_kernel<2><<<grid, block, 0, st>>>(P, d_dogmax, peak_thresh, d_cand, cap, d_count); break;
@@ -222,7 +229,7 @@ int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, in
         }
     } else {
         dim3 block(128, 1, 1);
-        dim3 grid((unsigned) ((nx + 127) / 128), (unsigned) ny, (unsigned) nz);
+        dim3 grid((unsigned) ((nx + 127) / 128), (unsigned) ny, (unsigned) (z1 - z0));
         extrema_kernel<<<grid, block, 0, st>>>(P, d_dogmax, 0.f, peak_thresh, d_cand, cap, d_count);
     }
     if (launches) *launches += 1;

@@ -65,6 +65,7 @@ struct sift3d_cuda_ctx {
     OrientPlan *h_plan = nullptr;       // pinned staging copy
     DevBuf work;                        // work counter of the persistent orientation kernel
     DevBuf taps;                        // (1 + filters) * SIFT3D_CUDA_MAX_TAPS floats
+    int base_octave = 0;                // octave number of this context's octave 0
     DevBuf scalars;                     // [0] image max-abs; [1 + o*MAX_FILTERS + s] DoG max
     DevBuf cand_raw, cand_sorted;       // Cand regions, one per octave
     DevBuf counts;                      // int per octave
@@ -330,9 +331,18 @@ int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
     return 0;
 }
 
-int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_device,
+// The whole detection pipeline. Three ways in:
+//   * plain: image -> all octaves (sift3d_cuda_detect);
+//   * seed:  `image` is level -1 of this context's octave 0, already blurred and decimated
+//            by a bigger pyramid (sift3d_cuda_detect_from_seed): no im_scale, no first blur;
+//   * slab:  this context holds a z-slab (+ halo planes) of a taller volume
+//            (sift3d_cuda_detect_slab): octaves 0 .. slab->num_sharded_octaves-1 produce only
+//            the planes this rank owns, the halo planes of every level are filled by the
+//            caller's exchange callback and the global max reductions by its reduce callback.
+static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_device,
                        const double units[3], double peak_thresh, double corner_thresh,
-                       int *num_candidates) {
+                       int *num_candidates, bool from_seed, const sift3d_cuda_slab_desc *slab,
+                       const sift3d_cuda_slab_callbacks *cb) {
     if (!ctx || !ctx->planned || !image || !units) {
         S3D_ERR("sift3d_cuda_detect: context not planned or NULL argument\n");
         return -1;
@@ -340,14 +350,39 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     if (set_device(ctx)) return -1;
     cudaStream_t st = ctx->stream;
     const sift3d_cuda_plan_desc &D = ctx->desc;
-    const int nlev = ctx->nlev, noct = D.num_octaves, kp = D.num_kp_levels;
+    const int nlev = ctx->nlev, kp = D.num_kp_levels;
+    const int noct_plan = D.num_octaves;
+    // octaves processed by this call
+    const int noct = slab ? slab->num_sharded_octaves : noct_plan;
     const size_t n0 = (size_t) D.nx * D.ny * D.nz;
     ctx->have_pyramid = false;
+    if (slab) {
+        if (!cb || !cb->reduce_max || !cb->exchange || noct < 1 || noct > noct_plan) {
+            S3D_ERR("sift3d_cuda_detect_slab: bad slab description\n");
+            return -1;
+        }
+        for (int o = 0; o < noct_plan && o <= noct; o++) {
+            const Level &L = ctx->level(o, 0);
+            if (slab->own0[o] < 0 || slab->own1[o] > L.nz || slab->own0[o] >= slab->own1[o]) {
+                S3D_ERR("sift3d_cuda_detect_slab: bad owned range of octave %d\n", o);
+                return -1;
+            }
+        }
+    }
+    const bool serial = ctx->serial || slab != nullptr;
+    // planes [zr0(o), zr1(o)) of octave o are produced / scanned
+    auto zr0 = [&](int o) { return slab ? slab->own0[o] : 0; };
+    auto zr1 = [&](int o) { return slab ? slab->own1[o] : ctx->level(o, 0).nz; };
+    // hand the stream to the caller's collective (host callbacks, so the stream is drained)
+    auto host_sync = [&]() -> int {
+        S3D_CK(cudaStreamSynchronize(st));
+        return 0;
+    };
 
     // Units: octave 0 takes the units of this image (apply_Sep_FIR_filter copies them from
     // the source, imutil.c:1145); octaves >= 1 keep what resize_Pyramid assigned when the
     // dims last changed, doubled per octave (imutil.c:1545-1548, sift.c:651-656).
-    for (int o = 0; o < noct; o++)
+    for (int o = 0; o < noct_plan; o++)
         for (int s = -1; s < nlev - 1; s++) {
             Level &L = ctx->level(o, s);
             const double *u = o == 0 ? units : D.units;
@@ -358,14 +393,28 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
 
     S3D_CK(cudaEventRecord(ctx->ev[EV_START], st));
     const float *d_in = image;
-    if (!image_on_device) {
+    if (from_seed) {
+        // level -1 of octave 0 is given (sift.c:694-705 produced it in the bigger pyramid)
+        S3D_CK(cudaMemcpyAsync(ctx->level(0, -1).d, image, n0 * sizeof(float),
+                               image_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+    } else if (!image_on_device) {
         S3D_CK(cudaMemcpyAsync(ctx->input.p, image, n0 * sizeof(float), cudaMemcpyHostToDevice, st));
         d_in = (const float *) ctx->input.p;
     }
     S3D_CK(cudaEventRecord(ctx->ev[EV_H2D], st));
 
     // im_scale: max |v| (imutil.c:681-695); the division is applied on load by the first blur.
-    if (launch_absmax(st, d_in, n0, ctx->d_scalar(0), &ctx->launches)) return -1;
+    if (slab) S3D_CK(cudaMemsetAsync(ctx->scalars.p, 0, ctx->scalars.bytes, st));
+    if (!from_seed) {
+        const size_t plane = (size_t) D.nx * D.ny;
+        if (launch_absmax(st, d_in + (size_t) zr0(0) * plane, (size_t) (zr1(0) - zr0(0)) * plane,
+                          ctx->d_scalar(0), &ctx->launches))
+            return -1;
+        if (slab) {  // the maximum is over the whole volume
+            if (host_sync()) return -1;
+            if (cb->reduce_max(cb->user, ctx->d_scalar(0), 1)) return -1;
+        }
+    }
     S3D_CK(cudaMemsetAsync(ctx->counts.p, 0, sizeof(int) * 64, st));
     S3D_CK(cudaMemsetAsync(ctx->work.p, 0, sizeof(int) * 4, st));
     S3D_CK(cudaEventRecord(ctx->ev[EV_SCALE], st));
@@ -374,7 +423,7 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     // octave o + 1 starts as soon as its seed level (2x decimation of level ds_level of octave
     // o, fused into that blur's epilogue) exists, while octave o finishes its upper levels.
     const int ds_level = (nlev - 2) - 2 > -1 ? (nlev - 2) - 2 : -1;  // sift.c:696-697
-    auto stream_of = [&](int o) { return (o == 0 || ctx->serial) ? st : ctx->oct_stream[o]; };
+    auto stream_of = [&](int o) { return (o == 0 || serial) ? st : ctx->oct_stream[o]; };
     auto run_level = [&](int o, int s) -> int {  // blur that produces level (o, s)
         cudaStream_t so = stream_of(o);
         float *ta, *tb;
@@ -390,12 +439,13 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         const uint64_t l0 = ctx->launches;
         if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li], so));
         // the level that seeds the next octave is decimated as it is produced
-        float *ds_dst = (o != noct - 1 && s == ds_level) ? ctx->level(o + 1, -1).d : nullptr;
+        float *ds_dst = (o != noct_plan - 1 && s == ds_level) ? ctx->level(o + 1, -1).d : nullptr;
         int rc;
         if (s == -1) {
             const double u[3] = {L.ux, L.uy, L.uz};
             rc = launch_blur(so, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
-                             ctx->d_scalar(0), nullptr, nullptr, ds_dst, false, &ctx->launches);
+                             ctx->d_scalar(0), nullptr, nullptr, ds_dst, false, &ctx->launches,
+                             zr0(o), zr1(o));
         } else {
             Level &P = ctx->level(o, s - 1);
             const double u[3] = {P.ux, P.uy, P.uz};
@@ -403,40 +453,60 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             float *slot = nullptr;
             if (s - 1 >= 0 && s - 1 < kp) slot = ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (s - 1));
             rc = launch_blur(so, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
-                             nullptr, slot, P.d, ds_dst, false, &ctx->launches);
+                             nullptr, slot, P.d, ds_dst, false, &ctx->launches, zr0(o), zr1(o));
         }
         if (rc) return -1;
         if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], so));
         ctx->blur_launches[li] = (int) (ctx->launches - l0);
-        if (ds_dst != nullptr && !ctx->serial) S3D_CK(cudaEventRecord(ctx->ev_seed[o], so));
+        if (ds_dst != nullptr && !serial) S3D_CK(cudaEventRecord(ctx->ev_seed[o], so));
+        if (slab) {
+            // halo planes of the new level (and of the seed it decimated into) come from the
+            // neighbouring ranks, which own them
+            if (host_sync()) return -1;
+            if (cb->exchange(cb->user, o, s, L.d, L.nx, L.ny, L.nz, zr0(o), zr1(o))) return -1;
+            if (ds_dst != nullptr) {
+                const Level &N = ctx->level(o + 1, -1);
+                if (cb->exchange(cb->user, o + 1, -1, N.d, N.nx, N.ny, N.nz, zr0(o + 1), zr1(o + 1)))
+                    return -1;
+            }
+        }
         return 0;
     };
     // Phase A, the critical chain: every octave up to the level that seeds the next one.
     for (int o = 0; o < noct; o++) {
-        if (o > 0 && !ctx->serial) S3D_CK(cudaStreamWaitEvent(stream_of(o), ctx->ev_seed[o - 1], 0));
-        for (int s = (o == 0 ? -1 : 0); s <= ds_level && s < nlev - 1; s++)
+        if (o > 0 && !serial) S3D_CK(cudaStreamWaitEvent(stream_of(o), ctx->ev_seed[o - 1], 0));
+        for (int s = (o == 0 && !from_seed ? -1 : 0); s <= ds_level && s < nlev - 1; s++)
             if (run_level(o, s)) return -1;
     }
     // Phase B, the bulk: remaining levels and the extrema scan of each octave. Octave 0's
     // one-wave kernels would otherwise occupy every SM while octave 1 still has to produce
     // the seed of octave 2, so octave 0 resumes only after octave 1's seed level.
-    if (noct > 1 && !ctx->serial) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_seed[noct > 2 ? 1 : 0], 0));
+    if (noct > 1 && !serial) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_seed[noct > 2 ? 1 : 0], 0));
     for (int o = 0; o < noct; o++) {
-        cudaStream_t so = stream_of(o);
-        for (int s = (ds_level + 1 > (o == 0 ? -1 : 0) ? ds_level + 1 : (o == 0 ? -1 : 0)); s < nlev - 1; s++)
+        const int sfirst = (o == 0 && !from_seed) ? -1 : 0;
+        for (int s = (ds_level + 1 > sfirst ? ds_level + 1 : sfirst); s < nlev - 1; s++)
             if (run_level(o, s)) return -1;
         if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_PYR], st));
+    }
+    if (slab) {  // DoG maxima are over whole levels
+        if (host_sync()) return -1;
+        if (cb->reduce_max(cb->user, (float *) ctx->scalars.p,
+                           (int) (ctx->scalars.bytes / sizeof(float))))
+            return -1;
+    }
+    for (int o = 0; o < noct; o++) {
+        cudaStream_t so = stream_of(o);
         const float *g[SIFT3D_CUDA_MAX_FILTERS + 1];
         for (int s = -1; s < nlev - 1; s++) g[s + 1] = ctx->level(o, s).d;
         Level &L = ctx->level(o, 0);
         if (launch_extrema(so, g, kp, L.nx, L.ny, L.nz,
                            ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS), peak_thresh,
                            (Cand *) ctx->cand_raw.p + ctx->cand_base[o], ctx->cand_cap[o],
-                           (int *) ctx->counts.p + o, &ctx->launches))
+                           (int *) ctx->counts.p + o, &ctx->launches, zr0(o), zr1(o)))
             return -1;
         if (so != st) S3D_CK(cudaEventRecord(ctx->ev_done[o], so));
     }
-    if (!ctx->serial)
+    if (!serial)
         for (int o = 1; o < noct; o++) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_done[o], 0));
     S3D_CK(cudaEventRecord(ctx->ev[EV_EXTREMA], st));
 
@@ -458,7 +528,7 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
                 info.sd[s] = ctx->level(o, s).scale;
             }
             Level &L = ctx->level(o, 0);
-            info.o = o;
+            info.o = o + ctx->base_octave;
             info.nx = L.nx; info.ny = L.ny; info.nz = L.nz;
             info.ux = (float) L.ux; info.uy = (float) L.uy; info.uz = (float) L.uz;
             H.base[o] = ctx->cand_base[o];
@@ -487,6 +557,45 @@ int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     ctx->have_pyramid = true;
     if (num_candidates) *num_candidates = total;
     return 0;
+}
+
+int sift3d_cuda_detect(sift3d_cuda_ctx *ctx, const float *image, int image_on_device,
+                       const double units[3], double peak_thresh, double corner_thresh,
+                       int *num_candidates) {
+    return detect_impl(ctx, image, image_on_device, units, peak_thresh, corner_thresh,
+                       num_candidates, false, nullptr, nullptr);
+}
+
+int sift3d_cuda_detect_slab(sift3d_cuda_ctx *ctx, const float *image, int image_on_device,
+                            const double units[3], double peak_thresh, double corner_thresh,
+                            const sift3d_cuda_slab_desc *slab,
+                            const sift3d_cuda_slab_callbacks *cb, int *num_candidates) {
+    if (!slab || !cb) {
+        S3D_ERR("sift3d_cuda_detect_slab: NULL slab description\n");
+        return -1;
+    }
+    return detect_impl(ctx, image, image_on_device, units, peak_thresh, corner_thresh,
+                       num_candidates, false, slab, cb);
+}
+
+int sift3d_cuda_detect_from_seed(sift3d_cuda_ctx *ctx, const float *seed, int seed_on_device,
+                                 const double units[3], double peak_thresh,
+                                 double corner_thresh, int *num_candidates) {
+    return detect_impl(ctx, seed, seed_on_device, units, peak_thresh, corner_thresh,
+                       num_candidates, true, nullptr, nullptr);
+}
+
+int sift3d_cuda_set_base_octave(sift3d_cuda_ctx *ctx, int base_octave) {
+    if (!ctx || base_octave < 0) return -1;
+    ctx->base_octave = base_octave;
+    return 0;
+}
+
+float *sift3d_cuda_level_ptr(sift3d_cuda_ctx *ctx, int o, int s) {
+    if (!ctx || !ctx->planned || o < 0 || o >= ctx->desc.num_octaves || s < -1 ||
+        s > ctx->nlev - 2)
+        return nullptr;
+    return ctx->level(o, s).d;
 }
 
 int sift3d_cuda_fetch_candidates(sift3d_cuda_ctx *ctx, sift3d_cuda_keypoint *out, int max) {
@@ -529,12 +638,13 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
     for (int i = 0; i < num; i++) {
         const sift3d_cuda_keypoint &k = keys[i];
         // any Gaussian level may be addressed (the reference indexes gpyr by key->o, key->s)
-        if (k.o < 0 || k.o >= noct || k.s < -1 || k.s > kp + 1) {
+        const int ko = k.o - ctx->base_octave;
+        if (ko < 0 || ko >= noct || k.s < -1 || k.s > kp + 1) {
             S3D_ERR("sift3d_cuda_describe: keypoint %d has invalid octave/level (%d, %d)\n", i,
                     k.o, k.s);
             return -1;
         }
-        const Level &L = ctx->level(k.o, k.s);
+        const Level &L = ctx->level(ko, k.s);
         DescJob &J = jobs[(size_t) i];
         J.img = L.d;
         J.nx = L.nx; J.ny = L.ny; J.nz = L.nz;
