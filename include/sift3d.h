@@ -139,6 +139,15 @@ SIFT3D_EXPORT int sift3d_image_make_resident(sift3d_image *, int device);
  * $SIFT3D_CUDA_DEVICE or device 0). */
 SIFT3D_EXPORT sift3d_detector *sift3d_make_detector_on_device(int device);
 
+/* Extension: fill a sift3d_cuda_plan_desc (sift3d_cuda.h) with the scales and filters this
+ * detector's parameters give for the octaves base_octave .. base_octave + num_octaves - 1
+ * of a pyramid, whose first described octave is nx x ny x nz with the given units
+ * (num_octaves 0: as many as fit, sift.c:441-452). Used by the z-slab multi-GPU harness,
+ * which drives the CUDA contexts itself. */
+SIFT3D_EXPORT int sift3d_detector_fill_plan(const sift3d_detector *, int nx, int ny, int nz,
+                                            double ux, double uy, double uz, int base_octave,
+                                            int num_octaves, void *plan_desc);
+
 /* Number of keypoints / descriptors held by a store. */
 SIFT3D_EXPORT int sift3d_keypoint_store_count(const sift3d_keypoint_store *);
 SIFT3D_EXPORT int sift3d_descriptor_store_count(const sift3d_descriptor_store *);

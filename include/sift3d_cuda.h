@@ -117,6 +117,10 @@ typedef struct {
     int own0[SIFT3D_CUDA_MAX_OCTAVES];  /* owned planes [own0[o], own1[o]) of octave o,  */
     int own1[SIFT3D_CUDA_MAX_OCTAVES];  /* in slab-array coordinates; entry K describes  */
                                         /* the seed level (K, -1) when the plan has it   */
+    int org[SIFT3D_CUDA_MAX_OCTAVES];   /* plane of the whole volume's octave o that the  */
+                                        /* slab array's plane 0 is: interpolation         */
+                                        /* coordinates are formed in volume coordinates   */
+                                        /* so that they round as on a single device       */
 } sift3d_cuda_slab_desc;
 
 typedef struct {

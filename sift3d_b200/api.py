@@ -37,6 +37,29 @@ class CudaFilter(C.Structure):
     _fields_ = [("width", C.c_int), ("taps", C.c_float * MAX_TAPS)]
 
 
+class CudaPlanDesc(C.Structure):
+    _fields_ = [
+        ("nx", C.c_int), ("ny", C.c_int), ("nz", C.c_int), ("units", C.c_double * 3),
+        ("num_octaves", C.c_int), ("num_kp_levels", C.c_int),
+        ("scales", (C.c_double * (MAX_FILTERS + 1)) * MAX_OCTAVES),
+        ("first", CudaFilter), ("octave", CudaFilter * MAX_FILTERS),
+    ]
+
+
+class CudaSlabDesc(C.Structure):
+    _fields_ = [("num_sharded_octaves", C.c_int), ("own0", C.c_int * MAX_OCTAVES),
+                ("own1", C.c_int * MAX_OCTAVES), ("org", C.c_int * MAX_OCTAVES)]
+
+
+REDUCE_MAX_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_int)
+EXCHANGE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
+                          C.c_int, C.c_int, C.c_int)
+
+
+class CudaSlabCallbacks(C.Structure):
+    _fields_ = [("user", C.c_void_p), ("reduce_max", REDUCE_MAX_FN), ("exchange", EXCHANGE_FN)]
+
+
 class CudaKeypoint(C.Structure):
     _fields_ = [
         ("o", C.c_int32), ("s", C.c_int32),
@@ -92,6 +115,15 @@ def libcuda():
     L.sift3d_cuda_host_free.argtypes = [vp]
     L.sift3d_cuda_detect.argtypes = [vp, vp, C.c_int, C.POINTER(C.c_double), C.c_double,
                                      C.c_double, C.POINTER(C.c_int)]
+    L.sift3d_cuda_plan.argtypes = [vp, C.POINTER(CudaPlanDesc)]
+    L.sift3d_cuda_detect_slab.argtypes = [vp, vp, C.c_int, C.POINTER(C.c_double), C.c_double,
+                                          C.c_double, C.POINTER(CudaSlabDesc),
+                                          C.POINTER(CudaSlabCallbacks), C.POINTER(C.c_int)]
+    L.sift3d_cuda_detect_from_seed.argtypes = [vp, vp, C.c_int, C.POINTER(C.c_double),
+                                               C.c_double, C.c_double, C.POINTER(C.c_int)]
+    L.sift3d_cuda_set_base_octave.argtypes = [vp, C.c_int]
+    L.sift3d_cuda_level_ptr.argtypes = [vp, C.c_int, C.c_int]
+    L.sift3d_cuda_level_ptr.restype = vp
     L.sift3d_cuda_fetch_candidates.argtypes = [vp, vp, C.c_int]
     L.sift3d_cuda_describe.argtypes = [vp, vp, C.c_int, vp, C.c_int]
     L.sift3d_cuda_level_info.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_int),
@@ -152,6 +184,8 @@ def lib():
     L.sift3d_mat_rm_dimensions.restype = None
     L.sift3d_mat_rm_type.argtypes = [vp]
     L.sift3d_image_set_units.argtypes = [vp, C.c_double, C.c_double, C.c_double]
+    L.sift3d_detector_fill_plan.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double,
+                                            C.c_double, C.c_int, C.c_int, C.POINTER(CudaPlanDesc)]
     L.sift3d_image_get_units.argtypes = [vp] + [C.POINTER(C.c_double)] * 3
     L.sift3d_image_get_units.restype = None
     L.sift3d_image_dimensions.argtypes = [vp] + [C.POINTER(C.c_int)] * 4

@@ -22,13 +22,16 @@ namespace s3d {
 // ---------------------------------------------------------------------------------------
 // Literal per-tap sampling (SAMP_AND_ACC, imutil.c:779-796).
 // ---------------------------------------------------------------------------------------
+// Coordinates are those of the whole line: `line` holds samples org .. n-1 of it (org > 0 only
+// for the z axis of a z-slab, whose array starts at plane org of the volume -- the fractions
+// then round exactly as on a single device).
 __device__ __forceinline__ float samp(const float *__restrict__ line, size_t stride, float c,
-                                      int n, bool scale, float dv) {
+                                      int n, bool scale, float dv, int org) {
     int lo = (int) c;  // truncation toward zero, as the C cast
     const float fr = __fsub_rn(c, (float) lo);
     // Only reachable with lo outside [0, n-2] where the reference itself reads out of
     // bounds (single mirror on lines shorter than the kernel); keep the access legal.
-    lo = max(0, min(lo, n - 2));
+    lo = max(org, min(lo, n - 2)) - org;
     float a = line[(size_t) lo * stride];
     float b = line[(size_t) (lo + 1) * stride];
     if (scale) {
@@ -43,7 +46,7 @@ __device__ __forceinline__ float conv_point_generic(const float *__restrict__ li
                                                     size_t stride, int p, int n,
                                                     const float *__restrict__ taps, int hw,
                                                     float uf, int uhw, bool scale, float dv,
-                                                    int sh = -1) {
+                                                    int sh = -1, int org = 0) {
     const int start = uhw;
     const int end = n - 2 - uhw;
     const int dim_end = n - 1;
@@ -53,7 +56,7 @@ __device__ __forceinline__ float conv_point_generic(const float *__restrict__ li
         // so tap d samples position p + (-d >> sh) with fraction ((-d) mod 2^sh) * 2^-sh --
         // the same values the carried-coordinate loop below produces, without the
         // float <-> int round trips. frac == 0 taps are the sample itself: 1*a + 0*b == a.
-        const float *__restrict__ q = line + (size_t) p * stride;
+        const float *__restrict__ q = line + (size_t) (p - org) * stride;
         const ptrdiff_t st = (ptrdiff_t) stride;
         for (int d = -hw; d <= hw; d++) {
             const float tap = taps[d + hw];
@@ -88,7 +91,7 @@ __device__ __forceinline__ float conv_point_generic(const float *__restrict__ li
             }
             float sv[4];
 #pragma unroll
-            for (int j = 0; j < 4; j++) sv[j] = samp(line, stride, cs[j], n, scale, dv);
+            for (int j = 0; j < 4; j++) sv[j] = samp(line, stride, cs[j], n, scale, dv, org);
 #pragma unroll
             for (int j = 0; j < 4; j++) acc = __fadd_rn(acc, __fmul_rn(taps[d + j + hw], sv[j]));
         }
@@ -96,7 +99,7 @@ __device__ __forceinline__ float conv_point_generic(const float *__restrict__ li
             const float tap = taps[d + hw];
             const float step = __fmul_rn((float) d, uf);
             c = __fsub_rn(c, step);
-            acc = __fadd_rn(acc, __fmul_rn(tap, samp(line, stride, c, n, scale, dv)));
+            acc = __fadd_rn(acc, __fmul_rn(tap, samp(line, stride, c, n, scale, dv, org)));
             c = __fadd_rn(c, step);
         }
     } else {
@@ -110,7 +113,7 @@ __device__ __forceinline__ float conv_point_generic(const float *__restrict__ li
             } else if ((int) c >= dim_end) {
                 c = __fsub_rn(__fsub_rn(__fmul_rn(2.0f, (float) dim_end), c), 0.1f);
             }
-            acc = __fadd_rn(acc, __fmul_rn(tap, samp(line, stride, c, n, scale, dv)));
+            acc = __fadd_rn(acc, __fmul_rn(tap, samp(line, stride, c, n, scale, dv, org)));
         }
     }
     return acc;
@@ -126,7 +129,8 @@ __global__ void __launch_bounds__(256)
 blur_axis_generic_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny,
                          int nz, const float *__restrict__ taps, int hw, float uf, int uhw,
                          const float *__restrict__ divisor, const float *__restrict__ dog_prev,
-                         float *__restrict__ dogmax, float *__restrict__ ds_dst, int sh, int zoff) {
+                         float *__restrict__ dogmax, float *__restrict__ ds_dst, int sh, int zoff,
+                         int zorg) {
     // 3-D launch (x in the block, rows and planes in the grid): no 64-bit div/mod per thread
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     const int y = blockIdx.y * blockDim.y + threadIdx.y;
@@ -140,8 +144,10 @@ blur_axis_generic_kernel(const float *__restrict__ src, float *__restrict__ dst,
         float dv = 0.0f;
         if (divisor != nullptr) dv = *divisor;
         const bool scale = dv != 0.0f;  // im_scale leaves an all-zero image alone (imutil.c:706)
-        const float o = conv_point_generic(src + (idx - (size_t) p * stride), stride, p, n, taps, hw,
-                                           uf, uhw, scale, dv, sh);
+        // z of a z-slab: coordinates of the whole volume, array starting at plane zorg
+        const int org = AXIS == 2 ? zorg : 0;
+        const float o = conv_point_generic(src + (idx - (size_t) p * stride), stride, p + org,
+                                           n + org, taps, hw, uf, uhw, scale, dv, sh, org);
         dst[idx] = o;
         if (EPI) {
             if (dogmax != nullptr) vmax = fabsf(__fsub_rn(dog_prev[idx], o));
@@ -382,7 +388,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
                 int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
                 const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
                 const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches,
-                int z0, int z1) {
+                int z0, int z1, int zorg) {
     const int hw = f.width / 2;
     if (z1 < 0) {  // whole volume
         z0 = 0;
@@ -399,7 +405,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
     const unsigned blocks = (unsigned) ((total + 255) / 256);
     const AxisSpec ax = axis_spec(nx, units[0], hw);
     const AxisSpec ay = axis_spec(ny, units[1], hw);
-    const AxisSpec az = axis_spec(nz, units[2], hw);
+    const AxisSpec az = axis_spec(nz + zorg, units[2], hw);
 
     // Fused single-launch path: unit tap spacing on every axis, TMA-compatible rows, taps
     // symmetric bit for bit (the kernel shares the products of twin taps).
@@ -418,7 +424,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         P.dogmax = d_dogmax_slot;
         P.divisor = d_divisor;
         P.nx = nx; P.ny = ny; P.nz = nz;
-        P.z0 = z0; P.z1 = z1;
+        P.z0 = z0; P.z1 = z1; P.zorg = zorg;
         P.zchunk = nz;
         for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];
         for (int i = f.width; i < kMaxParamTaps; i++) P.taps.k[i] = 0.0f;
@@ -443,7 +449,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         P.dogmax = d_dogmax_slot;
         P.divisor = nullptr;
         P.nx = nx; P.ny = ny; P.nz = nz;
-        P.z0 = z0; P.z1 = z1;
+        P.z0 = z0; P.z1 = z1; P.zorg = zorg;
         P.zchunk = nz;
         for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];
         for (int i = f.width; i < kMaxParamTaps; i++) P.taps.k[i] = 0.0f;
@@ -468,12 +474,12 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
                         (unsigned) (zhi - zlo));
     const dim3 ggrid_z(ggrid_xy.x, ggrid_xy.y, (unsigned) (z1 - z0));
     blur_axis_generic_kernel<0, false><<<ggrid_xy, gblock, 0, st>>>(
-        src, tmp_a, nx, ny, nz, d_taps, hw, ax.uf, ax.uhw, d_divisor, nullptr, nullptr, nullptr, ax.sh, zlo);
+        src, tmp_a, nx, ny, nz, d_taps, hw, ax.uf, ax.uhw, d_divisor, nullptr, nullptr, nullptr, ax.sh, zlo, 0);
     blur_axis_generic_kernel<1, false><<<ggrid_xy, gblock, 0, st>>>(
-        tmp_a, tmp_b, nx, ny, nz, d_taps, hw, ay.uf, ay.uhw, nullptr, nullptr, nullptr, nullptr, ay.sh, zlo);
+        tmp_a, tmp_b, nx, ny, nz, d_taps, hw, ay.uf, ay.uhw, nullptr, nullptr, nullptr, nullptr, ay.sh, zlo, 0);
     blur_axis_generic_kernel<2, true><<<ggrid_z, gblock, 0, st>>>(
         tmp_b, dst, nx, ny, nz, d_taps, hw, az.uf, az.uhw, nullptr, dog_prev,
-        want_max ? d_dogmax_slot : nullptr, ds_dst, az.sh, z0);
+        want_max ? d_dogmax_slot : nullptr, ds_dst, az.sh, z0, zorg);
     if (launches) *launches += 3;
     S3D_CK(cudaGetLastError());
     return 0;

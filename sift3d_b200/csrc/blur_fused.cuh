@@ -83,6 +83,7 @@ struct FusedParams {
     const float *divisor;  // im_scale divisor applied to src on load, or nullptr
     int nx, ny, nz;
     int z0, z1;            // output planes [z0, z1)
+    int zorg;              // z-slab: plane of the whole volume that array plane 0 is (else 0)
     int zchunk;            // outputs per z-chunk
     TapsParam taps;        // taps in the parameter bank
 };
@@ -383,7 +384,7 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
 #pragma unroll
                     for (int c = 0; c < 4; c++) prev[c] = yv[c];
                 } else {
-                    const float fr = right_frac(dez, m);
+                    const float fr = right_frac(dez + P.zorg, m);
 #pragma unroll
                     for (int c = 0; c < 4; c++) {
                         const float cur = yv[c];

@@ -329,8 +329,11 @@ blur_fused_half_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
                 mode = 1;
                 if (n == 0) step = false;
                 int lo;
-                half_rule(2 * p + 1, dez, nz, lo, fr_h);
-                half_rule(2 * p, dez, nz, lo, fr_v);
+                // fractions from the coordinates of the whole volume (z-slab: array plane 0 is
+                // plane zorg), so that they round as on a single device
+                const int zg = P.zorg;
+                half_rule(2 * (p + zg) + 1, dez + zg, nz + zg, lo, fr_h);
+                half_rule(2 * (p + zg), dez + zg, nz + zg, lo, fr_v);
             } else {
                 p = pstart - (n - npro);
                 mode = p >= 0 ? 0 : (p == -1 ? 2 : 3);

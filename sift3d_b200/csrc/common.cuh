@@ -60,7 +60,8 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
                 int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
                 const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
                 const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches,
-                int z0 = 0, int z1 = -1);  // output planes [z0, z1); z1 < 0: the whole volume
+                int z0 = 0, int z1 = -1,   // output planes [z0, z1); z1 < 0: the whole volume
+                int zorg = 0);             // z-slab: volume plane of array plane 0
 int launch_downsample(cudaStream_t st, const float *src, float *dst, int snx, int sny, int snz,
                       uint64_t *launches);
 int launch_absmax(cudaStream_t st, const float *src, size_t n, float *d_out, uint64_t *launches);

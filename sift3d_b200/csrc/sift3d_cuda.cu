@@ -363,7 +363,8 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         }
         for (int o = 0; o < noct_plan && o <= noct; o++) {
             const Level &L = ctx->level(o, 0);
-            if (slab->own0[o] < 0 || slab->own1[o] > L.nz || slab->own0[o] >= slab->own1[o]) {
+            if (slab->own0[o] < 0 || slab->own1[o] > L.nz || slab->own0[o] >= slab->own1[o] ||
+                slab->org[o] < 0) {
                 S3D_ERR("sift3d_cuda_detect_slab: bad owned range of octave %d\n", o);
                 return -1;
             }
@@ -373,6 +374,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     // planes [zr0(o), zr1(o)) of octave o are produced / scanned
     auto zr0 = [&](int o) { return slab ? slab->own0[o] : 0; };
     auto zr1 = [&](int o) { return slab ? slab->own1[o] : ctx->level(o, 0).nz; };
+    auto zorg = [&](int o) { return slab ? slab->org[o] : 0; };
     // hand the stream to the caller's collective (host callbacks, so the stream is drained)
     auto host_sync = [&]() -> int {
         S3D_CK(cudaStreamSynchronize(st));
@@ -445,7 +447,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             const double u[3] = {L.ux, L.uy, L.uz};
             rc = launch_blur(so, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
                              ctx->d_scalar(0), nullptr, nullptr, ds_dst, false, &ctx->launches,
-                             zr0(o), zr1(o));
+                             zr0(o), zr1(o), zorg(o));
         } else {
             Level &P = ctx->level(o, s - 1);
             const double u[3] = {P.ux, P.uy, P.uz};
@@ -453,7 +455,8 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             float *slot = nullptr;
             if (s - 1 >= 0 && s - 1 < kp) slot = ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (s - 1));
             rc = launch_blur(so, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
-                             nullptr, slot, P.d, ds_dst, false, &ctx->launches, zr0(o), zr1(o));
+                             nullptr, slot, P.d, ds_dst, false, &ctx->launches, zr0(o), zr1(o),
+                             zorg(o));
         }
         if (rc) return -1;
         if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], so));

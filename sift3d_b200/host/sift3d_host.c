@@ -365,15 +365,17 @@ static double level_scale(const sift3d_detector *d, int o, int s) {
     return d->sigma0 * pow(2.0, o + (double) s / d->num_kp_levels);
 }
 
-/* resize_SIFT3D (sift.c:427-475) + make_gss (imutil.c:1360-1409) for the current dims
- * and parameters; uploads the plan to the device. */
-static int detector_plan(sift3d_detector *d, const double units[3]) {
-    sift3d_cuda_plan_desc *P;
+/* resize_SIFT3D (sift.c:427-475) + make_gss (imutil.c:1360-1409) written into a plan
+ * description. `base_octave` > 0 describes the part of a pyramid that starts at that octave
+ * (nx, ny, nz and units are then those of that octave); `num_octaves` 0 derives the count
+ * from the dimensions as the reference does. */
+static int fill_plan(const sift3d_detector *d, int nx, int ny, int nz, const double units[3],
+                     int base_octave, int num_octaves, sift3d_cuda_plan_desc *P) {
     const int first_level = -1;
-    int min_dim, last_octave, num_octaves, num_levels, o, s, ret;
+    int min_dim, last_octave, num_levels, o, s, ret;
 
-    min_dim = d->nx < d->ny ? d->nx : d->ny;
-    min_dim = min_dim < d->nz ? min_dim : d->nz;
+    min_dim = nx < ny ? nx : ny;
+    min_dim = min_dim < nz ? min_dim : nz;
     /* The minimum size of a pyramid level is 8 in any dimension (sift.c:441-452) */
     last_octave = (int) log2((double) min_dim) - 3;
     if (last_octave < 0) {
@@ -381,10 +383,16 @@ static int detector_plan(sift3d_detector *d, const double units[3]) {
             "dimension \n");
         return SIFT3D_FAILURE;
     }
-    num_octaves = last_octave + 1;
+    if (num_octaves <= 0)
+        num_octaves = last_octave + 1;
+    else if (num_octaves > last_octave + 1) {
+        ERR("resize_SIFT3D: %d octaves do not fit a %d x %d x %d image \n", num_octaves, nx, ny,
+            nz);
+        return SIFT3D_FAILURE;
+    }
     num_levels = d->num_kp_levels + 3; /* sift.c:434-435 */
     if (d->num_kp_levels < 1 || d->num_kp_levels + 2 > SIFT3D_CUDA_MAX_FILTERS ||
-        num_octaves > SIFT3D_CUDA_MAX_OCTAVES) {
+        num_octaves > SIFT3D_CUDA_MAX_OCTAVES || base_octave < 0) {
         ERR("resize_SIFT3D: unsupported pyramid shape (%d keypoint levels, %d octaves) \n",
             d->num_kp_levels, num_octaves);
         return SIFT3D_FAILURE;
@@ -395,11 +403,10 @@ static int detector_plan(sift3d_detector *d, const double units[3]) {
             level_scale(d, 0, first_level) - DBL_EPSILON);
         return SIFT3D_FAILURE;
     }
-    if ((P = (sift3d_cuda_plan_desc *) calloc(1, sizeof(*P))) == NULL)
-        return SIFT3D_FAILURE;
-    P->nx = d->nx;
-    P->ny = d->ny;
-    P->nz = d->nz;
+    memset(P, 0, sizeof(*P));
+    P->nx = nx;
+    P->ny = ny;
+    P->nz = nz;
     P->units[0] = units[0];
     P->units[1] = units[1];
     P->units[2] = units[2];
@@ -407,15 +414,38 @@ static int detector_plan(sift3d_detector *d, const double units[3]) {
     P->num_kp_levels = d->num_kp_levels;
     for (o = 0; o < num_octaves; o++)
         for (s = first_level; s < first_level + num_levels; s++)
-            P->scales[o][s - first_level] = level_scale(d, o, s);
+            P->scales[o][s - first_level] = level_scale(d, o + base_octave, s);
     ret = design_gauss_incremental(d->sigma_n, level_scale(d, 0, first_level), &P->first);
     for (s = first_level; !ret && s < first_level + num_levels - 1; s++)
         ret = design_gauss_incremental(level_scale(d, 0, s), level_scale(d, 0, s + 1),
                                        &P->octave[s - first_level]);
+    return ret;
+}
+
+/* Plan the detector's own context for its current dims. */
+static int detector_plan(sift3d_detector *d, const double units[3]) {
+    sift3d_cuda_plan_desc *P;
+    int ret;
+
+    if ((P = (sift3d_cuda_plan_desc *) calloc(1, sizeof(*P))) == NULL)
+        return SIFT3D_FAILURE;
+    ret = fill_plan(d, d->nx, d->ny, d->nz, units, 0, 0, P);
     if (!ret)
         ret = sift3d_cuda_plan(d->ctx, P) ? SIFT3D_FAILURE : SIFT3D_SUCCESS;
     free(P);
     return ret;
+}
+
+/* Extension (multi-GPU slab harness): the plan this detector's parameters give for an
+ * arbitrary part of a pyramid, for a caller that drives sift3d_cuda.h contexts itself. */
+int sift3d_detector_fill_plan(const sift3d_detector *d, int nx, int ny, int nz, double ux,
+                              double uy, double uz, int base_octave, int num_octaves,
+                              void *plan_desc) {
+    const double units[3] = {ux, uy, uz};
+    if (d == NULL || plan_desc == NULL)
+        return SIFT3D_FAILURE;
+    return fill_plan(d, nx, ny, nz, units, base_octave, num_octaves,
+                     (sift3d_cuda_plan_desc *) plan_desc);
 }
 
 /* ---- detector ---------------------------------------------------------------------- */
