@@ -559,21 +559,23 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     const int chunk = (total + kDescThreads - 1) / kDescThreads;
     const int t0 = min(tid * chunk, total), t1 = min(t0 + chunk, total);
 
-    float acc[8][3];
-    int cur_key = -1;
-    int ci0 = 0, ci1 = 0, ci2 = 0;
-
-#define S3D_FLUSH()                                                                        \
-    if (cur_key >= 0) {                                                                    \
-        const int hb = ((cur_key & 3) + ((cur_key >> 2) & 3) * kPadDim +                   \
-                        ((cur_key >> 4) & 3) * kPadDim * kPadDim) * kVerts;                \
-        _Pragma("unroll") for (int c = 0; c < 8; c++) {                                    \
-            const int off = ((c >> 2) + ((c >> 1) & 1) * kPadDim + (c & 1) * kPadDim * kPadDim) * kVerts; \
-            fix_add2(hlo, hhi, hb + off + ci0, acc[c][0]);                                 \
-            fix_add2(hlo, hhi, hb + off + ci1, acc[c][1]);                                 \
-            fix_add2(hlo, hhi, hb + off + ci2, acc[c][2]);                                 \
-        }                                                                                  \
-    }
+    // Accumulation in integers. The three vertex magnitudes m_k = mag * bary_k are rounded
+    // to S fractional bits and the eight trilinear weights to 10, so that a contribution is
+    // one exact IMAD: P = M_k * W_c (|P| < 2^30), added as two 32-bit words (low 12 bits,
+    // signed rest) with the native ATOMS.ADD -- integer adds commute, so descriptors are
+    // reproducible run to run. S is the largest exponent for which neither |M| < 2^20 nor the
+    // high word can overflow under the analytic bound of the path: levels lie in [-1, 1]
+    // (im_scale), so |grad| <= sqrt(3)/u_min (x2 safety), and the weights one bin can
+    // receive sum to about one cell volume in voxels (x2 safety).
+    const float umin = fminf(uxf, fminf(uyf, uzf));
+    const float gbound = 2.0f * 1.7320508f / umin;
+    const float cellvox = fmaxf(hist_w * hist_w * hist_w / (uxf * uyf * uzf), 1.0f);
+    int fixS = min(ilogbf(1048576.0f / gbound), ilogbf(4294967296.0f / (gbound * cellvox)));
+    fixS = max(0, min(fixS, 22));
+    const float magic_m = ldexpf(1.5f, 23 - fixS);     // ulp(magic_m) = 2^-S
+    const int magic_m_bits = __float_as_int(magic_m);
+    const float m_lim = ldexpf(1048575.0f, -fixS);      // |M| < 2^20
+    const float magic_w = 12288.0f;                     // 1.5 * 2^13: ulp = 2^-10
 
     if (t0 < t1) {
         // row containing entry t0: the last r with row_off[r] <= t0 (its length is > 0)
@@ -660,27 +662,35 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
 
                 // SIFT3D_desc_acc_interp (sift.c:1318-1397)
                 const int bxi = (int) vbx, byi = (int) vby, bzi = (int) vbz;
-                const int key = bxi | (byi << 2) | (bzi << 4) | (face << 6);
-                if (key != cur_key) {
-                    S3D_FLUSH();
-                    cur_key = key;
-                    ci0 = sidx[face * 3]; ci1 = sidx[face * 3 + 1]; ci2 = sidx[face * 3 + 2];
-#pragma unroll
-                    for (int c = 0; c < 8; c++) acc[c][0] = acc[c][1] = acc[c][2] = 0.0f;
-                }
+                const int hb = (bxi + byi * kPadDim + bzi * kPadDim * kPadDim) * kVerts;
                 const float fx = __fsub_rn(vbx, floorf(vbx));
                 const float fy = __fsub_rn(vby, floorf(vby));
                 const float fz = __fsub_rn(vbz, floorf(vbz));
+                int M[3], A[3];
+                {
+                    const float bary[3] = {bx, by, bz};
+#pragma unroll
+                    for (int k = 0; k < 3; k++) {
+                        const float m = fminf(fmaxf(__fmul_rn(mag, bary[k]), -m_lim), m_lim);
+                        M[k] = __float_as_int(__fadd_rn(m, magic_m)) - magic_m_bits;
+                        A[k] = hb + sidx[face * 3 + k];
+                    }
+                }
+                const float wx[2] = {__fsub_rn(1.0f, fx), fx};
+                const float wy2[2] = {__fsub_rn(1.0f, fy), fy};
+                const float wz2[2] = {__fsub_rn(1.0f, fz), fz};
 #pragma unroll
                 for (int c = 0; c < 8; c++) {
                     const int ddx = c >> 2, ddy = (c >> 1) & 1, ddz = c & 1;
-                    const float wgt = __fmul_rn(
-                        __fmul_rn(ddx == 0 ? __fsub_rn(1.0f, fx) : fx, ddy == 0 ? __fsub_rn(1.0f, fy) : fy),
-                        ddz == 0 ? __fsub_rn(1.0f, fz) : fz);
-                    const float mw = __fmul_rn(mag, wgt);
-                    acc[c][0] = __fadd_rn(acc[c][0], __fmul_rn(mw, bx));
-                    acc[c][1] = __fadd_rn(acc[c][1], __fmul_rn(mw, by));
-                    acc[c][2] = __fadd_rn(acc[c][2], __fmul_rn(mw, bz));
+                    const float wgt = __fmul_rn(__fmul_rn(wx[ddx], wy2[ddy]), wz2[ddz]);
+                    const int W = __float_as_int(__fadd_rn(wgt, magic_w)) & 0x7ff;
+                    const int off = (ddx + ddy * kPadDim + ddz * kPadDim * kPadDim) * kVerts;
+#pragma unroll
+                    for (int k = 0; k < 3; k++) {
+                        const int P = M[k] * W;
+                        atomicAdd(hlo + A[k] + off, (unsigned) P & ((1u << kFix2LoBits) - 1u));
+                        atomicAdd(hhi + A[k] + off, P >> kFix2LoBits);
+                    }
                 }
             } while (0);
             // next entry of the flattened list
@@ -694,11 +704,359 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
                 S3D_ROW_SETUP();
             }
         }
-        S3D_FLUSH();
 #undef S3D_ROW_SETUP
     }
-#undef S3D_FLUSH
     __syncthreads();
+    for (int i = tid; i < kDescNumel; i += kDescThreads) {
+        const int bin = i % kVerts, cell = i / kVerts;
+        const int hx = cell & 3, hy = (cell >> 2) & 3, hz = cell >> 4;
+        const int j = (hx + hy * kPadDim + hz * kPadDim * kPadDim) * kVerts + bin;
+        const long long q = (long long) hhi[j] * (1ll << kFix2LoBits) + (long long) hlo[j];
+        hist[i] = (float) ldexp((double) q, -(fixS + 10));
+    }
+    __syncthreads();
+
+    // normalise, clamp, normalise (sift.c:1513-1526)
+    const float trunc = __fdiv_rn(__fmul_rn(0.2f, 128.0f), (float) kDescNumel);  // sift.c:45
+    for (int pass = 0; pass < 2; pass++) {
+        double ssq = 0.0;
+        for (int i = tid; i < kDescNumel; i += kDescThreads) {
+            const float el = hist[i];
+            ssq += (double) el * (double) el;
+        }
+        for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
+        if (lane == 0) red[warp] = ssq;
+        __syncthreads();
+        if (tid == 0) {
+            double t = 0.0;
+            for (int wv = 0; wv < kDescThreads / 32; wv++) t += red[wv];
+            norm_sh = sqrt(t) + DBL_EPSILON;
+        }
+        __syncthreads();
+        const float norm_inv = (float) (1.0 / norm_sh);  // sift.c:1423
+        for (int i = tid; i < kDescNumel; i += kDescThreads) {
+            float el = __fmul_rn(hist[i], norm_inv);
+            if (pass == 0) el = fminf(el, trunc);
+            hist[i] = el;
+        }
+        __syncthreads();
+    }
+    float *o = desc_out + (size_t) J.out_index * kDescNumel;
+    for (int i = tid; i < kDescNumel; i += kDescThreads) o[i] = hist[i];
+}
+
+// ---------------------------------------------------------------------------------------
+// v4: cell-stationary accumulation, no atomics on the voxel path.
+//
+// ncu on v3: the 24 x 2 shared-memory ATOMS.ADD per voxel ran at 2.4 wavefronts per
+// instruction (random bank conflicts between lanes that walk far-apart voxels) and the
+// run-length flush executed under divergence -- the shared-memory pipe, not arithmetic, set
+// the time. v4 turns the loop around the 4x4x4 cell grid:
+//   * a warp takes one floor cell (b0, b1, b2) at a time (64 cells, centre-first order,
+//     handed out by a shared counter). All 32 lanes then hit the same 8 corner cells, so
+//     each lane owns a private copy of the 8 x 12 bins the cell can touch, laid out
+//     [bin][lane]: bank = lane, every LDS/STS is one conflict-free wavefront and the
+//     accumulation is plain fp32 LDS + FMA + STS in a fixed order;
+//   * the voxels of a cell come from closed-form x intervals: 32 rows of the cell's
+//     bounding box at a time (one per lane: chord of the sphere /\ three slabs of the rotated
+//     cell, with a margin), a warp scan, and lane t of step k takes flattened entry 32k + t --
+//     neighbouring lanes are neighbouring x, so the six gradient loads coalesce;
+//   * the reference's exact per-voxel tests are kept and a voxel is accepted only by the cell
+//     its own (int) vb indices name, so every voxel is counted exactly once whatever the
+//     margins;
+//   * when the cell is done the 96 x 32 partial sums are reduced (rotated reads, conflict-free)
+//     and added to the block histogram in 2^-28 fixed point (96 x 2 integer atomics per cell
+//     visit; integer adds commute and the per-cell sums have a fixed order, so descriptors
+//     are reproducible run to run).
+// No window-size limit: nothing is tabulated per row.
+// ---------------------------------------------------------------------------------------
+constexpr int kCellBins = 8 * kVerts;  // bins one floor cell can touch
+__constant__ unsigned char c_cell_order[64];
+
+static int upload_cell_order() {
+    static bool done = false;
+    if (done) return 0;
+    unsigned char order[64];
+    int key[64];
+    for (int c = 0; c < 64; c++) {
+        const int b0 = c & 3, b1 = (c >> 2) & 3, b2 = c >> 4;
+        const int d0 = 2 * b0 - 3, d1 = 2 * b1 - 3, d2 = 2 * b2 - 3;  // twice the centre offset
+        key[c] = (d0 * d0 + d1 * d1 + d2 * d2) * 64 + c;
+        order[c] = (unsigned char) c;
+    }
+    for (int i = 0; i < 64; i++)
+        for (int j = i + 1; j < 64; j++)
+            if (key[order[j]] < key[order[i]]) {
+                const unsigned char t = order[i];
+                order[i] = order[j];
+                order[j] = t;
+            }
+    S3D_CK(cudaMemcpyToSymbol(c_cell_order, order, sizeof(order)));
+    done = true;
+    return 0;
+}
+
+__global__ void __launch_bounds__(kDescThreads)
+descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ desc_out) {
+    extern __shared__ __align__(16) float wacc_all[];  // [warps][kCellBins][32]
+    __shared__ unsigned hlo[kPadNumel];
+    __shared__ int hhi[kPadNumel];
+    __shared__ __align__(16) float smesh[kFaces * 16];
+    __shared__ int sidx[kFaces * 3];
+    __shared__ unsigned char slut[32];
+    __shared__ double red[kDescThreads / 32];
+    __shared__ double norm_sh;
+    __shared__ int next_cell;
+    const int ki = blockIdx.x;
+    if (ki >= n) return;
+    const DescJob J = jobs[ki];
+    const int tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5;
+    const unsigned full = 0xffffffffu;
+    float *__restrict__ wacc = wacc_all + warp * (kCellBins * 32);
+    for (int i = tid; i < kPadNumel; i += kDescThreads) {
+        hlo[i] = 0u;
+        hhi[i] = 0;
+    }
+    if (tid < kFaces) {
+        float *fm = smesh + tid * 16;
+        for (int k = 0; k < 3; k++) {
+            fm[k] = c_mesh.e1[tid][k];
+            fm[3 + k] = c_mesh.e2[tid][k];
+            fm[6 + k] = c_mesh.t[tid][k];
+            fm[9 + k] = c_mesh.q[tid][k];
+            sidx[tid * 3 + k] = c_mesh.idx[tid][k];
+        }
+        fm[12] = c_mesh.e2q[tid];
+        fm[13] = fm[14] = fm[15] = 0.0f;
+    }
+    if (tid < 32) slut[tid] = c_mesh.lut[tid >> 2][tid & 3];
+    if (tid == 0) next_cell = 0;
+
+    const float *__restrict__ img = J.img;
+    const int nx = J.nx, ny = J.ny, nz = J.nz;
+    const float uxf = J.ux, uyf = J.uy, uzf = J.uz;
+    const float cx = J.cx, cy = J.cy, cz = J.cz;
+    // sift.c:1453-1458
+    const float sigma = J.sigma;
+    const float rad = (float) (kDescRadFctr * (double) sigma);
+    const float half_w = (float) ((double) rad / sqrt(2.0));
+    const float desc_w = __fmul_rn(2.0f, half_w);
+    const float hist_w = __fdiv_rn(desc_w, (float) kHistPerDim);
+    const float bin_fctr = __fdiv_rn(1.0f, hist_w);
+    const float rad2 = __fmul_rn(rad, rad);
+    const float sig2 = __fmul_rn(sigma, sigma);
+    const float ixu = __fdiv_rn(1.0f, uxf), iyu = __fdiv_rn(1.0f, uyf), izu = __fdiv_rn(1.0f, uzf);
+
+    // Window (sift.c:91-99), all-float here because win_radius is a float.
+    const int x0 = (int) fmaxf(floorf(__fsub_rn(cx, __fdiv_rn(rad, uxf))), 1.0f);
+    const int x1 = (int) fminf(ceilf(__fadd_rn(cx, __fdiv_rn(rad, uxf))), (float) (nx - 2));
+    const int y0 = (int) fmaxf(floorf(__fsub_rn(cy, __fdiv_rn(rad, uyf))), 1.0f);
+    const int y1 = (int) fminf(ceilf(__fadd_rn(cy, __fdiv_rn(rad, uyf))), (float) (ny - 2));
+    const int z0 = (int) fmaxf(floorf(__fsub_rn(cz, __fdiv_rn(rad, uzf))), 1.0f);
+    const int z1 = (int) fminf(ceilf(__fadd_rn(cz, __fdiv_rn(rad, uzf))), (float) (nz - 2));
+    const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
+
+    // Rt = R^T (sift.c:1462-1464): Rt[i][j] = R[j][i]
+    const float r00 = J.R[0], r01 = J.R[1], r02 = J.R[2];
+    const float r10 = J.R[3], r11 = J.R[4], r12 = J.R[5];
+    const float r20 = J.R[6], r21 = J.R[7], r22 = J.R[8];
+    const float avx = r00 * uxf, avy = r01 * uxf, avz = r02 * uxf;  // d(vkp)/dx per voxel
+    const float cmar = hist_w * 1.0e-3f + 1.0e-6f;                  // slab margin
+    __syncthreads();
+
+    for (;;) {
+        int ci = 0;
+        if (lane == 0) ci = atomicAdd(&next_cell, 1);
+        ci = __shfl_sync(full, ci, 0);
+        if (ci >= 64) break;
+        const int cell = c_cell_order[ci];
+        const int b0 = cell & 3, b1 = (cell >> 2) & 3, b2 = cell >> 4;
+        // rotated-frame slab of the cell along each axis, and its centre
+        const float lo0 = (float) b0 * hist_w - half_w, lo1 = (float) b1 * hist_w - half_w,
+                    lo2 = (float) b2 * hist_w - half_w;
+        const float kc0 = lo0 + 0.5f * hist_w, kc1 = lo1 + 0.5f * hist_w, kc2 = lo2 + 0.5f * hist_w;
+        // bounding rows: vim = R * vkp; half extents of the rotated cube along y and z
+        const float dyc = r10 * kc0 + r11 * kc1 + r12 * kc2;
+        const float dzc = r20 * kc0 + r21 * kc1 + r22 * kc2;
+        const float ey = 0.5f * hist_w * (fabsf(r10) + fabsf(r11) + fabsf(r12));
+        const float ez = 0.5f * hist_w * (fabsf(r20) + fabsf(r21) + fabsf(r22));
+        const int ya = max(y0, (int) floorf(cy + (dyc - ey) * iyu) - 2);
+        const int yb = min(y1, (int) ceilf(cy + (dyc + ey) * iyu) + 2);
+        const int za = max(z0, (int) floorf(cz + (dzc - ez) * izu) - 2);
+        const int zb = min(z1, (int) ceilf(cz + (dzc + ez) * izu) + 2);
+        const int wyc = yb - ya + 1, wzc = zb - za + 1;
+        if (wyc <= 0 || wzc <= 0 || x1 < x0) continue;
+        const int nrows = wyc * wzc;
+#pragma unroll 8
+        for (int i = 0; i < kCellBins; i++) wacc[i * 32 + lane] = 0.0f;
+        bool any = false;
+
+        for (int batch = 0; batch < nrows; batch += 32) {
+            // ---- one row per lane: x interval of row /\ sphere /\ cell
+            const int rr = batch + lane;
+            int len = 0, xa = x0, ry = ya, rz = za;
+            if (rr < nrows) {
+                ry = ya + rr % wyc;
+                rz = za + rr / wyc;
+                const float dy = ((float) ry - cy) * uyf, dz = ((float) rz - cz) * uzf;
+                const float rem = rad2 * 1.0001f - dy * dy - dz * dz;
+                if (rem >= 0.0f) {
+                    const float half = sqrtf(rem) * ixu + 0.01f;
+                    float lo = cx - half, hi = cx + half;
+                    bool empty = false;
+                    const float av[3] = {avx, avy, avz};
+                    const float bv[3] = {r10 * dy + r20 * dz, r11 * dy + r21 * dz, r12 * dy + r22 * dz};
+                    const float sl[3] = {lo0, lo1, lo2};
+#pragma unroll
+                    for (int i = 0; i < 3; i++) {
+                        const float a = sl[i] - cmar - bv[i], b = sl[i] + hist_w + cmar - bv[i];
+                        if (fabsf(av[i]) > 1e-6f) {
+                            const float inv = 1.0f / av[i];
+                            const float t1 = a * inv, t2 = b * inv;
+                            lo = fmaxf(lo, cx + fminf(t1, t2) - 0.01f);
+                            hi = fminf(hi, cx + fmaxf(t1, t2) + 0.01f);
+                        } else if (a > 0.0f || b < 0.0f) {
+                            empty = true;
+                        }
+                    }
+                    if (!empty) {
+                        xa = max(x0, (int) ceilf(lo));
+                        const int xb = min(x1, (int) floorf(hi));
+                        len = max(0, xb - xa + 1);
+                    }
+                }
+            }
+            // ---- exclusive scan of the lengths over the warp
+            int incl = len;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(full, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const int total = __shfl_sync(full, incl, 31);
+            const int pre = incl - len;
+            if (total == 0) continue;
+            any = true;
+
+            for (int tb = 0; tb < total; tb += 32) {
+                const int t = tb + lane;
+                // row of entry t: the last lane j with pre_j <= t
+                int j = 0;
+#pragma unroll
+                for (int st = 16; st >= 1; st >>= 1) {
+                    const int pv = __shfl_sync(full, pre, (j + st) & 31);
+                    if (j + st < 32 && pv <= t) j += st;
+                }
+                const int x = __shfl_sync(full, xa, j) + (t - __shfl_sync(full, pre, j));
+                const int y = __shfl_sync(full, ry, j);
+                const int z = __shfl_sync(full, rz, j);
+                if (t >= total) continue;
+                do {  // one voxel; `break` = the reference's `continue`
+                    const float dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);
+                    const float dz = __fmul_rn(__fsub_rn((float) z, cz), uzf);
+                    const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
+                    const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+                    if (sq > rad2) break;
+                    // vkp = Rt * vim (SIFT3D_MUL_MAT_RM_CVEC, immacros.h:326-342)
+                    const float kx = __fadd_rn(__fadd_rn(__fmul_rn(r00, dx), __fmul_rn(r10, dy)), __fmul_rn(r20, dz));
+                    const float ky = __fadd_rn(__fadd_rn(__fmul_rn(r01, dx), __fmul_rn(r11, dy)), __fmul_rn(r21, dz));
+                    const float kz = __fadd_rn(__fadd_rn(__fmul_rn(r02, dx), __fmul_rn(r12, dy)), __fmul_rn(r22, dz));
+                    const float vbx = __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
+                    const float vby = __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
+                    const float vbz = __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
+                    if (vbx < 0.0f || vby < 0.0f || vbz < 0.0f || vbx >= (float) kHistPerDim ||
+                        vby >= (float) kHistPerDim || vbz >= (float) kHistPerDim)
+                        break;
+                    // the voxel belongs to the cell its own indices name (margins overlap)
+                    if ((int) vbx != b0 || (int) vby != b1 || (int) vbz != b2) break;
+
+                    const float *__restrict__ row = img + (size_t) z * zs + (size_t) y * ys;
+                    float gx = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + 1], row[x - 1])), ixu);
+                    float gy = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys])), iyu);
+                    float gz = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + zs], row[(ptrdiff_t) x - (ptrdiff_t) zs])), izu);
+                    const float w = expf(__fdiv_rn(__fmul_rn(-0.5f, sq), sig2));  // sift.c:1498
+                    gx = __fmul_rn(gx, w);
+                    gy = __fmul_rn(gy, w);
+                    gz = __fmul_rn(gz, w);
+                    const float rx = __fadd_rn(__fadd_rn(__fmul_rn(r00, gx), __fmul_rn(r10, gy)), __fmul_rn(r20, gz));
+                    const float ry2 = __fadd_rn(__fadd_rn(__fmul_rn(r01, gx), __fmul_rn(r11, gy)), __fmul_rn(r21, gz));
+                    const float rz2 = __fadd_rn(__fadd_rn(__fmul_rn(r02, gx), __fmul_rn(r12, gy)), __fmul_rn(r22, gz));
+
+                    // icos_hist_bin (sift.c:1254-1291)
+                    const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry2, ry2)), __fmul_rn(rz2, rz2));
+                    if ((double) n2 < kBaryEps) break;
+                    // nearest face centre among the 4 candidates of this octant (selection only)
+                    const float ax = fabsf(rx), ay = fabsf(ry2), az = fabsf(rz2);
+                    const float kA = 2.6180339887f, kB = 1.6180339887f, kC = 4.2360679775f;  // 1+phi, phi, 2phi+1
+                    const float d0 = kA * (ax + ay + az);
+                    const float d1 = fmaf(kB, ax, kC * az);
+                    const float d2 = fmaf(kC, ay, kB * az);
+                    const float d3 = fmaf(kC, ax, kB * ay);
+                    int which = 0;
+                    float dbest = d0;
+                    if (d1 > dbest) { dbest = d1; which = 1; }
+                    if (d2 > dbest) { dbest = d2; which = 2; }
+                    if (d3 > dbest) { dbest = d3; which = 3; }
+                    const int oct = (rx < 0.0f ? 1 : 0) | (ry2 < 0.0f ? 2 : 0) | (rz2 < 0.0f ? 4 : 0);
+                    const int best = slut[oct * 4 + which];
+                    float bx, by, bz;
+                    int face = -1;
+                    if (face_hit_s(smesh + best * 16, rx, ry2, rz2, bx, by, bz) && bx > 1e-5f && by > 1e-5f &&
+                        bz > 1e-5f) {
+                        face = best;
+                    } else {
+                        for (int f = 0; f < kFaces; f++) {
+                            if (face_hit_s(smesh + f * 16, rx, ry2, rz2, bx, by, bz)) { face = f; break; }
+                        }
+                    }
+                    if (face < 0) break;  // "unreachable" in the reference (sift.c:1288-1290)
+                    const float mag = sqrtf(n2);
+
+                    // SIFT3D_desc_acc_interp (sift.c:1318-1397) into this lane's copy of the
+                    // cell's 8 x 12 bins: corner c = (ddx, ddy, ddz), bin (c, vertex)
+                    const float fx = __fsub_rn(vbx, floorf(vbx));
+                    const float fy = __fsub_rn(vby, floorf(vby));
+                    const float fz = __fsub_rn(vbz, floorf(vbz));
+                    const float m3[3] = {__fmul_rn(mag, bx), __fmul_rn(mag, by), __fmul_rn(mag, bz)};
+                    float *a3[3];
+#pragma unroll
+                    for (int k = 0; k < 3; k++) a3[k] = wacc + sidx[face * 3 + k] * 32 + lane;
+                    const float wx[2] = {__fsub_rn(1.0f, fx), fx};
+                    const float wy2[2] = {__fsub_rn(1.0f, fy), fy};
+                    const float wz2[2] = {__fsub_rn(1.0f, fz), fz};
+#pragma unroll
+                    for (int c = 0; c < 8; c++) {
+                        const int ddx = c >> 2, ddy = (c >> 1) & 1, ddz = c & 1;
+                        const float wgt = __fmul_rn(__fmul_rn(wx[ddx], wy2[ddy]), wz2[ddz]);
+#pragma unroll
+                        for (int k = 0; k < 3; k++) {
+                            float *q = a3[k] + c * (kVerts * 32);
+                            *q = fmaf(m3[k], wgt, *q);
+                        }
+                    }
+                } while (0);
+            }
+        }
+        __syncwarp();
+        if (any) {
+            // ---- reduce the 32 lane copies of each bin and add to the block histogram
+            const int hb = (b0 + b1 * kPadDim + b2 * kPadDim * kPadDim) * kVerts;
+#pragma unroll
+            for (int q = 0; q < kCellBins / 32; q++) {
+                const int bin = q * 32 + lane;
+                float sum = 0.0f;
+#pragma unroll 8
+                for (int i = 0; i < 32; i++) sum = __fadd_rn(sum, wacc[bin * 32 + ((lane + i) & 31)]);
+                const int c = bin / kVerts, v = bin - c * kVerts;
+                const int off = ((c >> 2) + ((c >> 1) & 1) * kPadDim + (c & 1) * kPadDim * kPadDim) * kVerts;
+                if (sum != 0.0f) fix_add2(hlo, hhi, hb + off + v, sum);
+            }
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    float *hist = wacc_all;  // the lane copies are dead: reuse (keeps two CTAs per SM in 228 KB)
     for (int i = tid; i < kDescNumel; i += kDescThreads) {
         const int bin = i % kVerts, cell = i / kVerts;
         const int hx = cell & 3, hy = (cell >> 2) & 3, hz = cell >> 4;
@@ -716,7 +1074,7 @@ descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             const float el = hist[i];
             ssq += (double) el * (double) el;
         }
-        for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
+        for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(full, ssq, o);
         if (lane == 0) red[warp] = ssq;
         __syncthreads();
         if (tid == 0) {
@@ -754,6 +1112,21 @@ int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_ro
     // the flattened-list kernel keeps 6 bytes per window row in shared memory; windows too
     // large for that (huge sigma / tiny units) take the row-walking kernel
     static const bool force_rows = getenv("SIFT3D_CUDA_DESC_ROWS") != nullptr;
+    static const bool force_v3 = getenv("SIFT3D_CUDA_DESC_V3") != nullptr;
+    if (!force_rows && !force_v3) {
+        const size_t dyn4 = (size_t) (kDescThreads / 32) * kCellBins * 32 * sizeof(float);
+        static bool attr4 = false;
+        if (!attr4) {
+            if (upload_cell_order()) return -1;
+            S3D_CK(cudaFuncSetAttribute(descriptor_cell_kernel,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int) dyn4));
+            attr4 = true;
+        }
+        descriptor_cell_kernel<<<(unsigned) n, kDescThreads, dyn4, st>>>(d_jobs, n, d_desc);
+        if (launches) *launches += 1;
+        S3D_CK(cudaGetLastError());
+        return 0;
+    }
     const size_t dyn = ((size_t) max_rows + 1) * 4 + (size_t) max_rows * 2 + 16;
     const size_t kMaxDyn = 96 * 1024;
     if (!force_rows && max_rows >= 1 && dyn <= kMaxDyn) {
