@@ -135,6 +135,14 @@ SIFT3D_EXPORT void sift3d_image_dimensions(const sift3d_image *, int *nx, int *n
  * drops the copy. */
 SIFT3D_EXPORT int sift3d_image_make_resident(sift3d_image *, int device);
 
+/* Start an asynchronous copy of the current contents to CUDA device `device` and return at
+ * once; the next sift3d_detect_keypoints on a detector of that device consumes it without
+ * blocking the host on the transfer. Lets the upload of the next volume overlap the kernels
+ * of the current one. The host buffer must stay unchanged until that detect. */
+SIFT3D_EXPORT int sift3d_image_prefetch(sift3d_image *, int device);
+/* Block until that copy has completed (not needed before detect). */
+SIFT3D_EXPORT int sift3d_image_prefetch_wait(sift3d_image *);
+
 /* Detector bound to a given CUDA device (sift3d_make_detector() uses
  * $SIFT3D_CUDA_DEVICE or device 0). */
 SIFT3D_EXPORT sift3d_detector *sift3d_make_detector_on_device(int device);

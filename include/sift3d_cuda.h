@@ -187,6 +187,23 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_synchronize(sift3d_cuda_ctx *ctx);
  * skip the per-call upload). Returns NULL / -1 on failure. */
 SIFT3D_CUDA_EXPORT void *sift3d_cuda_device_upload(int device, const float *host, size_t count);
 SIFT3D_CUDA_EXPORT void sift3d_cuda_device_free(int device, void *dptr);
+
+/* Asynchronous upload on a copy stream of its own, so that the transfer of the NEXT volume
+ * overlaps the kernels of the current one (the reference reads its input from host memory,
+ * sift.c:629-659; on a GPU the PCIe copy is a fifth of the step and hides completely).
+ * begin() returns at once; `host` must be page-locked (sift3d_cuda_host_alloc) and unchanged
+ * until the transfer is consumed. `reuse` (may be NULL) recycles a previous ticket's device
+ * buffer. wait() makes the context's stream wait for the transfer without blocking the host. */
+typedef struct sift3d_cuda_upload sift3d_cuda_upload;
+SIFT3D_CUDA_EXPORT sift3d_cuda_upload *sift3d_cuda_upload_begin(int device, const float *host,
+                                                                size_t count,
+                                                                sift3d_cuda_upload *reuse);
+SIFT3D_CUDA_EXPORT const float *sift3d_cuda_upload_ptr(const sift3d_cuda_upload *up);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_upload_device(const sift3d_cuda_upload *up);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_upload_wait(sift3d_cuda_ctx *ctx, sift3d_cuda_upload *up);
+/* Block the host until the transfer has completed. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_upload_sync(sift3d_cuda_upload *up);
+SIFT3D_CUDA_EXPORT void sift3d_cuda_upload_free(sift3d_cuda_upload *up);
 SIFT3D_CUDA_EXPORT int sift3d_cuda_ctx_device(sift3d_cuda_ctx *ctx);
 
 /* User timing marks on the context's stream (slots 0..7): record now / elapsed ms

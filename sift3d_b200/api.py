@@ -191,6 +191,8 @@ def lib():
     L.sift3d_image_dimensions.argtypes = [vp] + [C.POINTER(C.c_int)] * 4
     L.sift3d_image_dimensions.restype = None
     L.sift3d_image_make_resident.argtypes = [vp, C.c_int]
+    L.sift3d_image_prefetch.argtypes = [vp, C.c_int]
+    L.sift3d_image_prefetch_wait.argtypes = [vp]
     L.sift3d_keypoint_store_count.argtypes = [vp]
     L.sift3d_descriptor_store_count.argtypes = [vp]
     L.sift3d_keypoint_store_get.argtypes = [vp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
@@ -246,6 +248,15 @@ class Image:
     def make_resident(self, device=0):
         if self._L.sift3d_image_make_resident(self.handle, int(device)):
             raise Sift3DError("sift3d_image_make_resident failed")
+
+    def prefetch(self, device=0):
+        """Start the asynchronous upload that the next detect on `device` will consume."""
+        if self._L.sift3d_image_prefetch(self.handle, int(device)):
+            raise Sift3DError("sift3d_image_prefetch failed")
+
+    def prefetch_wait(self):
+        if self._L.sift3d_image_prefetch_wait(self.handle):
+            raise Sift3DError("sift3d_image_prefetch_wait failed")
 
     def set_units(self, ux, uy, uz):
         if self._L.sift3d_image_set_units(self.handle, float(ux), float(uy), float(uz)):

@@ -113,6 +113,8 @@ int upload_mesh(void);
 // jobs may be reordered by the caller; max_rows = max over jobs of DescJob::max_rows
 int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_rows, float *d_desc,
                        uint64_t *launches);
+// copy n 32-bit words from page-locked host memory to device memory with a kernel
+int launch_pull_words(cudaStream_t st, const void *pinned_src, void *dst, size_t n, uint64_t *launches);
 int desc_job_rows(const DescJob &J);  // host: upper bound of window rows of one job
 
 }  // namespace s3d

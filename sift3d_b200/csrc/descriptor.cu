@@ -1095,6 +1095,22 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     for (int i = tid; i < kDescNumel; i += kDescThreads) o[i] = hist[i];
 }
 
+__global__ void __launch_bounds__(256)
+pull_words_kernel(const unsigned *__restrict__ src, unsigned *__restrict__ dst, size_t n) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[i];
+}
+
+int launch_pull_words(cudaStream_t st, const void *pinned_src, void *dst, size_t n, uint64_t *launches) {
+    if (n == 0) return 0;
+    static_assert(sizeof(DescJob) % 4 == 0, "DescJob is copied in 32-bit words");
+    pull_words_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, st>>>((const unsigned *) pinned_src,
+                                                                   (unsigned *) dst, n);
+    if (launches) *launches += 1;
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
 // Host: upper bound of the (y, z) rows of a job's window (the kernel clamps the window to
 // the volume, which only makes it smaller).
 int desc_job_rows(const DescJob &J) {

@@ -77,6 +77,8 @@ struct sift3d_cuda_ctx {
 
     // describe
     DevBuf desc_jobs, desc_out;
+    DescJob *h_jobs = nullptr;          // pinned (device-readable) staging of the job list
+    size_t h_jobs_cap = 0;
     sift3d_cuda_timings tm;
 
     // user marks + per-blur profiling
@@ -171,6 +173,7 @@ void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx) {
         if (ctx->ev_done[o]) cudaEventDestroy(ctx->ev_done[o]);
     }
     if (ctx->h_plan) cudaFreeHost(ctx->h_plan);
+    if (ctx->h_jobs) cudaFreeHost(ctx->h_jobs);
     ctx->taps.release();
     ctx->scalars.release();
     ctx->cand_raw.release();
@@ -637,6 +640,18 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
     if (set_device(ctx)) return -1;
     cudaStream_t st = ctx->stream;
     const int noct = ctx->desc.num_octaves, kp = ctx->desc.num_kp_levels;
+    // The job list is staged in page-locked memory and pulled by a kernel (zero-copy reads)
+    // instead of a copy-engine transfer: a host-to-device copy would queue behind an image
+    // upload that is in flight for the next volume (sift3d_cuda_upload_begin) and stall the
+    // descriptor kernel for the length of that upload.
+    if (ctx->h_jobs_cap < (size_t) num) {
+        if (ctx->h_jobs) cudaFreeHost(ctx->h_jobs);
+        ctx->h_jobs = nullptr;
+        ctx->h_jobs_cap = 0;
+        const size_t cap = (size_t) num * 2 + 256;
+        S3D_CK(cudaMallocHost((void **) &ctx->h_jobs, cap * sizeof(DescJob)));
+        ctx->h_jobs_cap = cap;
+    }
     std::vector<DescJob> jobs((size_t) num);
     for (int i = 0; i < num; i++) {
         const sift3d_cuda_keypoint &k = keys[i];
@@ -669,8 +684,10 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
         d_out = (float *) ctx->desc_out.p;
     }
     S3D_CK(cudaEventRecord(ctx->dv[DV_START], st));
-    S3D_CK(cudaMemcpyAsync(ctx->desc_jobs.p, jobs.data(), sizeof(DescJob) * (size_t) num,
-                           cudaMemcpyHostToDevice, st));
+    memcpy(ctx->h_jobs, jobs.data(), sizeof(DescJob) * (size_t) num);
+    if (launch_pull_words(st, ctx->h_jobs, ctx->desc_jobs.p, sizeof(DescJob) * (size_t) num / 4,
+                          &ctx->launches))
+        return -1;
     S3D_CK(cudaEventRecord(ctx->dv[DV_H2D], st));
     if (launch_descriptors(st, (const DescJob *) ctx->desc_jobs.p, num, max_rows, d_out, &ctx->launches))
         return -1;
@@ -781,6 +798,87 @@ void sift3d_cuda_device_free(int device, void *dptr) {
     if (!dptr) return;
     cudaSetDevice(device);
     cudaFree(dptr);
+}
+
+struct sift3d_cuda_upload {
+    int device = 0;
+    void *d = nullptr;
+    size_t bytes = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+};
+
+void sift3d_cuda_upload_free(sift3d_cuda_upload *up) {
+    if (!up) return;
+    cudaSetDevice(up->device);
+    if (up->stream) cudaStreamSynchronize(up->stream);
+    if (up->d) cudaFree(up->d);
+    if (up->done) cudaEventDestroy(up->done);
+    if (up->stream) cudaStreamDestroy(up->stream);
+    delete up;
+}
+
+sift3d_cuda_upload *sift3d_cuda_upload_begin(int device, const float *host, size_t count,
+                                             sift3d_cuda_upload *reuse) {
+    if (!host || count == 0) {
+        S3D_ERR("sift3d_cuda_upload_begin: empty buffer\n");
+        return nullptr;
+    }
+    sift3d_cuda_upload *up = reuse;
+    if (up && up->device != device) {
+        sift3d_cuda_upload_free(up);
+        up = nullptr;
+    }
+    bool fresh = false;
+    if (!up) {
+        up = new (std::nothrow) sift3d_cuda_upload();
+        if (!up) return nullptr;
+        up->device = device;
+        fresh = true;
+    }
+    const size_t bytes = count * sizeof(float);
+    bool ok = cudaSetDevice(device) == cudaSuccess;
+    if (ok && fresh)
+        ok = cudaStreamCreateWithFlags(&up->stream, cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreateWithFlags(&up->done, cudaEventDisableTiming) == cudaSuccess;
+    if (ok && up->bytes < bytes) {
+        if (up->d) {
+            cudaStreamSynchronize(up->stream);
+            cudaFree(up->d);
+            up->d = nullptr;
+            up->bytes = 0;
+        }
+        ok = cudaMalloc(&up->d, bytes) == cudaSuccess;
+        if (ok) up->bytes = bytes;
+    }
+    ok = ok && cudaMemcpyAsync(up->d, host, bytes, cudaMemcpyHostToDevice, up->stream) == cudaSuccess &&
+         cudaEventRecord(up->done, up->stream) == cudaSuccess;
+    if (!ok) {
+        S3D_ERR("sift3d_cuda_upload_begin: %s\n", cudaGetErrorString(cudaGetLastError()));
+        sift3d_cuda_upload_free(up);
+        return nullptr;
+    }
+    return up;
+}
+
+const float *sift3d_cuda_upload_ptr(const sift3d_cuda_upload *up) {
+    return up ? (const float *) up->d : nullptr;
+}
+
+int sift3d_cuda_upload_device(const sift3d_cuda_upload *up) { return up ? up->device : -1; }
+
+int sift3d_cuda_upload_sync(sift3d_cuda_upload *up) {
+    if (!up) return -1;
+    S3D_CK(cudaSetDevice(up->device));
+    S3D_CK(cudaEventSynchronize(up->done));
+    return 0;
+}
+
+int sift3d_cuda_upload_wait(sift3d_cuda_ctx *ctx, sift3d_cuda_upload *up) {
+    if (!ctx || !up || up->device != ctx->device) return -1;
+    if (set_device(ctx)) return -1;
+    S3D_CK(cudaStreamWaitEvent(ctx->stream, up->done, 0));
+    return 0;
 }
 
 int sift3d_cuda_ctx_device(sift3d_cuda_ctx *ctx) { return ctx ? ctx->device : -1; }

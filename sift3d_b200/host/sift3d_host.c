@@ -49,6 +49,8 @@ struct _sift3d_image {
     double ux, uy, uz;
     void *dev;   /* optional HBM-resident copy (sift3d_image_make_resident) */
     int dev_id;
+    sift3d_cuda_upload *up; /* asynchronous upload ticket (sift3d_image_prefetch) */
+    int up_pending;         /* the ticket holds a transfer no detect has consumed yet */
 };
 
 struct _sift3d_mat_rm {
@@ -262,6 +264,7 @@ void sift3d_free_image(sift3d_image *im) {
         return;
     if (im->dev != NULL)
         sift3d_cuda_device_free(im->dev_id, im->dev);
+    sift3d_cuda_upload_free(im->up);
     sift3d_cuda_host_free(im->data);
     free(im);
 }
@@ -281,6 +284,25 @@ int sift3d_image_make_resident(sift3d_image *im, int device) {
     im->dev = sift3d_cuda_device_upload(device, im->data, im->size);
     im->dev_id = device;
     return im->dev != NULL ? SIFT3D_SUCCESS : SIFT3D_FAILURE;
+}
+
+/* Extension: start copying the current contents to device `device` and return at once. The
+ * next sift3d_detect_keypoints on a detector of that device consumes the copy (its stream
+ * waits for the transfer; the host does not), so the upload of volume i+1 hides behind the
+ * kernels of volume i. The host buffer must stay unchanged until that detect. */
+int sift3d_image_prefetch(sift3d_image *im, int device) {
+    if (im == NULL || device < 0)
+        return SIFT3D_FAILURE;
+    im->up = sift3d_cuda_upload_begin(device, im->data, im->size, im->up);
+    im->up_pending = im->up != NULL;
+    return im->up != NULL ? SIFT3D_SUCCESS : SIFT3D_FAILURE;
+}
+
+/* Extension: block until the transfer started by sift3d_image_prefetch has completed. */
+int sift3d_image_prefetch_wait(sift3d_image *im) {
+    if (im == NULL || im->up == NULL)
+        return SIFT3D_FAILURE;
+    return sift3d_cuda_upload_sync(im->up) ? SIFT3D_FAILURE : SIFT3D_SUCCESS;
 }
 
 sift3d_image *sift3d_read_image(const char *path) {
@@ -737,9 +759,20 @@ int sift3d_detect_keypoints(sift3d_detector *const d, const sift3d_image *const 
     }
 
     {
-        const int resident = im->dev != NULL && im->dev_id == sift3d_cuda_ctx_device(d->ctx);
-        if (sift3d_cuda_detect(d->ctx, resident ? (const float *) im->dev : im->data, resident,
-                               units, d->peak_thresh, d->corner_thresh, &num_cand))
+        const int dev = sift3d_cuda_ctx_device(d->ctx);
+        const int resident = im->dev != NULL && im->dev_id == dev;
+        const float *src = resident ? (const float *) im->dev : im->data;
+        int on_device = resident;
+        if (im->up_pending && sift3d_cuda_upload_device(im->up) == dev) {
+            /* a prefetched copy: the stream waits for the transfer, the host does not */
+            if (sift3d_cuda_upload_wait(d->ctx, im->up))
+                return SIFT3D_FAILURE;
+            src = sift3d_cuda_upload_ptr(im->up);
+            on_device = 1;
+            ((sift3d_image *) im)->up_pending = 0; /* internal transfer state, not image data */
+        }
+        if (sift3d_cuda_detect(d->ctx, src, on_device, units, d->peak_thresh, d->corner_thresh,
+                               &num_cand))
             return SIFT3D_FAILURE;
     }
 
