@@ -396,7 +396,7 @@ __device__ __forceinline__ bool face_hit_s(const float *__restrict__ fm, float g
     const float pz = __fsub_rn(__fmul_rn(gx, e2y), __fmul_rn(gy, e2x));
     const float det = __fadd_rn(__fadd_rn(__fmul_rn(m0.x, px), __fmul_rn(m0.y, py)), __fmul_rn(m0.z, pz));
     if ((double) fabsf(det) < kBaryEps) return false;
-    const float det_inv = __fdiv_rn(1.0f, det);
+    const float det_inv = __frcp_rn(det);  // == 1.0f / det, correctly rounded
     const float tp = __fadd_rn(__fadd_rn(__fmul_rn(m1.z, px), __fmul_rn(m1.w, py)), __fmul_rn(m2.x, pz));
     const float cq = __fadd_rn(__fadd_rn(__fmul_rn(gx, m2.y), __fmul_rn(gy, m2.z)), __fmul_rn(gz, m2.w));
     by = __fmul_rn(det_inv, tp);
@@ -846,6 +846,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     const float bin_fctr = __fdiv_rn(1.0f, hist_w);
     const float rad2 = __fmul_rn(rad, rad);
     const float sig2 = __fmul_rn(sigma, sigma);
+    const float nhs = -0.5f / sig2;
     const float ixu = __fdiv_rn(1.0f, uxf), iyu = __fdiv_rn(1.0f, uyf), izu = __fdiv_rn(1.0f, uzf);
 
     // Window (sift.c:91-99), all-float here because win_radius is a float.
@@ -863,6 +864,9 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     const float r20 = J.R[6], r21 = J.R[7], r22 = J.R[8];
     const float avx = r00 * uxf, avy = r01 * uxf, avz = r02 * uxf;  // d(vkp)/dx per voxel
     const float cmar = hist_w * 1.0e-3f + 1.0e-6f;                  // slab margin
+    const bool av_ok[3] = {fabsf(avx) > 1e-6f, fabsf(avy) > 1e-6f, fabsf(avz) > 1e-6f};
+    const float av_inv[3] = {av_ok[0] ? 1.0f / avx : 0.0f, av_ok[1] ? 1.0f / avy : 0.0f,
+                             av_ok[2] ? 1.0f / avz : 0.0f};
     __syncthreads();
 
     for (;;) {
@@ -892,28 +896,30 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         for (int i = 0; i < kCellBins; i++) wacc[i * 32 + lane] = 0.0f;
         bool any = false;
 
-        for (int batch = 0; batch < nrows; batch += 32) {
-            // ---- one row per lane: x interval of row /\ sphere /\ cell
-            const int rr = batch + lane;
-            int len = 0, xa = x0, ry = ya, rz = za;
+        // Rows are taken 32 at a time (one per lane): x interval of row /\ sphere /\ cell, then
+        // an exclusive scan -> a set of up to 32 segments holding `T` flattened entries. Steps
+        // consume 32 entries; when the current set runs short the step is topped up from the
+        // next set, so only the last step of a cell can be partial.
+        auto load_set = [&](int batch, int &pre, int &xa, int &ry, int &rz, int &T) {
+            const int rr = batch * 32 + lane;
+            int len = 0;
+            xa = x0; ry = ya; rz = za;
             if (rr < nrows) {
-                ry = ya + rr % wyc;
                 rz = za + rr / wyc;
+                ry = ya + (rr - (rz - za) * wyc);
                 const float dy = ((float) ry - cy) * uyf, dz = ((float) rz - cz) * uzf;
                 const float rem = rad2 * 1.0001f - dy * dy - dz * dz;
                 if (rem >= 0.0f) {
                     const float half = sqrtf(rem) * ixu + 0.01f;
                     float lo = cx - half, hi = cx + half;
                     bool empty = false;
-                    const float av[3] = {avx, avy, avz};
                     const float bv[3] = {r10 * dy + r20 * dz, r11 * dy + r21 * dz, r12 * dy + r22 * dz};
                     const float sl[3] = {lo0, lo1, lo2};
 #pragma unroll
                     for (int i = 0; i < 3; i++) {
                         const float a = sl[i] - cmar - bv[i], b = sl[i] + hist_w + cmar - bv[i];
-                        if (fabsf(av[i]) > 1e-6f) {
-                            const float inv = 1.0f / av[i];
-                            const float t1 = a * inv, t2 = b * inv;
+                        if (av_ok[i]) {
+                            const float t1 = a * av_inv[i], t2 = b * av_inv[i];
                             lo = fmaxf(lo, cx + fminf(t1, t2) - 0.01f);
                             hi = fminf(hi, cx + fmaxf(t1, t2) + 0.01f);
                         } else if (a > 0.0f || b < 0.0f) {
@@ -927,116 +933,207 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
                     }
                 }
             }
-            // ---- exclusive scan of the lengths over the warp
             int incl = len;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int v = __shfl_up_sync(full, incl, o);
                 if (lane >= o) incl += v;
             }
-            const int total = __shfl_sync(full, incl, 31);
-            const int pre = incl - len;
-            if (total == 0) continue;
-            any = true;
-
-            for (int tb = 0; tb < total; tb += 32) {
-                const int t = tb + lane;
-                // row of entry t: the last lane j with pre_j <= t
-                int j = 0;
+            T = __shfl_sync(full, incl, 31);
+            pre = incl - len;
+        };
+        // segment of entry t in a set: the last lane j with pre_j <= t
+        auto find_row = [&](int pre, int t) {
+            int j = 0;
 #pragma unroll
-                for (int st = 16; st >= 1; st >>= 1) {
-                    const int pv = __shfl_sync(full, pre, (j + st) & 31);
-                    if (j + st < 32 && pv <= t) j += st;
-                }
-                const int x = __shfl_sync(full, xa, j) + (t - __shfl_sync(full, pre, j));
-                const int y = __shfl_sync(full, ry, j);
-                const int z = __shfl_sync(full, rz, j);
-                if (t >= total) continue;
-                do {  // one voxel; `break` = the reference's `continue`
-                    const float dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);
-                    const float dz = __fmul_rn(__fsub_rn((float) z, cz), uzf);
-                    const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
-                    const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
-                    if (sq > rad2) break;
-                    // vkp = Rt * vim (SIFT3D_MUL_MAT_RM_CVEC, immacros.h:326-342)
-                    const float kx = __fadd_rn(__fadd_rn(__fmul_rn(r00, dx), __fmul_rn(r10, dy)), __fmul_rn(r20, dz));
-                    const float ky = __fadd_rn(__fadd_rn(__fmul_rn(r01, dx), __fmul_rn(r11, dy)), __fmul_rn(r21, dz));
-                    const float kz = __fadd_rn(__fadd_rn(__fmul_rn(r02, dx), __fmul_rn(r12, dy)), __fmul_rn(r22, dz));
-                    const float vbx = __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
-                    const float vby = __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
-                    const float vbz = __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
-                    if (vbx < 0.0f || vby < 0.0f || vbz < 0.0f || vbx >= (float) kHistPerDim ||
-                        vby >= (float) kHistPerDim || vbz >= (float) kHistPerDim)
-                        break;
-                    // the voxel belongs to the cell its own indices name (margins overlap)
-                    if ((int) vbx != b0 || (int) vby != b1 || (int) vbz != b2) break;
-
-                    const float *__restrict__ row = img + (size_t) z * zs + (size_t) y * ys;
-                    float gx = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + 1], row[x - 1])), ixu);
-                    float gy = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys])), iyu);
-                    float gz = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + zs], row[(ptrdiff_t) x - (ptrdiff_t) zs])), izu);
-                    const float w = expf(__fdiv_rn(__fmul_rn(-0.5f, sq), sig2));  // sift.c:1498
-                    gx = __fmul_rn(gx, w);
-                    gy = __fmul_rn(gy, w);
-                    gz = __fmul_rn(gz, w);
-                    const float rx = __fadd_rn(__fadd_rn(__fmul_rn(r00, gx), __fmul_rn(r10, gy)), __fmul_rn(r20, gz));
-                    const float ry2 = __fadd_rn(__fadd_rn(__fmul_rn(r01, gx), __fmul_rn(r11, gy)), __fmul_rn(r21, gz));
-                    const float rz2 = __fadd_rn(__fadd_rn(__fmul_rn(r02, gx), __fmul_rn(r12, gy)), __fmul_rn(r22, gz));
-
-                    // icos_hist_bin (sift.c:1254-1291)
-                    const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry2, ry2)), __fmul_rn(rz2, rz2));
-                    if ((double) n2 < kBaryEps) break;
-                    // nearest face centre among the 4 candidates of this octant (selection only)
-                    const float ax = fabsf(rx), ay = fabsf(ry2), az = fabsf(rz2);
-                    const float kA = 2.6180339887f, kB = 1.6180339887f, kC = 4.2360679775f;  // 1+phi, phi, 2phi+1
-                    const float d0 = kA * (ax + ay + az);
-                    const float d1 = fmaf(kB, ax, kC * az);
-                    const float d2 = fmaf(kC, ay, kB * az);
-                    const float d3 = fmaf(kC, ax, kB * ay);
-                    int which = 0;
-                    float dbest = d0;
-                    if (d1 > dbest) { dbest = d1; which = 1; }
-                    if (d2 > dbest) { dbest = d2; which = 2; }
-                    if (d3 > dbest) { dbest = d3; which = 3; }
-                    const int oct = (rx < 0.0f ? 1 : 0) | (ry2 < 0.0f ? 2 : 0) | (rz2 < 0.0f ? 4 : 0);
-                    const int best = slut[oct * 4 + which];
-                    float bx, by, bz;
-                    int face = -1;
-                    if (face_hit_s(smesh + best * 16, rx, ry2, rz2, bx, by, bz) && bx > 1e-5f && by > 1e-5f &&
-                        bz > 1e-5f) {
-                        face = best;
-                    } else {
-                        for (int f = 0; f < kFaces; f++) {
-                            if (face_hit_s(smesh + f * 16, rx, ry2, rz2, bx, by, bz)) { face = f; break; }
-                        }
-                    }
-                    if (face < 0) break;  // "unreachable" in the reference (sift.c:1288-1290)
-                    const float mag = sqrtf(n2);
-
-                    // SIFT3D_desc_acc_interp (sift.c:1318-1397) into this lane's copy of the
-                    // cell's 8 x 12 bins: corner c = (ddx, ddy, ddz), bin (c, vertex)
-                    const float fx = __fsub_rn(vbx, floorf(vbx));
-                    const float fy = __fsub_rn(vby, floorf(vby));
-                    const float fz = __fsub_rn(vbz, floorf(vbz));
-                    const float m3[3] = {__fmul_rn(mag, bx), __fmul_rn(mag, by), __fmul_rn(mag, bz)};
-                    float *a3[3];
-#pragma unroll
-                    for (int k = 0; k < 3; k++) a3[k] = wacc + sidx[face * 3 + k] * 32 + lane;
-                    const float wx[2] = {__fsub_rn(1.0f, fx), fx};
-                    const float wy2[2] = {__fsub_rn(1.0f, fy), fy};
-                    const float wz2[2] = {__fsub_rn(1.0f, fz), fz};
-#pragma unroll
-                    for (int c = 0; c < 8; c++) {
-                        const int ddx = c >> 2, ddy = (c >> 1) & 1, ddz = c & 1;
-                        const float wgt = __fmul_rn(__fmul_rn(wx[ddx], wy2[ddy]), wz2[ddz]);
-#pragma unroll
-                        for (int k = 0; k < 3; k++) {
-                            float *q = a3[k] + c * (kVerts * 32);
-                            *q = fmaf(m3[k], wgt, *q);
-                        }
-                    }
-                } while (0);
+            for (int st = 16; st >= 1; st >>= 1) {
+                const int pv = __shfl_sync(full, pre, (j + st) & 31);
+                if (j + st < 32 && pv <= t) j += st;
             }
+            return j;
+        };
+        const int nbatch = (nrows + 31) >> 5;
+        int bi = 0;
+        int c_pre, c_xa, c_y, c_z, c_T, c_off = 0;
+        int n_pre = 0, n_xa = 0, n_y = 0, n_z = 0, n_T = 0;
+        bool have_next = false;
+        load_set(bi++, c_pre, c_xa, c_y, c_z, c_T);
+        // the next 32 flattened entries: one voxel per lane (warp-uniform control flow)
+        auto next_entries = [&](int &x, int &y, int &z, bool &active) -> bool {
+            for (;;) {
+                if (c_T - c_off > 0) break;
+                if (have_next) {
+                    c_pre = n_pre; c_xa = n_xa; c_y = n_y; c_z = n_z; c_T = n_T; c_off = 0;
+                    have_next = false;
+                } else if (bi < nbatch) {
+                    load_set(bi++, c_pre, c_xa, c_y, c_z, c_T);
+                    c_off = 0;
+                } else {
+                    x = x0; y = ya; z = za; active = false;
+                    return false;
+                }
+            }
+            const int avail = c_T - c_off;
+            const int fill_a = min(avail, 32);
+            bool mixed = false;
+            if (avail < 32 && (have_next || bi < nbatch)) {
+                if (!have_next) {
+                    load_set(bi++, n_pre, n_xa, n_y, n_z, n_T);
+                    have_next = true;
+                }
+                mixed = true;
+            }
+            const int take_b = mixed ? min(32 - fill_a, n_T) : 0;
+            const bool from_a = lane < fill_a;
+            const bool from_b = !from_a && lane - fill_a < take_b;
+            const int t = from_a ? c_off + lane : lane - fill_a;
+            const int j = find_row(c_pre, from_a ? t : 0);
+            x = __shfl_sync(full, c_xa, j) + (t - __shfl_sync(full, c_pre, j));
+            y = __shfl_sync(full, c_y, j);
+            z = __shfl_sync(full, c_z, j);
+            if (take_b > 0) {  // warp-uniform
+                const int jb = find_row(n_pre, from_b ? t : 0);
+                const int xb = __shfl_sync(full, n_xa, jb) + (t - __shfl_sync(full, n_pre, jb));
+                const int yb2 = __shfl_sync(full, n_y, jb);
+                const int zb2 = __shfl_sync(full, n_z, jb);
+                if (from_b) { x = xb; y = yb2; z = zb2; }
+            }
+            c_off += fill_a;
+            if (mixed && c_off >= c_T) {  // the current set is used up: the next one takes over
+                c_pre = n_pre; c_xa = n_xa; c_y = n_y; c_z = n_z; c_T = n_T; c_off = take_b;
+                have_next = false;
+            }
+            active = from_a || from_b;
+            if (!active) { x = x0; y = ya; z = za; }  // a legal address for the unused lanes
+            return true;
+        };
+
+        // One voxel up to its face and magnitudes, WITHOUT branches: two voxels per lane are
+        // evaluated back to back so that their (long, serial) dependency chains interleave --
+        // with 4 warps per scheduler a single chain leaves ~45 % of the issue slots empty.
+        struct Vox {
+            bool valid, slow;
+            float rx, ry, rz, n2;
+            float b0, b1, b2;
+            int face;
+            float fx, fy, fz;
+        };
+        auto eval_fast = [&](int x, int y, int z, bool active) -> Vox {
+            Vox v;
+            const float dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);
+            const float dz = __fmul_rn(__fsub_rn((float) z, cz), uzf);
+            const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
+            const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+            bool ok = active && !(sq > rad2);
+            // vkp = Rt * vim (SIFT3D_MUL_MAT_RM_CVEC, immacros.h:326-342)
+            const float kx = __fadd_rn(__fadd_rn(__fmul_rn(r00, dx), __fmul_rn(r10, dy)), __fmul_rn(r20, dz));
+            const float ky = __fadd_rn(__fadd_rn(__fmul_rn(r01, dx), __fmul_rn(r11, dy)), __fmul_rn(r21, dz));
+            const float kz = __fadd_rn(__fadd_rn(__fmul_rn(r02, dx), __fmul_rn(r12, dy)), __fmul_rn(r22, dz));
+            const float vbx = __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
+            const float vby = __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
+            const float vbz = __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
+            ok = ok && !(vbx < 0.0f || vby < 0.0f || vbz < 0.0f || vbx >= (float) kHistPerDim ||
+                         vby >= (float) kHistPerDim || vbz >= (float) kHistPerDim);
+            // the voxel belongs to the cell its own indices name (the interval margins overlap)
+            ok = ok && (int) vbx == b0 && (int) vby == b1 && (int) vbz == b2;
+            v.fx = __fsub_rn(vbx, floorf(vbx));
+            v.fy = __fsub_rn(vby, floorf(vby));
+            v.fz = __fsub_rn(vbz, floorf(vbz));
+
+            const float *__restrict__ row = img + (size_t) z * zs + (size_t) y * ys;
+            float gx = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + 1], row[x - 1])), ixu);
+            float gy = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys])), iyu);
+            float gz = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + zs], row[(ptrdiff_t) x - (ptrdiff_t) zs])), izu);
+            const float w = __expf(sq * nhs);  // exp(-0.5 * sq / sigma^2), sift.c:1498
+            gx = __fmul_rn(gx, w);
+            gy = __fmul_rn(gy, w);
+            gz = __fmul_rn(gz, w);
+            const float rx = __fadd_rn(__fadd_rn(__fmul_rn(r00, gx), __fmul_rn(r10, gy)), __fmul_rn(r20, gz));
+            const float ry2 = __fadd_rn(__fadd_rn(__fmul_rn(r01, gx), __fmul_rn(r11, gy)), __fmul_rn(r21, gz));
+            const float rz2 = __fadd_rn(__fadd_rn(__fmul_rn(r02, gx), __fmul_rn(r12, gy)), __fmul_rn(r22, gz));
+            // icos_hist_bin (sift.c:1254-1291)
+            const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry2, ry2)), __fmul_rn(rz2, rz2));
+            ok = ok && !((double) n2 < kBaryEps);
+            // nearest face centre among the 4 candidates of this octant (selection only)
+            const float ax = fabsf(rx), ay = fabsf(ry2), az = fabsf(rz2);
+            const float kA = 2.6180339887f, kB = 1.6180339887f, kC = 4.2360679775f;  // 1+phi, phi, 2phi+1
+            const float d0 = kA * (ax + ay + az);
+            const float d1 = fmaf(kB, ax, kC * az);
+            const float d2 = fmaf(kC, ay, kB * az);
+            const float d3 = fmaf(kC, ax, kB * ay);
+            int which = 0;
+            float dbest = d0;
+            if (d1 > dbest) { dbest = d1; which = 1; }
+            if (d2 > dbest) { dbest = d2; which = 2; }
+            if (d3 > dbest) { dbest = d3; which = 3; }
+            const int oct = (rx < 0.0f ? 1 : 0) | (ry2 < 0.0f ? 2 : 0) | (rz2 < 0.0f ? 4 : 0);
+            const int best = slut[oct * 4 + which];
+            float bx, by, bz;
+            const bool hit = face_hit_s(smesh + best * 16, rx, ry2, rz2, bx, by, bz) && bx > 1e-5f &&
+                             by > 1e-5f && bz > 1e-5f;
+            v.valid = ok;
+            v.slow = ok && !hit;  // near an edge: the literal first-hit scan decides
+            v.rx = rx; v.ry = ry2; v.rz = rz2; v.n2 = n2;
+            v.b0 = bx; v.b1 = by; v.b2 = bz;
+            v.face = best;
+            return v;
+        };
+        auto eval_slow = [&](Vox &v) {
+            float bx, by, bz;
+            int face = -1;
+            for (int f = 0; f < kFaces; f++) {
+                if (face_hit_s(smesh + f * 16, v.rx, v.ry, v.rz, bx, by, bz)) { face = f; break; }
+            }
+            if (face < 0) {  // "unreachable" in the reference (sift.c:1288-1290)
+                v.valid = false;
+            } else {
+                v.face = face; v.b0 = bx; v.b1 = by; v.b2 = bz;
+            }
+        };
+        // SIFT3D_desc_acc_interp (sift.c:1318-1397) into this lane's copy of the cell's
+        // 8 x 12 bins: corner c = (ddx, ddy, ddz), bin (c, vertex)
+        auto accumulate = [&](const Vox &v) {
+            const float mag = sqrtf(v.n2);
+            const float m3[3] = {__fmul_rn(mag, v.b0), __fmul_rn(mag, v.b1), __fmul_rn(mag, v.b2)};
+            float *a3[3];
+#pragma unroll
+            for (int k = 0; k < 3; k++) a3[k] = wacc + sidx[v.face * 3 + k] * 32 + lane;
+            const float wx[2] = {__fsub_rn(1.0f, v.fx), v.fx};
+            const float wy2[2] = {__fsub_rn(1.0f, v.fy), v.fy};
+            const float wz2[2] = {__fsub_rn(1.0f, v.fz), v.fz};
+            // all 24 loads first, then the FMAs, then the stores: written bin by bin the
+            // compiler must assume the three vertex columns alias and serialises
+            // LDS -> FFMA -> STS 24 times (~35 cycles each)
+            float acc[8][3];
+#pragma unroll
+            for (int c = 0; c < 8; c++)
+#pragma unroll
+                for (int k = 0; k < 3; k++) acc[c][k] = a3[k][c * (kVerts * 32)];
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                const int ddx = c >> 2, ddy = (c >> 1) & 1, ddz = c & 1;
+                const float wgt = __fmul_rn(__fmul_rn(wx[ddx], wy2[ddy]), wz2[ddz]);
+#pragma unroll
+                for (int k = 0; k < 3; k++) acc[c][k] = fmaf(m3[k], wgt, acc[c][k]);
+            }
+#pragma unroll
+            for (int c = 0; c < 8; c++)
+#pragma unroll
+                for (int k = 0; k < 3; k++) a3[k][c * (kVerts * 32)] = acc[c][k];
+        };
+
+        for (;;) {
+            int xA, yA, zA, xB, yB, zB;
+            bool actA, actB;
+            if (!next_entries(xA, yA, zA, actA)) break;
+            next_entries(xB, yB, zB, actB);
+            any = true;
+            Vox va = eval_fast(xA, yA, zA, actA);
+            Vox vb = eval_fast(xB, yB, zB, actB);
+            if (va.slow) eval_slow(va);
+            if (vb.slow) eval_slow(vb);
+            if (va.valid) accumulate(va);
+            if (vb.valid) accumulate(vb);
         }
         __syncwarp();
         if (any) {
