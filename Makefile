@@ -22,7 +22,7 @@ CU_HDRS := $(wildcard $(CSRC)/*.cuh) include/sift3d_cuda.h
 
 all: product oracle
 
-product: $(LIBDIR)/libsift3d_cuda.so $(LIBDIR)/libsift3D.so $(LIBDIR)/libsift3d_synth.so
+product: $(LIBDIR)/libsift3d_cuda.so $(LIBDIR)/libsift3D.so $(LIBDIR)/libsift3d_synth.so sift3d_b200/bin/kpSift3D
 
 build/%.o: $(CSRC)/%.cu $(CU_HDRS)
 	@mkdir -p build
@@ -32,9 +32,9 @@ $(LIBDIR)/libsift3d_cuda.so: $(CU_OBJS)
 	@mkdir -p $(LIBDIR)
 	$(NVCC) $(ARCH) -shared -ccbin $(HOSTCXX) -o $@ $(CU_OBJS)
 
-$(LIBDIR)/libsift3D.so: sift3d_b200/host/sift3d_host.c include/sift3d.h include/sift3d_cuda.h $(LIBDIR)/libsift3d_cuda.so
+$(LIBDIR)/libsift3D.so: sift3d_b200/host/sift3d_host.c sift3d_b200/host/nifti1.c sift3d_b200/host/nifti1.h include/sift3d.h include/sift3d_cuda.h $(LIBDIR)/libsift3d_cuda.so
 	$(HOSTCC) -O2 -ffp-contract=off -fno-fast-math -fPIC -shared -fvisibility=hidden -Wall \
-	    -o $@ sift3d_b200/host/sift3d_host.c -L$(LIBDIR) -lsift3d_cuda -lz -lm \
+	    -o $@ sift3d_b200/host/sift3d_host.c sift3d_b200/host/nifti1.c -L$(LIBDIR) -lsift3d_cuda -lz -lm \
 	    -Wl,-rpath,'$$ORIGIN'
 
 $(LIBDIR)/libsift3d_synth.so: sift3d_b200/synth.c
@@ -42,11 +42,17 @@ $(LIBDIR)/libsift3d_synth.so: sift3d_b200/synth.c
 	$(HOSTCC) -O2 -ffp-contract=off -fno-fast-math -fopenmp -fPIC -shared -fvisibility=hidden \
 	    -Wall -o $@ $< -lm
 
+# The reference's command-line program (cli/kpSift3D.c), rewritten against the drop-in API.
+sift3d_b200/bin/kpSift3D: cli/kpSift3D.c include/sift3d.h $(LIBDIR)/libsift3D.so
+	@mkdir -p sift3d_b200/bin
+	$(HOSTCC) -O2 -Wall -Iinclude -o $@ cli/kpSift3D.c -L$(LIBDIR) -lsift3D \
+	    -Wl,-rpath,'$$ORIGIN/../lib'
+
 oracle:
 	$(MAKE) -C oracle all
 
 clean:
-	rm -rf build $(LIBDIR)/*.so
+	rm -rf build $(LIBDIR)/*.so sift3d_b200/bin
 	$(MAKE) -C oracle clean
 
 .PHONY: all product oracle clean

@@ -156,6 +156,17 @@ SIFT3D_EXPORT int sift3d_detector_fill_plan(const sift3d_detector *, int nx, int
                                             double ux, double uy, double uz, int base_octave,
                                             int num_octaves, void *plan_desc);
 
+/* im_write (imutil.c:385-402, not exported by the fork): float32 NIfTI-1, .nii or .nii.gz. */
+SIFT3D_EXPORT int sift3d_write_image(const char *path, const sift3d_image *);
+
+/* The NIfTI-1 / Analyze reader and writer behind sift3d_read_image / sift3d_write_image
+ * without the page-locked image object (usable without a GPU). dims = nx, ny, nz, nc; data is
+ * channel-fastest, c + nc*(x + nx*(y + ny*z)); *data is released with sift3d_nifti_free. */
+SIFT3D_EXPORT int sift3d_nifti_read_raw(const char *path, int dims[4], double units[3], float **data);
+SIFT3D_EXPORT int sift3d_nifti_write_raw(const char *path, const int dims[4], const double units[3],
+                                         const float *data);
+SIFT3D_EXPORT void sift3d_nifti_free(float *data);
+
 /* Number of keypoints / descriptors held by a store. */
 SIFT3D_EXPORT int sift3d_keypoint_store_count(const sift3d_keypoint_store *);
 SIFT3D_EXPORT int sift3d_descriptor_store_count(const sift3d_descriptor_store *);

@@ -26,6 +26,7 @@
 
 #include "../../include/sift3d.h"
 #include "../../include/sift3d_cuda.h"
+#include "nifti1.h"
 
 #define ERR(...) fprintf(stderr, __VA_ARGS__)
 
@@ -305,17 +306,98 @@ int sift3d_image_prefetch_wait(sift3d_image *im) {
     return sift3d_cuda_upload_sync(im->up) ? SIFT3D_FAILURE : SIFT3D_SUCCESS;
 }
 
+static void *pinned_alloc(size_t bytes, void *user) {
+    (void) user;
+    return sift3d_cuda_host_alloc(bytes);
+}
+
+static void *plain_alloc(size_t bytes, void *user) {
+    (void) user;
+    return malloc(bytes ? bytes : 1);
+}
+
+/* im_read (imutil.c:352-372) + read_nii (nifti.c:52-167). The reference needs nifticlib for
+ * this and fails on every path without it (nifti.c:16-31); here the format is read by
+ * nifti1.c, so .nii, .nii.gz and .hdr/.img pairs always work. */
 sift3d_image *sift3d_read_image(const char *path) {
-    /* The reference build without nifticlib answers every path the same way
-     * (nifti.c:16-31 via imutil.c:352-372, 1657-1670). */
-    const char *ext = file_ext(path);
-    if (strcmp(ext, "img") && strcmp(ext, "gz") && strcmp(ext, "nii")) {
+    const char *ext;
+    sift3d_image *im;
+    nifti1_info info;
+    float *data = NULL;
+
+    if (path == NULL)
+        return NULL;
+    ext = file_ext(path);
+    /* im_get_format (imutil.c:318-331) */
+    if (strcmp(ext, "img") && strcmp(ext, "gz") && strcmp(ext, "nii") && strcmp(ext, "hdr")) {
         ERR("im_read: unrecognized file extension from file %s \n", path);
         return NULL;
     }
-    ERR("nii_error_message: SIFT3D was not compiled with NIFTI support!\n");
-    return NULL;
+    if (nifti1_read(path, &info, pinned_alloc, NULL, &data)) {
+        sift3d_cuda_host_free(data);
+        return NULL;
+    }
+    if ((im = (sift3d_image *) calloc(1, sizeof(*im))) == NULL) {
+        sift3d_cuda_host_free(data);
+        return NULL;
+    }
+    im->nx = info.nx;
+    im->ny = info.ny;
+    im->nz = info.nz;
+    im->nc = info.nc;
+    /* nifti.c:89-91 stores pixdim as is; a negative spacing would make every tap offset
+     * negative, so its magnitude is used */
+    im->ux = fabs(info.ux);
+    im->uy = fabs(info.uy);
+    im->uz = fabs(info.uz);
+    im->size = (size_t) info.nx * (size_t) info.ny * (size_t) info.nz * (size_t) info.nc;
+    im->data = data;
+    return im;
 }
+
+/* Extension: im_write (imutil.c:385-402) + write_nii (nifti.c:170-222): float32 NIfTI-1,
+ * .nii or .nii.gz, units in pixdim. */
+int sift3d_write_image(const char *path, const sift3d_image *im) {
+    nifti1_info info;
+    if (path == NULL || im == NULL)
+        return SIFT3D_FAILURE;
+    info.nx = im->nx;
+    info.ny = im->ny;
+    info.nz = im->nz;
+    info.nc = im->nc;
+    info.ux = im->ux;
+    info.uy = im->uy;
+    info.uz = im->uz;
+    return nifti1_write(path, &info, im->data) ? SIFT3D_FAILURE : SIFT3D_SUCCESS;
+}
+
+/* Extension (tools and tests on machines without a GPU): the reader without the page-locked
+ * image object. dims = nx, ny, nz, nc; *data is malloc'ed, release with sift3d_nifti_free. */
+int sift3d_nifti_read_raw(const char *path, int dims[4], double units[3], float **data) {
+    nifti1_info info;
+    if (path == NULL || dims == NULL || units == NULL || data == NULL)
+        return SIFT3D_FAILURE;
+    if (nifti1_read(path, &info, plain_alloc, NULL, data)) {
+        free(*data);
+        *data = NULL;
+        return SIFT3D_FAILURE;
+    }
+    dims[0] = info.nx; dims[1] = info.ny; dims[2] = info.nz; dims[3] = info.nc;
+    units[0] = info.ux; units[1] = info.uy; units[2] = info.uz;
+    return SIFT3D_SUCCESS;
+}
+
+int sift3d_nifti_write_raw(const char *path, const int dims[4], const double units[3],
+                           const float *data) {
+    nifti1_info info;
+    if (path == NULL || dims == NULL || units == NULL || data == NULL)
+        return SIFT3D_FAILURE;
+    info.nx = dims[0]; info.ny = dims[1]; info.nz = dims[2]; info.nc = dims[3];
+    info.ux = units[0]; info.uy = units[1]; info.uz = units[2];
+    return nifti1_write(path, &info, data) ? SIFT3D_FAILURE : SIFT3D_SUCCESS;
+}
+
+void sift3d_nifti_free(float *data) { free(data); }
 
 float *sift3d_image_data(const sift3d_image *im) { return im->data; }
 
