@@ -215,6 +215,10 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_elapsed_ms(sift3d_cuda_ctx *ctx, int a, int b
  * produce one Gaussian level) with CUDA events. blur_ms returns the duration of the blur
  * that produced level (o, s) in the last detect, and the number of launches it took. */
 SIFT3D_CUDA_EXPORT int sift3d_cuda_set_profiling(sift3d_cuda_ctx *ctx, int enabled);
+/* Start and end of the blur of level (o, s) relative to the start of the last detect, in
+ * milliseconds (profiling mode): the timeline of the octave streams. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_level_span_ms(sift3d_cuda_ctx *ctx, int o, int s, float *begin_ms,
+                                                 float *end_ms);
 SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_ms(sift3d_cuda_ctx *ctx, int o, int s, float *ms,
                                            int *launches);
 

@@ -74,7 +74,8 @@ int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, in
                    int *d_count, uint64_t *launches, int z0 = 0, int z1 = -1);  // planes [z0, z1)
 // all octaves in one launch; counts stay on the device
 int launch_order_all(cudaStream_t st, const Cand *d_raw, Cand *d_sorted, const int *base,
-                     const int *cap, int noct, const int *d_counts, uint64_t *launches);
+                     const int *cap, int noct, const int *d_counts, uint64_t *launches,
+                     int o_begin = 0, int o_end = -1);  // octaves [o_begin, o_end) only
 
 // orient.cu
 struct OctaveInfo {  // what the per-candidate kernels need to know about one octave
@@ -96,7 +97,8 @@ struct OrientPlan {
 // candidate in the concatenated (o, s, z, y, x) order.
 int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d_plan,
                       const int *d_counts, int *d_work, double corner_thresh,
-                      sift3d_cuda_keypoint *d_out, uint64_t *launches);
+                      sift3d_cuda_keypoint *d_out, uint64_t *launches,
+                      int o_begin = 0, int o_end = -1);  // octaves [o_begin, o_end); own d_work slot
 
 // descriptor.cu
 struct DescJob {

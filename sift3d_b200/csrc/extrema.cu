@@ -171,9 +171,9 @@ struct OrderParams {
 
 __global__ void __launch_bounds__(256)
 order_all_kernel(const Cand *__restrict__ raw, Cand *__restrict__ sorted, const OrderParams P,
-                 const int *__restrict__ counts) {
+                 const int *__restrict__ counts, int o_begin) {
     __shared__ unsigned long long tile[256];
-    const int o = blockIdx.y;
+    const int o = blockIdx.y + o_begin;
     const int n = min(counts[o], P.cap[o]);
     const Cand *__restrict__ in = raw + P.base[o];
     Cand *__restrict__ out = sorted + P.base[o];
@@ -238,13 +238,17 @@ int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, in
 }
 
 int launch_order_all(cudaStream_t st, const Cand *d_raw, Cand *d_sorted, const int *base,
-                     const int *cap, int noct, const int *d_counts, uint64_t *launches) {
+                     const int *cap, int noct, const int *d_counts, uint64_t *launches,
+                     int o_begin, int o_end) {
     OrderParams P;
     for (int o = 0; o < SIFT3D_CUDA_MAX_OCTAVES; o++) {
         P.base[o] = o < noct ? base[o] : 0;
         P.cap[o] = o < noct ? cap[o] : 0;
     }
-    order_all_kernel<<<dim3(32, (unsigned) noct), 256, 0, st>>>(d_raw, d_sorted, P, d_counts);
+    if (o_end < 0) o_end = noct;
+    if (o_end <= o_begin) return 0;
+    order_all_kernel<<<dim3(32, (unsigned) (o_end - o_begin)), 256, 0, st>>>(d_raw, d_sorted, P, d_counts,
+                                                                            o_begin);
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
     return 0;

@@ -96,7 +96,7 @@ constexpr int kOrientThreads = 128;
 __global__ void __launch_bounds__(kOrientThreads)
 orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict__ plan,
                   const int *__restrict__ counts, int *__restrict__ work, double corner_thresh,
-                  sift3d_cuda_keypoint *__restrict__ out) {
+                  sift3d_cuda_keypoint *__restrict__ out, int o_begin, int o_end) {
     __shared__ int s_first[SIFT3D_CUDA_MAX_OCTAVES + 1];  // rank of each octave's first candidate
     __shared__ int s_ci;
     __shared__ double red[kOrientThreads / 32][9];
@@ -110,11 +110,13 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
         s_first[noct] = acc;
     }
     __syncthreads();
-    const int total = s_first[noct];
+    // candidates of octaves [o_begin, o_end): ranks [s_first[o_begin], s_first[o_end])
+    const int total = s_first[min(o_end, noct)];
+    const int first = s_first[min(o_begin, noct)];
   for (;;) {
     // dynamic hand-out: windows differ 4x in size between keypoint levels
     __syncthreads();
-    if (threadIdx.x == 0) s_ci = atomicAdd(work, 1);
+    if (threadIdx.x == 0) s_ci = first + atomicAdd(work, 1);
     __syncthreads();
     const int ci = s_ci;
     if (ci >= total) break;
@@ -266,10 +268,12 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
 
 int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d_plan,
                       const int *d_counts, int *d_work, double corner_thresh,
-                      sift3d_cuda_keypoint *d_out, uint64_t *launches) {
+                      sift3d_cuda_keypoint *d_out, uint64_t *launches, int o_begin, int o_end) {
+    if (o_end < 0) o_end = SIFT3D_CUDA_MAX_OCTAVES;
+    if (o_end <= o_begin) return 0;
     // persistent grid: 148 SMs x the CTAs that fit (94 registers x 128 threads -> 5 per SM)
     orient_all_kernel<<<kNumSMs * 5, kOrientThreads, 0, st>>>(d_sorted, d_plan, d_counts, d_work,
-                                                          corner_thresh, d_out);
+                                                          corner_thresh, d_out, o_begin, o_end);
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
     return 0;

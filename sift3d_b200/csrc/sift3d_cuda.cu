@@ -70,7 +70,7 @@ struct sift3d_cuda_ctx {
     DevBuf cand_raw, cand_sorted;       // Cand regions, one per octave
     DevBuf counts;                      // int per octave
     DevBuf kps;                         // sift3d_cuda_keypoint, compact across octaves
-    std::vector<int> cand_base, cand_cap;
+    std::vector<int> cand_base, cand_cap, cand_min;
     int *h_counts = nullptr;            // pinned
     bool have_pyramid = false;
     int total_candidates = 0;
@@ -208,6 +208,32 @@ void sift3d_cuda_host_free(void *p) {
     if (p) cudaFreeHost(p);
 }
 
+// Candidate regions, one per octave: room for 1/32 of the octave's voxels (typical images
+// yield 0.04 - 0.4 %), or for what an earlier detect on this plan was seen to need.
+static int plan_candidates(sift3d_cuda_ctx *ctx) {
+    const int noct = ctx->desc.num_octaves;
+    ctx->cand_base.assign(noct, 0);
+    ctx->cand_cap.assign(noct, 0);
+    size_t cand_total = 0;
+    for (int o = 0; o < noct; o++) {
+        const size_t nv = ctx->level(o, 0).nvox();
+        size_t cap = nv / 32;
+        if (cap < 4096) cap = 4096;
+        if (cap < (size_t) ctx->cand_min[o]) cap = (size_t) ctx->cand_min[o];
+        if (cap > nv) cap = nv;
+        if (cap > ((size_t) 1 << 27)) cap = (size_t) 1 << 27;
+        ctx->cand_base[o] = (int) cand_total;
+        ctx->cand_cap[o] = (int) cap;
+        cand_total += cap;
+    }
+    if (ctx->cand_raw.ensure(cand_total * sizeof(Cand)) ||
+        ctx->cand_sorted.ensure(cand_total * sizeof(Cand)) ||
+        ctx->counts.ensure(sizeof(int) * 64) ||
+        ctx->kps.ensure(cand_total * sizeof(sift3d_cuda_keypoint)))
+        return -1;
+    return 0;
+}
+
 int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
     if (!ctx || !d) return -1;
     if (set_device(ctx)) return -1;
@@ -312,23 +338,8 @@ int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
         return -1;
 
     // candidate regions
-    ctx->cand_base.assign(noct, 0);
-    ctx->cand_cap.assign(noct, 0);
-    size_t cand_total = 0;
-    for (int o = 0; o < noct; o++) {
-        const size_t nv = ctx->level(o, 0).nvox();
-        size_t cap = nv / 32;
-        if (cap < 4096) cap = 4096;
-        if (cap > ((size_t) 1 << 26)) cap = (size_t) 1 << 26;
-        ctx->cand_base[o] = (int) cand_total;
-        ctx->cand_cap[o] = (int) cap;
-        cand_total += cap;
-    }
-    if (ctx->cand_raw.ensure(cand_total * sizeof(Cand)) ||
-        ctx->cand_sorted.ensure(cand_total * sizeof(Cand)) ||
-        ctx->counts.ensure(sizeof(int) * 64) ||
-        ctx->kps.ensure(cand_total * sizeof(sift3d_cuda_keypoint)))
-        return -1;
+    ctx->cand_min.assign(noct, 0);
+    if (plan_candidates(ctx)) return -1;
     S3D_CK(cudaStreamSynchronize(ctx->stream));
     ctx->planned = true;
     return 0;
@@ -345,7 +356,7 @@ int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
 static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_device,
                        const double units[3], double peak_thresh, double corner_thresh,
                        int *num_candidates, bool from_seed, const sift3d_cuda_slab_desc *slab,
-                       const sift3d_cuda_slab_callbacks *cb) {
+                       const sift3d_cuda_slab_callbacks *cb, int attempt = 0) {
     if (!ctx || !ctx->planned || !image || !units) {
         S3D_ERR("sift3d_cuda_detect: context not planned or NULL argument\n");
         return -1;
@@ -512,17 +523,11 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             return -1;
         if (so != st) S3D_CK(cudaEventRecord(ctx->ev_done[o], so));
     }
-    if (!serial)
-        for (int o = 1; o < noct; o++) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_done[o], 0));
-    S3D_CK(cudaEventRecord(ctx->ev[EV_EXTREMA], st));
-
-    // scan order (o, s, z, y, x) and assign_orientations (sift.c:1109-1143): one launch each
-    // over all octaves, candidate counts read on the device
-    if (launch_order_all(st, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
-                         ctx->cand_base.data(), ctx->cand_cap.data(), noct,
-                         (const int *) ctx->counts.p, &ctx->launches))
-        return -1;
-    S3D_CK(cudaEventRecord(ctx->ev[EV_ORDER], st));
+    // scan order (o, s, z, y, x) and assign_orientations (sift.c:1109-1143), candidate counts
+    // read on the device. Octave 0 holds ~90 % of the candidates and finishes its extrema
+    // ~100 us before the chain of small octaves does, so it is ordered and oriented first;
+    // the other octaves follow in a second, short pass (their slots in the output start at
+    // count[0], which is known by then).
     {
         OrientPlan &H = *ctx->h_plan;
         memset(&H, 0, sizeof(H));
@@ -542,22 +547,52 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         }
         S3D_CK(cudaMemcpyAsync(ctx->orient_plan.p, &H, sizeof(H), cudaMemcpyHostToDevice, st));
     }
+    const int split = noct > 1 ? 1 : noct;
+    S3D_CK(cudaEventRecord(ctx->ev[EV_EXTREMA], st));  // octave 0's extrema are done here
+    if (launch_order_all(st, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
+                         ctx->cand_base.data(), ctx->cand_cap.data(), noct,
+                         (const int *) ctx->counts.p, &ctx->launches, 0, split))
+        return -1;
+    S3D_CK(cudaEventRecord(ctx->ev[EV_ORDER], st));
     if (launch_orient_all(st, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
                           (const int *) ctx->counts.p, (int *) ctx->work.p, corner_thresh,
-                          (sift3d_cuda_keypoint *) ctx->kps.p, &ctx->launches))
+                          (sift3d_cuda_keypoint *) ctx->kps.p, &ctx->launches, 0, split))
+        return -1;
+    if (!serial)
+        for (int o = 1; o < noct; o++) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_done[o], 0));
+    if (launch_order_all(st, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
+                         ctx->cand_base.data(), ctx->cand_cap.data(), noct,
+                         (const int *) ctx->counts.p, &ctx->launches, split, noct) ||
+        launch_orient_all(st, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
+                          (const int *) ctx->counts.p, (int *) ctx->work.p + 1, corner_thresh,
+                          (sift3d_cuda_keypoint *) ctx->kps.p, &ctx->launches, split, noct))
         return -1;
     S3D_CK(cudaMemcpyAsync(ctx->h_counts, ctx->counts.p, sizeof(int) * noct,
                            cudaMemcpyDeviceToHost, st));
     S3D_CK(cudaEventRecord(ctx->ev[EV_ORIENT], st));
     S3D_CK(cudaStreamSynchronize(st));
     int total = 0;
+    bool overflow = false;
     for (int o = 0; o < noct; o++) {
-        if (ctx->h_counts[o] > ctx->cand_cap[o]) {
-            S3D_ERR("sift3d_cuda_detect: octave %d produced %d extrema, capacity %d\n", o,
-                    ctx->h_counts[o], ctx->cand_cap[o]);
-            return -1;
-        }
+        if (ctx->h_counts[o] > ctx->cand_cap[o]) overflow = true;
         total += ctx->h_counts[o];
+    }
+    if (overflow) {
+        // An unusually busy image (e.g. noise-free synthetic blobs): the extrema kernel kept
+        // counting past the end of a region without writing. Size the regions for what was
+        // counted and run the detection again (a slab cannot: its peers would not follow).
+        for (int o = 0; o < noct; o++)
+            if (ctx->h_counts[o] > ctx->cand_cap[o]) {
+                if (slab != nullptr || attempt >= 2) {
+                    S3D_ERR("sift3d_cuda_detect: octave %d produced %d extrema, capacity %d\n", o,
+                            ctx->h_counts[o], ctx->cand_cap[o]);
+                    return -1;
+                }
+                ctx->cand_min[o] = ctx->h_counts[o] + ctx->h_counts[o] / 4 + 1024;
+            }
+        if (plan_candidates(ctx)) return -1;
+        return detect_impl(ctx, image, image_on_device, units, peak_thresh, corner_thresh,
+                           num_candidates, from_seed, slab, cb, attempt + 1);
     }
     ctx->total_candidates = total;
     ctx->have_pyramid = true;
@@ -913,6 +948,18 @@ int sift3d_cuda_blur_ms(sift3d_cuda_ctx *ctx, int o, int s, float *ms, int *laun
     S3D_CK(cudaEventSynchronize(ctx->blur_ev[2 * li + 1]));
     if (ms) S3D_CK(cudaEventElapsedTime(ms, ctx->blur_ev[2 * li], ctx->blur_ev[2 * li + 1]));
     if (launches) *launches = ctx->blur_launches[li];
+    return 0;
+}
+
+int sift3d_cuda_level_span_ms(sift3d_cuda_ctx *ctx, int o, int s, float *begin_ms, float *end_ms) {
+    if (!ctx || !ctx->have_pyramid || !ctx->profiling || o < 0 || o >= ctx->desc.num_octaves ||
+        s < -1 || s > ctx->nlev - 2 || (s == -1 && o != 0))
+        return -1;
+    if (set_device(ctx)) return -1;
+    const size_t li = (size_t) o * ctx->nlev + (s + 1);
+    S3D_CK(cudaEventSynchronize(ctx->blur_ev[2 * li + 1]));
+    if (begin_ms) S3D_CK(cudaEventElapsedTime(begin_ms, ctx->ev[EV_START], ctx->blur_ev[2 * li]));
+    if (end_ms) S3D_CK(cudaEventElapsedTime(end_ms, ctx->ev[EV_START], ctx->blur_ev[2 * li + 1]));
     return 0;
 }
 
