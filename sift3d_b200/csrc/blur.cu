@@ -485,6 +485,115 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------
+// The last octaves of a pyramid are a few thousand voxels each, yet every level costs three
+// launches and the octaves form a serial chain (octave o+1 starts from level 2 of octave o):
+// at 256^3 the octaves of 16^3 and 8^3 voxels alone took 320 us of launch latency at the end
+// of a 1.7 ms detection. This kernel runs a whole chain of such octaves in ONE single-CTA
+// launch: levels live in shared memory, each blur is the same x / y / z sequence of
+// conv_point_generic calls as the generic kernels (so the bits are the same), with the DoG
+// max-abs and the 2x decimation into the next octave done in place. All levels are also
+// written to global memory for the extrema / orientation / descriptor kernels.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTinyThreads)
+tiny_octaves_kernel(const TinyChainParams P) {
+    extern __shared__ float tiny_smem[];
+    __shared__ float red[kTinyThreads / 32];
+    const int tid = threadIdx.x;
+    float *cur = tiny_smem, *nxt = tiny_smem + kTinyMaxVox, *ta = tiny_smem + 2 * kTinyMaxVox,
+          *tb = tiny_smem + 3 * kTinyMaxVox;
+    float *const seed = tiny_smem + 4 * kTinyMaxVox;  // level -1 of the next octave
+    for (int t = 0; t < P.noct; t++) {
+        const TinyOctave &O = P.oct[t];
+        const int nx = O.nx, ny = O.ny, nz = O.nz;
+        const int n = nx * ny * nz;
+        // level -1: from global for the first octave, else already decimated into `cur`
+        if (t == 0)
+            for (int i = tid; i < n; i += kTinyThreads) cur[i] = O.lvl[0][i];
+        __syncthreads();
+        for (int s = 0; s < P.nfilt; s++) {
+            const float *__restrict__ taps = P.taps[s];
+            const int hw = P.hw[s];
+            for (int axis = 0; axis < 3; axis++) {
+                const float *__restrict__ src = axis == 0 ? cur : (axis == 1 ? ta : tb);
+                float *__restrict__ dst = axis == 0 ? ta : (axis == 1 ? tb : nxt);
+                const float uf = O.uf[axis];
+                const int uhw = (int) ceilf((float) hw * uf);  // imutil.c:756-757
+                const int sh = O.sh[axis];
+                const int len = axis == 0 ? nx : (axis == 1 ? ny : nz);
+                const size_t stride = axis == 0 ? 1 : (axis == 1 ? (size_t) nx : (size_t) nx * ny);
+                for (int i = tid; i < n; i += kTinyThreads) {
+                    const int x = i % nx, y = (i / nx) % ny, z = i / (nx * ny);
+                    const int p = axis == 0 ? x : (axis == 1 ? y : z);
+                    dst[i] = conv_point_generic(src + ((size_t) i - (size_t) p * stride), stride, p, len,
+                                                taps, hw, uf, uhw, false, 0.0f, sh);
+                }
+                __syncthreads();
+            }
+            // level s is in `nxt`: global copy, DoG max-abs of level s-1, decimation
+            float *__restrict__ g = O.lvl[s + 1];
+            float vmax = 0.0f;
+            const bool want_max = O.dogmax[s] != nullptr;
+            for (int i = tid; i < n; i += kTinyThreads) {
+                const float o = nxt[i];
+                g[i] = o;
+                if (want_max) vmax = fmaxf(vmax, fabsf(__fsub_rn(cur[i], o)));
+            }
+            if (want_max) {
+                for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+                if ((tid & 31) == 0) red[tid >> 5] = vmax;
+                __syncthreads();
+                if (tid == 0) {
+                    float m = 0.0f;
+                    for (int w = 0; w < kTinyThreads / 32; w++) m = fmaxf(m, red[w]);
+                    *O.dogmax[s] = m;
+                }
+            }
+            if (s == P.ds_level && t + 1 < P.noct) {
+                // im_downsample_2x (imutil.c:597-613) into the next octave's level -1
+                const TinyOctave &N = P.oct[t + 1];
+                float *__restrict__ gn = N.lvl[0];
+                const int dn = N.nx * N.ny * N.nz;
+                for (int i = tid; i < dn; i += kTinyThreads) {
+                    const int x = i % N.nx, y = (i / N.nx) % N.ny, z = i / (N.nx * N.ny);
+                    const float v = nxt[((size_t) (2 * z) * ny + (size_t) (2 * y)) * nx + (size_t) (2 * x)];
+                    gn[i] = v;
+                    seed[i] = v;  // becomes `cur` of the next octave
+                }
+            }
+            __syncthreads();
+            float *sw = cur; cur = nxt; nxt = sw;
+        }
+        if (t + 1 < P.noct) {
+            const TinyOctave &N = P.oct[t + 1];
+            const int dn = N.nx * N.ny * N.nz;
+            __syncthreads();
+            for (int i = tid; i < dn; i += kTinyThreads) cur[i] = seed[i];
+        }
+    }
+}
+
+int launch_tiny_octaves(cudaStream_t st, const TinyChainParams &P, uint64_t *launches) {
+    const size_t dyn = (size_t) (4 * kTinyMaxVox + kTinyMaxVox / 8 + 64) * sizeof(float);
+    static bool attr = false;
+    if (!attr) {
+        S3D_CK(cudaFuncSetAttribute(tiny_octaves_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int) dyn));
+        attr = true;
+    }
+    tiny_octaves_kernel<<<1, kTinyThreads, dyn, st>>>(P);
+    if (launches) *launches += 1;
+    S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+// Host: sampling parameters of one axis for the tiny chain (same as the generic launcher)
+void tiny_axis(int n, double unit, float *uf, int *sh) {
+    const AxisSpec a = axis_spec(n, unit, 1);
+    *uf = a.uf;
+    *sh = a.sh;
+}
+
 int launch_downsample(cudaStream_t st, const float *src, float *dst, int snx, int sny, int snz,
                       uint64_t *launches) {
     const int dnx = snx / 2, dny = sny / 2, dnz = snz / 2;

@@ -62,6 +62,25 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
                 const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches,
                 int z0 = 0, int z1 = -1,   // output planes [z0, z1); z1 < 0: the whole volume
                 int zorg = 0);             // z-slab: volume plane of array plane 0
+// Chain of tiny octaves in one launch (blur.cu: tiny_octaves_kernel)
+constexpr int kTinyThreads = 1024;
+constexpr int kTinyMaxVox = 4096;   // voxels of the largest octave the chain kernel takes
+constexpr int kTinyMaxOct = 8;
+struct TinyOctave {
+    int nx, ny, nz;
+    float uf[3];                                  // unit factor per axis (1 / level units)
+    int sh[3];                                    // dyadic exponent per axis or -1
+    float *lvl[SIFT3D_CUDA_MAX_FILTERS + 1];      // level -1 .. nfilt-1
+    float *dogmax[SIFT3D_CUDA_MAX_FILTERS];       // [s]: slot for max|G(s-1) - G(s)| or nullptr
+};
+struct TinyChainParams {
+    int noct, nfilt, ds_level;
+    const float *taps[SIFT3D_CUDA_MAX_FILTERS];   // filter s: level s-1 -> s
+    int hw[SIFT3D_CUDA_MAX_FILTERS];
+    TinyOctave oct[kTinyMaxOct];
+};
+int launch_tiny_octaves(cudaStream_t st, const TinyChainParams &P, uint64_t *launches);
+void tiny_axis(int n, double unit, float *uf, int *sh);
 int launch_downsample(cudaStream_t st, const float *src, float *dst, int snx, int sny, int snz,
                       uint64_t *launches);
 int launch_absmax(cudaStream_t st, const float *src, size_t n, float *d_out, uint64_t *launches);

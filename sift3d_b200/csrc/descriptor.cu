@@ -864,6 +864,8 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     const float r20 = J.R[6], r21 = J.R[7], r22 = J.R[8];
     const float avx = r00 * uxf, avy = r01 * uxf, avz = r02 * uxf;  // d(vkp)/dx per voxel
     const float cmar = hist_w * 1.0e-3f + 1.0e-6f;                  // slab margin
+    const int cyi = (int) floorf(cy), czi = (int) floorf(cz);
+    const float cyf = cy - (float) cyi, czf = cz - (float) czi;
     const bool av_ok[3] = {fabsf(avx) > 1e-6f, fabsf(avy) > 1e-6f, fabsf(avz) > 1e-6f};
     const float av_inv[3] = {av_ok[0] ? 1.0f / avx : 0.0f, av_ok[1] ? 1.0f / avy : 0.0f,
                              av_ok[2] ? 1.0f / avz : 0.0f};
@@ -885,10 +887,13 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         const float dzc = r20 * kc0 + r21 * kc1 + r22 * kc2;
         const float ey = 0.5f * hist_w * (fabsf(r10) + fabsf(r11) + fabsf(r12));
         const float ez = 0.5f * hist_w * (fabsf(r20) + fabsf(r21) + fabsf(r22));
-        const int ya = max(y0, (int) floorf(cy + (dyc - ey) * iyu) - 2);
-        const int yb = min(y1, (int) ceilf(cy + (dyc + ey) * iyu) + 2);
-        const int za = max(z0, (int) floorf(cz + (dzc - ez) * izu) - 2);
-        const int zb = min(z1, (int) ceilf(cz + (dzc + ez) * izu) + 2);
+        // (integer part of the centre + offset: the row box, and with it the order in which
+        // voxels are summed, does not change when the volume is translated by whole voxels --
+        // a z-slab of a taller volume gives the same bits as the volume itself)
+        const int ya = max(y0, cyi + (int) floorf(cyf + (dyc - ey) * iyu) - 2);
+        const int yb = min(y1, cyi + (int) ceilf(cyf + (dyc + ey) * iyu) + 2);
+        const int za = max(z0, czi + (int) floorf(czf + (dzc - ez) * izu) - 2);
+        const int zb = min(z1, czi + (int) ceilf(czf + (dzc + ez) * izu) + 2);
         const int wyc = yb - ya + 1, wzc = zb - za + 1;
         if (wyc <= 0 || wzc <= 0 || x1 < x0) continue;
         const int nrows = wyc * wzc;

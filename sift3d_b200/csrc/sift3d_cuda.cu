@@ -439,9 +439,57 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     // octave o + 1 starts as soon as its seed level (2x decimation of level ds_level of octave
     // o, fused into that blur's epilogue) exists, while octave o finishes its upper levels.
     const int ds_level = (nlev - 2) - 2 > -1 ? (nlev - 2) - 2 : -1;  // sift.c:696-697
-    auto stream_of = [&](int o) { return (o == 0 || serial) ? st : ctx->oct_stream[o]; };
+    // Octaves of at most kTinyMaxVox voxels (and everything after them) run as one chain
+    // kernel on the stream of the first of them.
+    int tiny_from = -1;
+    static const bool no_tiny = getenv("SIFT3D_CUDA_NO_TINY") != nullptr;
+    if (!slab && !no_tiny) {
+        for (int o = from_seed ? 0 : 1; o < noct; o++)
+            if (ctx->level(o, 0).nvox() <= (size_t) kTinyMaxVox) {
+                if (noct - o <= kTinyMaxOct) tiny_from = o;
+                break;
+            }
+    }
+    auto stream_of = [&](int o) {
+        if (o == 0 || serial) return st;
+        return ctx->oct_stream[tiny_from >= 0 && o > tiny_from ? tiny_from : o];
+    };
+    auto run_tiny = [&](cudaStream_t so) -> int {
+        TinyChainParams T;
+        memset(&T, 0, sizeof(T));
+        T.noct = noct - tiny_from;
+        T.nfilt = nlev - 1;
+        T.ds_level = ds_level;
+        for (int i = 0; i < T.nfilt; i++) {
+            T.taps[i] = ctx->d_taps(i);
+            T.hw[i] = D.octave[i].width / 2;
+        }
+        for (int t = 0; t < T.noct; t++) {
+            const int o = tiny_from + t;
+            const Level &L = ctx->level(o, 0);
+            TinyOctave &O = T.oct[t];
+            O.nx = L.nx; O.ny = L.ny; O.nz = L.nz;
+            tiny_axis(L.nx, L.ux, &O.uf[0], &O.sh[0]);
+            tiny_axis(L.ny, L.uy, &O.uf[1], &O.sh[1]);
+            tiny_axis(L.nz, L.uz, &O.uf[2], &O.sh[2]);
+            for (int i = 0; i <= T.nfilt; i++) O.lvl[i] = ctx->level(o, i - 1).d;
+            for (int i = 0; i < T.nfilt; i++)
+                O.dogmax[i] = (i - 1 >= 0 && i - 1 < kp)
+                                  ? ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (i - 1)) : nullptr;
+        }
+        return launch_tiny_octaves(so, T, &ctx->launches);
+    };
     auto run_level = [&](int o, int s) -> int {  // blur that produces level (o, s)
         cudaStream_t so = stream_of(o);
+        if (tiny_from >= 0 && o >= tiny_from) {
+            const size_t li = (size_t) o * nlev + (s + 1);
+            if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li], so));
+            const bool first = o == tiny_from && s == 0;
+            if (first && run_tiny(so)) return -1;
+            if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], so));
+            ctx->blur_launches[li] = first ? 1 : 0;
+            return 0;
+        }
         float *ta, *tb;
         if (o == 0) {
             ta = (float *) ctx->tmp_a.p;
