@@ -148,6 +148,7 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
     const int total = wx * wy * wz;
     const double rad2 = rad * rad;
     const double sig2 = sigma * sigma;
+    const double nhs = -0.5 / sig2;  // one division per candidate instead of one per voxel
     const float ixu = __fdiv_rn(1.0f, uxf), iyu = __fdiv_rn(1.0f, uyf), izu = __fdiv_rn(1.0f, uzf);
     const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
 
@@ -174,7 +175,7 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
             if ((double) sq > rad2) continue;
             // weight = expf(-0.5 * sq_dist / (sigma * sigma)): the argument is evaluated in
             // double and narrowed to float (sift.c:972); expf itself in fp32 (<= 2 ulp)
-            const float arg = (float) (-0.5 * (double) sq / sig2);
+            const float arg = (float) ((double) sq * nhs);  // -0.5 * sq / sigma^2 in double
             const float w = expf(arg);
             float vx = __fmul_rn(0.5f, __fsub_rn(row[x + 1], row[x - 1]));
             float vy = __fmul_rn(0.5f, __fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys]));
@@ -184,12 +185,14 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
             vz = __fmul_rn(vz, izu);
             const double wd = (double) w;
             const double dvx = (double) vx, dvy = (double) vy, dvz = (double) vz;
-            a00 += dvx * dvx * wd;
-            a01 += dvx * dvy * wd;
-            a02 += dvx * dvz * wd;
-            a11 += dvy * dvy * wd;
-            a12 += dvy * dvz * wd;
-            a22 += dvz * dvz * wd;
+            // structure tensor (sift.c:978-986) with the weight folded in once per row
+            const double wx = dvx * wd, wy = dvy * wd, wz = dvz * wd;
+            a00 = fma(dvx, wx, a00);
+            a01 = fma(dvx, wy, a01);
+            a02 = fma(dvx, wz, a02);
+            a11 = fma(dvy, wy, a11);
+            a12 = fma(dvy, wz, a12);
+            a22 = fma(dvz, wz, a22);
             gx += (double) __fmul_rn(vx, w);
             gy += (double) __fmul_rn(vy, w);
             gz += (double) __fmul_rn(vz, w);
