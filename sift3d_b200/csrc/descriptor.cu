@@ -21,6 +21,9 @@ constexpr int kVerts = 12;
 constexpr int kHistPerDim = 4;
 constexpr int kDescNumel = SIFT3D_CUDA_DESC_NUMEL;
 constexpr double kBaryEps = (double) FLT_EPSILON * 1E1;  // sift.c:40
+// 10 * 2^-23 is a float, so for a float x the reference's (double) x < BARY_EPS is x < kBaryEpsF
+constexpr float kBaryEpsF = FLT_EPSILON * 10.0f;
+static_assert((double) kBaryEpsF == kBaryEps, "BARY_EPS must be exactly representable in fp32");
 constexpr double kDescRadFctr = 2.0;                     // sift.c:44
 
 // Per-face constants of cart2bary that do not depend on the query vector.
@@ -395,7 +398,7 @@ __device__ __forceinline__ bool face_hit_s(const float *__restrict__ fm, float g
     const float py = __fsub_rn(__fmul_rn(gz, e2x), __fmul_rn(gx, e2z));
     const float pz = __fsub_rn(__fmul_rn(gx, e2y), __fmul_rn(gy, e2x));
     const float det = __fadd_rn(__fadd_rn(__fmul_rn(m0.x, px), __fmul_rn(m0.y, py)), __fmul_rn(m0.z, pz));
-    if ((double) fabsf(det) < kBaryEps) return false;
+    if (fabsf(det) < kBaryEpsF) return false;
     const float det_inv = __frcp_rn(det);  // == 1.0f / det, correctly rounded
     const float tp = __fadd_rn(__fadd_rn(__fmul_rn(m1.z, px), __fmul_rn(m1.w, py)), __fmul_rn(m2.x, pz));
     const float cq = __fadd_rn(__fadd_rn(__fmul_rn(gx, m2.y), __fmul_rn(gy, m2.z)), __fmul_rn(gz, m2.w));
@@ -403,7 +406,7 @@ __device__ __forceinline__ bool face_hit_s(const float *__restrict__ fm, float g
     bz = __fmul_rn(det_inv, cq);
     bx = __fsub_rn(__fsub_rn(1.0f, by), bz);
     const float k = __fmul_rn(e2q, det_inv);
-    if ((double) bx < -kBaryEps || (double) by < -kBaryEps || (double) bz < -kBaryEps || k < 0.0f)
+    if (bx < -kBaryEpsF || by < -kBaryEpsF || bz < -kBaryEpsF || k < 0.0f)
         return false;
     return true;
 }
@@ -1058,7 +1061,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             const float rz2 = __fadd_rn(__fadd_rn(__fmul_rn(r02, gx), __fmul_rn(r12, gy)), __fmul_rn(r22, gz));
             // icos_hist_bin (sift.c:1254-1291)
             const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry2, ry2)), __fmul_rn(rz2, rz2));
-            ok = ok && !((double) n2 < kBaryEps);
+            ok = ok && !(n2 < kBaryEpsF);
             // nearest face centre among the 4 candidates of this octant (selection only)
             const float ax = fabsf(rx), ay = fabsf(ry2), az = fabsf(rz2);
             const float kA = 2.6180339887f, kB = 1.6180339887f, kC = 4.2360679775f;  // 1+phi, phi, 2phi+1
