@@ -569,6 +569,11 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
                            (Cand *) ctx->cand_raw.p + ctx->cand_base[o], ctx->cand_cap[o],
                            (int *) ctx->counts.p + o, &ctx->launches, zr0(o), zr1(o)))
             return -1;
+        // octaves >= 1 are put into scan order on their own stream, off the critical path
+        if (o >= 1 && launch_order_all(so, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
+                                       ctx->cand_base.data(), ctx->cand_cap.data(), noct,
+                                       (const int *) ctx->counts.p, &ctx->launches, o, o + 1))
+            return -1;
         if (so != st) S3D_CK(cudaEventRecord(ctx->ev_done[o], so));
     }
     // scan order (o, s, z, y, x) and assign_orientations (sift.c:1109-1143), candidate counts
@@ -608,10 +613,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         return -1;
     if (!serial)
         for (int o = 1; o < noct; o++) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_done[o], 0));
-    if (launch_order_all(st, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
-                         ctx->cand_base.data(), ctx->cand_cap.data(), noct,
-                         (const int *) ctx->counts.p, &ctx->launches, split, noct) ||
-        launch_orient_all(st, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
+    if (launch_orient_all(st, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
                           (const int *) ctx->counts.p, (int *) ctx->work.p + 1, corner_thresh,
                           (sift3d_cuda_keypoint *) ctx->kps.p, &ctx->launches, split, noct))
         return -1;
