@@ -90,7 +90,8 @@ int launch_absdiffmax(cudaStream_t st, const float *a, const float *b, size_t n,
 // extrema.cu
 int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, int nx, int ny,
                    int nz, const float *d_dogmax, double peak_thresh, Cand *d_cand, int cap,
-                   int *d_count, uint64_t *launches, int z0 = 0, int z1 = -1);  // planes [z0, z1)
+                   int *d_count, uint64_t *launches, int z0 = 0, int z1 = -1,
+                   int s_begin = 0, int s_end = -1)  /* keypoint levels [s_begin, s_end) */;  // planes [z0, z1)
 // all octaves in one launch; counts stay on the device
 int launch_order_all(cudaStream_t st, const Cand *d_raw, Cand *d_sorted, const int *base,
                      const int *cap, int noct, const int *d_counts, uint64_t *launches,

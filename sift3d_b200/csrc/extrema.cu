@@ -18,6 +18,7 @@ struct ExtremaParams {
     int num_kp_levels;
     int nx, ny, nz;
     int z0, z1;  // planes [z0, z1) are scanned (z-slab mode: the planes this rank owns)
+    int s_off;   // keypoint level of g[1] (a launch may cover a sub-range of the levels)
 };
 
 __global__ void __launch_bounds__(256)
@@ -68,7 +69,7 @@ extrema_kernel(const ExtremaParams P, const float *__restrict__ dogmax, float pe
                 const int pos = base + __popc(ballot & ((1u << lane) - 1u));
                 if (pos < cap) {
                     Cand c;
-                    c.key = ((unsigned long long) s << 60) | ((unsigned long long) z << 40) |
+                    c.key = ((unsigned long long) (s + P.s_off) << 60) | ((unsigned long long) z << 40) |
                             ((unsigned long long) y << 20) | (unsigned long long) x;
                     c.strength = fabsf(v);
                     c.pad = 0;
@@ -142,7 +143,7 @@ extrema_vec4_kernel(const ExtremaParams P, const float *__restrict__ dogmax, dou
             const int bit = __ffs(m) - 1;
             m &= m - 1;
             const int s = bit >> 2, c = bit & 3;
-            items[warp][pos++] = ((unsigned long long) s << 60) | ((unsigned long long) z << 40) |
+            items[warp][pos++] = ((unsigned long long) (s + P.s_off) << 60) | ((unsigned long long) z << 40) |
                                  ((unsigned long long) y << 20) | (unsigned long long) (x4 * 4 + c);
         }
     }
@@ -155,7 +156,7 @@ extrema_vec4_kernel(const ExtremaParams P, const float *__restrict__ dogmax, dou
         float v = 0.0f;
         if (i < total) {
             key = items[warp][i];
-            const int s = (int) (key >> 60);
+            const int s = (int) (key >> 60) - P.s_off;
             const size_t idx = (size_t) ((key >> 40) & 0xFFFFF) * zs + (size_t) ((key >> 20) & 0xFFFFF) * ys +
                                (size_t) (key & 0xFFFFF);
             const float *__restrict__ ga = P.g[s + 1];
@@ -232,13 +233,20 @@ order_all_kernel(const Cand *__restrict__ raw, Cand *__restrict__ sorted, const 
 
 int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, int nx, int ny,
                    int nz, const float *d_dogmax, double peak_thresh, Cand *d_cand, int cap,
-                   int *d_count, uint64_t *launches, int z0, int z1) {
+                   int *d_count, uint64_t *launches, int z0, int z1, int s_begin, int s_end) {
     if (z1 < 0) {
         z0 = 0;
         z1 = nz;
     }
+    // keypoint levels [s_begin, s_end) only: level s needs g[s] .. g[s+3] and dogmax[s]
+    if (s_end < 0) s_end = num_kp_levels;
+    if (s_end <= s_begin) return 0;
+    g += s_begin;
+    d_dogmax += s_begin;
+    num_kp_levels = s_end - s_begin;
     ExtremaParams P;
     for (int i = 0; i < num_kp_levels + 3; i++) P.g[i] = g[i];
+    P.s_off = s_begin;
     P.num_kp_levels = num_kp_levels;
     P.nx = nx;
     P.ny = ny;

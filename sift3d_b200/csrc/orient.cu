@@ -105,7 +105,8 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
         int acc = 0;
         for (int o = 0; o < noct; o++) {
             s_first[o] = acc;
-            acc += min(counts[o], plan->cap[o]);
+            // only this launch's octaves are counted: the others may still be scanning
+            if (o >= o_begin && o < o_end) acc += min(counts[o], plan->cap[o]);
         }
         s_first[noct] = acc;
     }
@@ -265,7 +266,9 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
         }
     }
     kp.valid = ok ? 1 : 0;
-    out[ci] = kp;
+    // results stay in the octave's own region (slot = rank within the octave): octaves are
+    // oriented independently, as each finishes, without knowing the counts of the others
+    out[plan->base[oi] + (ci - s_first[oi])] = kp;
   }  // candidates
 }
 
@@ -275,8 +278,12 @@ int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d
     if (o_end < 0) o_end = SIFT3D_CUDA_MAX_OCTAVES;
     if (o_end <= o_begin) return 0;
     // persistent grid: 148 SMs x the CTAs that fit (94 registers x 128 threads -> 5 per SM)
-    orient_all_kernel<<<kNumSMs * 5, kOrientThreads, 0, st>>>(d_sorted, d_plan, d_counts, d_work,
-                                                          corner_thresh, d_out, o_begin, o_end);
+    // Octave 0 on the main stream: persistent grid (148 SMs x the CTAs that fit). Other octaves
+    // run on side streams while octave 0's one-wave blurs still need whole SMs: many short
+    // CTAs (about one candidate each) so that an SM is never held for long.
+    const int grid = o_begin == 0 ? kNumSMs * 5 : kNumSMs * 8;
+    orient_all_kernel<<<grid, kOrientThreads, 0, st>>>(d_sorted, d_plan, d_counts, d_work, corner_thresh,
+                                                   d_out, o_begin, o_end);
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
     return 0;

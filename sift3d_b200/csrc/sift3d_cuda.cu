@@ -312,7 +312,7 @@ int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
             }
         }
         if (ctx->tmp_side.ensure((side_total + 64) * sizeof(float)) ||
-            ctx->orient_plan.ensure(sizeof(OrientPlan)) || ctx->work.ensure(sizeof(int) * 4))
+            ctx->orient_plan.ensure(sizeof(OrientPlan)) || ctx->work.ensure(sizeof(int) * 64))
             return -1;
     }
 
@@ -432,7 +432,28 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         }
     }
     S3D_CK(cudaMemsetAsync(ctx->counts.p, 0, sizeof(int) * 64, st));
-    S3D_CK(cudaMemsetAsync(ctx->work.p, 0, sizeof(int) * 4, st));
+    S3D_CK(cudaMemsetAsync(ctx->work.p, 0, sizeof(int) * 64, st));
+    // what the per-candidate kernels need to know about each octave (read by every octave's
+    // orientation pass, so it is uploaded before any side stream starts)
+    {
+        OrientPlan &H = *ctx->h_plan;
+        memset(&H, 0, sizeof(H));
+        H.noct = noct;
+        for (int o = 0; o < noct; o++) {
+            OctaveInfo &info = H.oct[o];
+            for (int s = 0; s < kp; s++) {
+                info.lvl[s] = ctx->level(o, s).d;
+                info.sd[s] = ctx->level(o, s).scale;
+            }
+            Level &L = ctx->level(o, 0);
+            info.o = o + ctx->base_octave;
+            info.nx = L.nx; info.ny = L.ny; info.nz = L.nz;
+            info.ux = (float) L.ux; info.uy = (float) L.uy; info.uz = (float) L.uz;
+            H.base[o] = ctx->cand_base[o];
+            H.cap[o] = ctx->cand_cap[o];
+        }
+        S3D_CK(cudaMemcpyAsync(ctx->orient_plan.p, &H, sizeof(H), cudaMemcpyHostToDevice, st));
+    }
     S3D_CK(cudaEventRecord(ctx->ev[EV_SCALE], st));
 
     // build_gpyr (sift.c:662-711) + detect_extrema (sift.c:735-871), one octave per stream:
@@ -537,11 +558,26 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         }
         return 0;
     };
+    // Extrema of octave o, keypoint levels [s_begin, s_end)
+    auto run_extrema = [&](int o, int s_begin, int s_end) -> int {
+        const float *g[SIFT3D_CUDA_MAX_FILTERS + 1];
+        for (int s = -1; s < nlev - 1; s++) g[s + 1] = ctx->level(o, s).d;
+        Level &L = ctx->level(o, 0);
+        return launch_extrema(stream_of(o), g, kp, L.nx, L.ny, L.nz,
+                              ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS), peak_thresh,
+                              (Cand *) ctx->cand_raw.p + ctx->cand_base[o], ctx->cand_cap[o],
+                              (int *) ctx->counts.p + o, &ctx->launches, zr0(o), zr1(o), s_begin, s_end);
+    };
+    // Keypoint levels of octave 0 whose four Gaussian levels exist once the seed level does
+    // (level s needs G(s-1) .. G(s+2)): scanned while octave 0 waits for octave 1's seed
+    // chain, instead of on the critical path after the last blur.
+    const int early_levels = (!slab && noct > 1) ? (ds_level - 1 > 0 ? (ds_level - 1 < kp ? ds_level - 1 : kp) : 0) : 0;
     // Phase A, the critical chain: every octave up to the level that seeds the next one.
     for (int o = 0; o < noct; o++) {
         if (o > 0 && !serial) S3D_CK(cudaStreamWaitEvent(stream_of(o), ctx->ev_seed[o - 1], 0));
         for (int s = (o == 0 && !from_seed ? -1 : 0); s <= ds_level && s < nlev - 1; s++)
             if (run_level(o, s)) return -1;
+        if (o == 0 && early_levels > 0 && run_extrema(0, 0, early_levels)) return -1;
     }
     // Phase B, the bulk: remaining levels and the extrema scan of each octave. Octave 0's
     // one-wave kernels would otherwise occupy every SM while octave 1 still has to produce
@@ -561,62 +597,26 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     }
     for (int o = 0; o < noct; o++) {
         cudaStream_t so = stream_of(o);
-        const float *g[SIFT3D_CUDA_MAX_FILTERS + 1];
-        for (int s = -1; s < nlev - 1; s++) g[s + 1] = ctx->level(o, s).d;
-        Level &L = ctx->level(o, 0);
-        if (launch_extrema(so, g, kp, L.nx, L.ny, L.nz,
-                           ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS), peak_thresh,
-                           (Cand *) ctx->cand_raw.p + ctx->cand_base[o], ctx->cand_cap[o],
-                           (int *) ctx->counts.p + o, &ctx->launches, zr0(o), zr1(o)))
+        if (run_extrema(o, o == 0 ? early_levels : 0, kp)) return -1;
+        // Scan order (o, s, z, y, x) and assign_orientations (sift.c:1109-1143) per octave, on
+        // the octave's own stream as soon as its extrema exist: candidate counts are read on
+        // the device and results go to the octave's own region, so no octave waits for another.
+        // (At 256^3 three quarters of the candidates are in octaves >= 1, which finish long
+        // before octave 0 -- orienting everything after the last octave cost 0.2 ms.)
+        if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_EXTREMA], st));
+        if (launch_order_all(so, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
+                             ctx->cand_base.data(), ctx->cand_cap.data(), noct,
+                             (const int *) ctx->counts.p, &ctx->launches, o, o + 1))
             return -1;
-        // octaves >= 1 are put into scan order on their own stream, off the critical path
-        if (o >= 1 && launch_order_all(so, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
-                                       ctx->cand_base.data(), ctx->cand_cap.data(), noct,
-                                       (const int *) ctx->counts.p, &ctx->launches, o, o + 1))
+        if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_ORDER], st));
+        if (launch_orient_all(so, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
+                              (const int *) ctx->counts.p, (int *) ctx->work.p + o, corner_thresh,
+                              (sift3d_cuda_keypoint *) ctx->kps.p, &ctx->launches, o, o + 1))
             return -1;
         if (so != st) S3D_CK(cudaEventRecord(ctx->ev_done[o], so));
     }
-    // scan order (o, s, z, y, x) and assign_orientations (sift.c:1109-1143), candidate counts
-    // read on the device. Octave 0 holds ~90 % of the candidates and finishes its extrema
-    // ~100 us before the chain of small octaves does, so it is ordered and oriented first;
-    // the other octaves follow in a second, short pass (their slots in the output start at
-    // count[0], which is known by then).
-    {
-        OrientPlan &H = *ctx->h_plan;
-        memset(&H, 0, sizeof(H));
-        H.noct = noct;
-        for (int o = 0; o < noct; o++) {
-            OctaveInfo &info = H.oct[o];
-            for (int s = 0; s < kp; s++) {
-                info.lvl[s] = ctx->level(o, s).d;
-                info.sd[s] = ctx->level(o, s).scale;
-            }
-            Level &L = ctx->level(o, 0);
-            info.o = o + ctx->base_octave;
-            info.nx = L.nx; info.ny = L.ny; info.nz = L.nz;
-            info.ux = (float) L.ux; info.uy = (float) L.uy; info.uz = (float) L.uz;
-            H.base[o] = ctx->cand_base[o];
-            H.cap[o] = ctx->cand_cap[o];
-        }
-        S3D_CK(cudaMemcpyAsync(ctx->orient_plan.p, &H, sizeof(H), cudaMemcpyHostToDevice, st));
-    }
-    const int split = noct > 1 ? 1 : noct;
-    S3D_CK(cudaEventRecord(ctx->ev[EV_EXTREMA], st));  // octave 0's extrema are done here
-    if (launch_order_all(st, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
-                         ctx->cand_base.data(), ctx->cand_cap.data(), noct,
-                         (const int *) ctx->counts.p, &ctx->launches, 0, split))
-        return -1;
-    S3D_CK(cudaEventRecord(ctx->ev[EV_ORDER], st));
-    if (launch_orient_all(st, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
-                          (const int *) ctx->counts.p, (int *) ctx->work.p, corner_thresh,
-                          (sift3d_cuda_keypoint *) ctx->kps.p, &ctx->launches, 0, split))
-        return -1;
     if (!serial)
         for (int o = 1; o < noct; o++) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_done[o], 0));
-    if (launch_orient_all(st, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
-                          (const int *) ctx->counts.p, (int *) ctx->work.p + 1, corner_thresh,
-                          (sift3d_cuda_keypoint *) ctx->kps.p, &ctx->launches, split, noct))
-        return -1;
     S3D_CK(cudaMemcpyAsync(ctx->h_counts, ctx->counts.p, sizeof(int) * noct,
                            cudaMemcpyDeviceToHost, st));
     S3D_CK(cudaEventRecord(ctx->ev[EV_ORIENT], st));
@@ -693,9 +693,21 @@ int sift3d_cuda_fetch_candidates(sift3d_cuda_ctx *ctx, sift3d_cuda_keypoint *out
     if (!ctx || !ctx->have_pyramid || (!out && max > 0)) return -1;
     if (set_device(ctx)) return -1;
     int n = ctx->total_candidates < max ? ctx->total_candidates : max;
-    if (n > 0)
-        S3D_CK(cudaMemcpyAsync(out, ctx->kps.p, sizeof(sift3d_cuda_keypoint) * (size_t) n,
-                               cudaMemcpyDeviceToHost, ctx->stream));
+    {
+        // results live in per-octave regions on the device; the caller gets them packed in
+        // scan order (octave-major)
+        int done = 0;
+        for (size_t o = 0; o < ctx->cand_base.size() && done < n; o++) {
+            int c = ctx->h_counts[o];
+            if (c > n - done) c = n - done;
+            if (c > 0)
+                S3D_CK(cudaMemcpyAsync(out + done,
+                                       (const sift3d_cuda_keypoint *) ctx->kps.p + ctx->cand_base[o],
+                                       sizeof(sift3d_cuda_keypoint) * (size_t) c, cudaMemcpyDeviceToHost,
+                                       ctx->stream));
+            done += c;
+        }
+    }
     S3D_CK(cudaEventRecord(ctx->ev[EV_D2H], ctx->stream));
     S3D_CK(cudaStreamSynchronize(ctx->stream));
     float ms;
