@@ -299,8 +299,84 @@ static EncodeTiledFn encode_tiled_fn() {
     return fn;
 }
 
+// Cut the flattened (column tile, output plane) space of the fused unit-spacing kernel into
+// one contiguous range per CTA with equal COST: a chunk (the part of a range inside one
+// tile) costs its outputs plus the 2*hw halo planes that warm its z window up (plus the
+// hw + 2 prologue planes of a chunk that ends at the top of the volume). Equal z-chunks per
+// tile would leave 148 mod tiles SMs idle (128 of 148 CTAs at 256^3). Chunks hold at least
+// hw + 1 outputs: a chunk below the top must not reach plane nz-1 with its halo.
+static bool fill_chunk_table(ChunkTable &t, int ncta, int tiles, int nzr, int hw, bool top_is_volume_top,
+                             int budget, int *max_cost) {
+    const int minlen = hw + 1 < nzr ? hw + 1 : nzr;
+    const long total = (long) tiles * nzr;
+    long pos = 0;
+    int worst = 0;
+    t.b[0] = 0;
+    for (int i = 0; i < ncta; i++) {
+        int left = budget, cost = 0;
+        while (pos < total) {
+            const int rem = nzr - (int) (pos % nzr);  // outputs left in this tile
+            const int halo = 2 * hw;
+            int take = left - halo;
+            if (take < minlen) {
+                if (cost > 0) break;
+                take = minlen;
+            }
+            if (take > rem) take = rem;
+            if (rem - take > 0 && rem - take < minlen) {  // never leave a stub behind
+                if (take - (minlen - (rem - take)) >= minlen) take = rem - minlen;
+                else take = rem;
+            }
+            const int c = take + halo + ((take == rem && top_is_volume_top) ? hw + 2 : 0);
+            pos += take;
+            left -= c;
+            cost += c;
+        }
+        t.b[i + 1] = (int) pos;
+        if (cost > worst) worst = cost;
+    }
+    *max_cost = worst;
+    return pos == total;
+}
+
+static const ChunkTable &fused_chunk_table(int ncta, int tiles, int nzr, int hw, bool top) {
+    struct Entry { int ncta, tiles, nzr, hw, top; ChunkTable t; };
+    static thread_local Entry cache[16];
+    static thread_local int used = 0, next = 0;
+    for (int i = 0; i < used; i++) {
+        const Entry &e = cache[i];
+        if (e.ncta == ncta && e.tiles == tiles && e.nzr == nzr && e.hw == hw && e.top == (int) top) return e.t;
+    }
+    Entry &e = cache[next];
+    next = (next + 1) % 16;
+    if (used < 16) used++;
+    e.ncta = ncta; e.tiles = tiles; e.nzr = nzr; e.hw = hw; e.top = (int) top;
+    const long total = (long) tiles * nzr;
+    int budget = (int) ((total + ncta - 1) / ncta) + 2 * hw;
+    ChunkTable best;
+    int best_cost = 0x7fffffff, cost = 0;
+    // the first feasible budget is near optimal; a few more are tried because a range may
+    // overshoot its budget where a tile's remainder would be shorter than a legal chunk
+    for (int tries = 0, feasible = 0; tries < 4096 && feasible < 8; tries++, budget++) {
+        ChunkTable t;
+        if (!fill_chunk_table(t, ncta, tiles, nzr, hw, top, budget, &cost)) continue;
+        feasible++;
+        if (cost < best_cost) {
+            best_cost = cost;
+            best = t;
+        }
+    }
+    if (best_cost == 0x7fffffff) {  // cannot happen (budget = one tile is always feasible)
+        for (int i = 0; i <= ncta; i++) best.b[i] = (int) (total * i / ncta / nzr * nzr);
+        best.b[ncta] = (int) total;
+    }
+    for (int i = ncta + 1; i <= kMaxFusedCtas; i++) best.b[i] = best.b[ncta];
+    e.t = best;
+    return e.t;
+}
+
 template <int HW, int TY>
-static int launch_fused_t(cudaStream_t st, const FusedParams &P, int nzc) {
+static int launch_fused_t(cudaStream_t st, const FusedParams &P, int occ) {
     using C = FusedCfg<HW>;
     constexpr int TROWS = TY + 2 * HW;
     constexpr int TILE_FLOATS = TROWS * C::BW;
@@ -324,8 +400,16 @@ static int launch_fused_t(cudaStream_t st, const FusedParams &P, int nzc) {
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int) SMEM));
         attr_set = true;
     }
-    dim3 grid((unsigned) ((P.nx + kFTX - 1) / kFTX), (unsigned) ((P.ny + TY - 1) / TY), (unsigned) nzc);
-    blur_fused_unit_kernel<HW, TY><<<grid, 8 * TY, SMEM, st>>>(tmap, P);
+    const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
+    const int nzr = P.z1 - P.z0;
+    // one wave of CTAs, but no CTA with less than ~8 outputs of one tile
+    long ncta = (long) kNumSMs * occ;
+    const long most = (long) tiles * (nzr / (HW + 1 > 8 ? HW + 1 : 8) > 0 ? nzr / (HW + 1 > 8 ? HW + 1 : 8) : 1);
+    if (ncta > most) ncta = most;
+    if (ncta > kMaxFusedCtas) ncta = kMaxFusedCtas;
+    if ((long) tiles * nzr > 0x7fffffffL) return 1;
+    const ChunkTable &tab = fused_chunk_table((int) ncta, tiles, nzr, HW, P.z1 == P.nz);
+    blur_fused_unit_kernel<HW, TY><<<(unsigned) ncta, 8 * TY, SMEM, st>>>(tmap, P, tab);
     S3D_CK(cudaGetLastError());
     return 0;
 }
@@ -333,31 +417,16 @@ static int launch_fused_t(cudaStream_t st, const FusedParams &P, int nzc) {
 // Returns 0 if launched, 1 if this blur is not eligible for the fused kernel, -1 on error.
 template <int TY>
 static int launch_fused(cudaStream_t st, FusedParams &P, int hw, int occ) {
-    const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
-    // One wave: as many z-chunks as fit 148 SMs x resident CTAs. Every chunk pays 2*hw halo
-    // planes of x/y work, so chunks are as long as one wave allows. Constraints: a chunk
-    // below the top must not reach plane nz-1 with its halo and a chunk above the bottom
-    // must not reach below plane 0: every chunk holds at least hw + 1 outputs.
-    int nzc = (kNumSMs * occ) / tiles;
-    if (nzc < 1) nzc = 1;
-    const int nzr = P.z1 - P.z0;  // planes to produce
-    int zc = (nzr + nzc - 1) / nzc;
-    if (zc < hw + 1) zc = hw + 1;
-    nzc = (nzr + zc - 1) / zc;
-    while (nzc > 1 && nzr - (nzc - 1) * zc < hw + 1) {
-        zc++;
-        nzc = (nzr + zc - 1) / zc;
-    }
-    P.zchunk = zc;
+    P.zchunk = P.z1 - P.z0;
     switch (hw) {
-    case 1: return launch_fused_t<1, TY>(st, P, nzc);
-    case 2: return launch_fused_t<2, TY>(st, P, nzc);
-    case 3: return launch_fused_t<3, TY>(st, P, nzc);
-    case 4: return launch_fused_t<4, TY>(st, P, nzc);
-    case 5: return launch_fused_t<5, TY>(st, P, nzc);
-    case 6: return launch_fused_t<6, TY>(st, P, nzc);
-    case 7: return launch_fused_t<7, TY>(st, P, nzc);
-    case 8: return launch_fused_t<8, TY>(st, P, nzc);
+    case 1: return launch_fused_t<1, TY>(st, P, occ);
+    case 2: return launch_fused_t<2, TY>(st, P, occ);
+    case 3: return launch_fused_t<3, TY>(st, P, occ);
+    case 4: return launch_fused_t<4, TY>(st, P, occ);
+    case 5: return launch_fused_t<5, TY>(st, P, occ);
+    case 6: return launch_fused_t<6, TY>(st, P, occ);
+    case 7: return launch_fused_t<7, TY>(st, P, occ);
+    case 8: return launch_fused_t<8, TY>(st, P, occ);
     default: return 1;
     }
 }
@@ -456,14 +525,15 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
     if (!force_generic && symmetric && ax.uf == 1.0f && ay.uf == 1.0f && az.uf == 1.0f && hw >= 1 &&
         hw <= 8 && f.width <= kMaxParamTaps && nx % 4 == 0 && nx >= kFTX && ny >= ty &&
         ny >= 2 * hw + 2 && nz >= 2 * hw + 2 && ((uintptr_t) src & 15) == 0 &&
-        (d_dogmax_slot == nullptr || dog_prev == src)) {
+        (d_dogmax_slot == nullptr || dog_prev == src) &&
+        (d_divisor == nullptr || (tmp_a != nullptr && tmp_a != src))) {
         FusedParams P;
         P.src = src;
         P.dst = dst;
         P.ds_dst = ds_dst;
         P.dogmax = d_dogmax_slot;
-        P.divisor = d_divisor;
-        if (d_divisor != nullptr && tmp_a != nullptr && tmp_a != src) {
+        P.divisor = nullptr;
+        if (d_divisor != nullptr) {
             // im_scale (imutil.c:699-713) as its own streaming pass: inside the blur every
             // voxel would be divided once per register window that holds it (3x for this
             // filter) and the reciprocal's latency stalls the tile pipeline (145 us against

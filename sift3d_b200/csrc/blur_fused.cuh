@@ -80,7 +80,7 @@ struct FusedParams {
     float *dst;            // this level
     float *ds_dst;         // next octave's level -1 (2x decimation of dst) or nullptr
     float *dogmax;         // slot for max|src - dst| or nullptr
-    const float *divisor;  // im_scale divisor applied to src on load, or nullptr
+    const float *divisor;  // unused by the fused kernels (im_scale runs as its own pass)
     int nx, ny, nz;
     int z0, z1;            // output planes [z0, z1)
     int zorg;              // z-slab: plane of the whole volume that array plane 0 is (else 0)
@@ -125,7 +125,7 @@ __device__ __forceinline__ constexpr int fold(int t) {
 template <int HW>
 __device__ __forceinline__ float4 xrow(const float *__restrict__ trow, const int gg, const bool left,
                                        const bool right, const float *__restrict__ frx,
-                                       const bool scale, const float dv, const TapsParam &k) {
+                                       const TapsParam &k) {
     using C = FusedCfg<HW>;
     constexpr int NW = C::NW, HWP = C::HWP, NIN = C::NIN;
     float in[NIN];
@@ -134,10 +134,6 @@ __device__ __forceinline__ float4 xrow(const float *__restrict__ trow, const int
     for (int q = 0; q < NIN / 4; q++) {
         const float4 t4 = s4[q];
         in[4 * q] = t4.x; in[4 * q + 1] = t4.y; in[4 * q + 2] = t4.z; in[4 * q + 3] = t4.w;
-    }
-    if (scale) {  // im_scale: v / max (imutil.c:710-712), first blur only
-#pragma unroll
-        for (int j = 0; j < NIN; j++) in[j] = __fdiv_rn(in[j], dv);
     }
     if (left) {  // E[-i] = E[i]: input j of group GG sits at x = 4*GG + j - HWP
 #pragma unroll
@@ -186,11 +182,21 @@ __device__ __forceinline__ float zfeed(float (&A)[2 * HW], const float v, const 
     return out;
 }
 
+// Chunk table: CTA i produces the outputs [b[i], b[i+1]) of the flattened (column tile,
+// output plane) space, tile-major: unit u is plane z0 + u % nzr of tile u / nzr. The host
+// cuts the space so that every CTA has the same cost (outputs + 2*HW halo planes per chunk,
+// a chunk being the part of a CTA's range inside one tile), see fused_chunk_table().
+constexpr int kMaxFusedCtas = 2 * kNumSMs;
+struct ChunkTable {
+    int b[kMaxFusedCtas + 1];
+};
+
 // Fused blur, unit tap spacing on all three axes. Block = 32 x TY/4 threads: thread
 // (lane, w) owns column x0 + lane, rows y0 + 4w .. 4w+3 in the y and z passes.
 template <int HW, int TY>
 __global__ void __launch_bounds__(8 * TY, TY == 64 ? 1 : 2)
-blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedParams P) {
+blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ FusedParams P,
+                       const __grid_constant__ ChunkTable tab) {
     using C = FusedCfg<HW>;
     constexpr int NT = 8 * TY;
     constexpr int HWP = C::HWP, BW = C::BW, NINY = C::NINY;
@@ -200,7 +206,7 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
     constexpr int TILE_STRIDE = (TILE_FLOATS + 31) / 32 * 32;  // 128-byte aligned TMA destinations
     constexpr int XF_FLOATS = TROWS * kFTX;
     constexpr int NITEMS = TROWS * 8;
-    constexpr int ROT = (TROWS - NT / 8 % TROWS) % TROWS;  // see the x-pass loop
+    constexpr int ROT = (TROWS - NT / 8 % TROWS) % TROWS;  // see the x-pass items
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float *tile = reinterpret_cast<float *>(smem_raw);                 // [kNB][TROWS][BW]
@@ -212,33 +218,13 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
 
     const int tid = threadIdx.x;
     const int lane = tid & 31, w = tid >> 5;
+    const int gg = tid & 7;
     const int nx = P.nx, ny = P.ny, nz = P.nz;
-    // tiles are shifted inwards at the high edges so every tile is full
-    const int x0 = min((int) blockIdx.x * kFTX, nx - kFTX);
-    const int y0 = min((int) blockIdx.y * TY, ny - TY);
-    const bool xleft = x0 == 0, xright = x0 == nx - kFTX;
-    const bool ybot = y0 == 0, ytop = y0 == ny - TY;
     const int dex = nx - 1, dey = ny - 1, dez = nz - 1;
-    const int zb = P.z0 + blockIdx.z * P.zchunk;  // outputs [P.z0, P.z1): the whole volume, or the
-    const int ze = min(zb + P.zchunk, P.z1);       // planes this rank owns in z-slab mode
-    const bool top = ze == nz;
-
-    // Stream of fed positions q (z_out = q + HW). Top chunk: a prologue walks planes
-    // dez-HW-1 .. dez upwards to build the virtual planes dez+HW .. dez (fed in that order),
-    // then the main stream feeds real planes dez-1 downwards. Other chunks: planes
-    // ze-1+HW downwards. Negative positions reflect (plane -q).
-    const int npro = top ? HW + 2 : 0;
-    const int qstart = top ? dez - 1 : ze - 1 + HW;
-    const int N = npro + (qstart - (zb - HW) + 1);
-    auto plane_of = [&](int n) -> int {
-        if (n < npro) return dez - HW - 1 + n;
-        const int q = qstart - (n - npro);
-        return q < 0 ? -q : q;
-    };
-
-    float dv = 0.0f;
-    if (P.divisor != nullptr) dv = *P.divisor;
-    const bool scale = dv != 0.0f;
+    const int nzr = P.z1 - P.z0;
+    const int ntx = (nx + kFTX - 1) / kFTX;
+    const size_t plane_stride = (size_t) nx * ny;
+    const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
 
     if (tid == 0) {
 #pragma unroll
@@ -250,89 +236,121 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
         fry[tid] = right_frac(dey, tid);
     }
     __syncthreads();
-    auto issue = [&](int n) {  // stage stream element n into buffer n % kNB (one thread)
-        const int b = n % kNB;
-        mbar_expect_tx(&mbar[b], TILE_BYTES);
-        tma_load_3d(tile + b * TILE_STRIDE, &tmap, x0 - HWP, y0 - HW, plane_of(n), &mbar[b]);
-    };
-    if (tid == 0) {
-        for (int n = 0; n < kNB && n < N; n++) issue(n);
-    }
 
-    float A[4][2 * HW];
-#pragma unroll
-    for (int c = 0; c < 4; c++)
-#pragma unroll
-        for (int t = 0; t < 2 * HW; t++) A[c][t] = 0.0f;
-    float prev[4] = {0.f, 0.f, 0.f, 0.f};
-    float vmax = 0.0f;
-
-    // ---- plane-invariant x-pass work of this thread: up to 2 items (tile row, 4-column
-    // group). Item k covers tile row ((tid + k*NT) >> 3) + ROT: the rotation hands the top
-    // tile's virtual rows (two source rows each) to threads that own a single item.
-    // offA = float offset of the source row in the tile, offB >= 0: result is
-    // lerp(row offB, row offA, frI) (the "- 0.1" right mirror, imutil.c:846-849).
-    constexpr int kItems = (NITEMS + NT - 1) / NT;
-    static_assert(kItems <= 2, "tile has at most 2 x-pass items per thread");
-    int offA[kItems], offB[kItems], offD[kItems];
-    float frI[kItems];
-    const int gg = tid & 7;
-#pragma unroll
-    for (int k = 0; k < kItems; k++) {
-        const int it = tid + k * NT;
-        int r = (it >> 3) + ROT;
-        if (r >= TROWS) r -= TROWS;
-        const int gy = y0 - HW + r;
-        int ra = r, rb = -1;
-        float fr = 0.0f;
-        if (gy < 0) {
-            ra = r - 2 * gy;  // mirror: row -gy
-        } else if (gy >= dey) {
-            const int m = gy - dey;  // virtual row dey + m; only the top tile's outputs use it
-            if (ytop) {
-                ra = r - 2 * m;
-                rb = r - 2 * m - 1;
-                fr = fry[m];
-            } else {
-                ra = -1;
-            }
-        }
-        if (it >= NITEMS) ra = -1;
-        offA[k] = ra >= 0 ? ra * BW : -1;
-        offB[k] = rb >= 0 ? rb * BW : -1;
-        offD[k] = r * kFTX + 4 * gg;
-        frI[k] = fr;
-    }
-
-    // ---- which outputs this thread stores: edge outputs belong to the tiles at the static
-    // edge positions (first / last), see xrow()
-    const int x = x0 + lane;
-    const bool xok = (xleft || x >= HW) && (xright || x + HW < dex);
-    const int ybase = y0 + 4 * w;
-    unsigned smask = 0;
-#pragma unroll
-    for (int c = 0; c < 4; c++) {
-        const int y = ybase + c;
-        if (xok && (ybot || y >= HW) && (ytop || y + HW < dey)) smask |= 1u << c;
-    }
-    const size_t plane_stride = (size_t) nx * ny;
-    const size_t col_off = (size_t) ybase * nx + (size_t) x;  // row c adds c * nx
-    // decimation targets: even z, even rows, even x
-    const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
-    unsigned dmask = 0;
-    if (P.ds_dst != nullptr && !(x & 1) && (x >> 1) < dnx) {
-#pragma unroll
-        for (int c = 0; c < 4; c++)
-            if ((smask & (1u << c)) && !((ybase + c) & 1) && ((ybase + c) >> 1) < dny) dmask |= 1u << c;
-    }
-    const size_t ds_col = (size_t) (ybase >> 1) * dnx + (size_t) (x >> 1);
-
+    // Tile buffers are filled and drained in the same cyclic order over the whole kernel
+    // (every chunk issues and consumes exactly its N stream elements), so the positions
+    // simply carry over from chunk to chunk.
+    int ib_buf = 0;          // (thread 0) tile buffer the next TMA load goes to
     int xb_buf = 0;          // tile buffer of the element the x pass consumes next
     uint32_t xb_par = 0;     // and its mbarrier phase parity
-    for (int n = -1; n < N; n++) {
-        // ---- x pass of stream element n + 1 into xf[(n + 1) & 1]
-        if (n + 1 < N) {
-            const int e = n + 1;
+    float vmax = 0.0f;
+
+    int pos = tab.b[blockIdx.x];
+    const int pend = tab.b[blockIdx.x + 1];
+    while (pos < pend) {
+        const int tl = pos / nzr;
+        const int zoff = pos - tl * nzr;
+        const int zlen = min(pend - pos, nzr - zoff);
+        pos += zlen;
+        const int tyi = tl / ntx, txi = tl - tyi * ntx;
+        // tiles are shifted inwards at the high edges so every tile is full
+        const int x0 = min(txi * kFTX, nx - kFTX);
+        const int y0 = min(tyi * TY, ny - TY);
+        const bool xleft = x0 == 0, xright = x0 == nx - kFTX;
+        const bool ybot = y0 == 0, ytop = y0 == ny - TY;
+        const int zb = P.z0 + zoff;  // outputs [zb, ze) of this tile
+        const int ze = zb + zlen;
+        const bool top = ze == nz;
+
+        // Stream of fed positions q (z_out = q + HW). Top chunk: a prologue walks planes
+        // dez-HW-1 .. dez upwards to build the virtual planes dez+HW .. dez (fed in that
+        // order), then the main stream feeds real planes dez-1 downwards. Other chunks:
+        // planes ze-1+HW downwards. Negative positions reflect (plane -q).
+        const int npro = top ? HW + 2 : 0;
+        const int qstart = top ? dez - 1 : ze - 1 + HW;
+        const int N = npro + (qstart - (zb - HW) + 1);
+        auto plane_of = [&](int n) -> int {
+            if (n < npro) return dez - HW - 1 + n;
+            const int q = qstart - (n - npro);
+            return q < 0 ? -q : q;
+        };
+        auto issue = [&](int n) {  // stage stream element n (thread 0 only)
+            mbar_expect_tx(&mbar[ib_buf], TILE_BYTES);
+            tma_load_3d(tile + ib_buf * TILE_STRIDE, &tmap, x0 - HWP, y0 - HW, plane_of(n), &mbar[ib_buf]);
+            if (++ib_buf == kNB) ib_buf = 0;
+        };
+        if (tid == 0) {
+            for (int n = 0; n < kNB && n < N; n++) issue(n);
+        }
+
+        float A[4][2 * HW];
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+#pragma unroll
+            for (int t = 0; t < 2 * HW; t++) A[c][t] = 0.0f;
+
+        // ---- chunk-invariant x-pass work of this thread: up to 2 items (tile row, 4-column
+        // group). Item k covers tile row ((tid + k*NT) >> 3) + ROT: the rotation hands the top
+        // tile's virtual rows (two source rows each) to threads that own a single item.
+        // offA = float offset of the source row in the tile, offB >= 0: result is
+        // lerp(row offB, row offA, frI) (the "- 0.1" right mirror, imutil.c:846-849).
+        constexpr int kItems = (NITEMS + NT - 1) / NT;
+        static_assert(kItems <= 2, "tile has at most 2 x-pass items per thread");
+        int offA[kItems], offB[kItems], offD[kItems];
+        float frI[kItems];
+#pragma unroll
+        for (int k = 0; k < kItems; k++) {
+            const int it = tid + k * NT;
+            int r = (it >> 3) + ROT;
+            if (r >= TROWS) r -= TROWS;
+            const int gy = y0 - HW + r;
+            int ra = r, rb = -1;
+            float fr = 0.0f;
+            if (gy < 0) {
+                ra = r - 2 * gy;  // mirror: row -gy
+            } else if (gy >= dey) {
+                const int m = gy - dey;  // virtual row dey + m; only the top tile's outputs use it
+                if (ytop) {
+                    ra = r - 2 * m;
+                    rb = r - 2 * m - 1;
+                    fr = fry[m];
+                } else {
+                    ra = -1;
+                }
+            }
+            if (it >= NITEMS) ra = -1;
+            offA[k] = ra >= 0 ? ra * BW : -1;
+            offB[k] = rb >= 0 ? rb * BW : -1;
+            offD[k] = r * kFTX + 4 * gg;
+            frI[k] = fr;
+        }
+
+        // ---- which outputs this thread stores: edge outputs belong to the tiles at the static
+        // edge positions (first / last), see xrow()
+        const int x = x0 + lane;
+        const bool xok = (xleft || x >= HW) && (xright || x + HW < dex);
+        const int ybase = y0 + 4 * w;
+        unsigned smask = 0;
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const int y = ybase + c;
+            if (xok && (ybot || y >= HW) && (ytop || y + HW < dey)) smask |= 1u << c;
+        }
+        // decimation targets: even z, even rows, even x
+        unsigned dmask = 0;
+        if (P.ds_dst != nullptr && !(x & 1) && (x >> 1) < dnx) {
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+                if ((smask & (1u << c)) && !((ybase + c) & 1) && ((ybase + c) >> 1) < dny) dmask |= 1u << c;
+        }
+        const size_t ds_col = (size_t) (ybase >> 1) * dnx + (size_t) (x >> 1);
+        // element (ze - 1, ybase, x): the first output stored; one plane down per fed plane
+        const size_t first_off = (size_t) (ze - 1) * plane_stride + (size_t) ybase * nx + (size_t) x;
+        float *dp = P.dst + first_off;
+        const float *sp = P.src + first_off;
+
+        // x pass of stream element e into xf[e & 1]
+        auto xpass = [&](const int e) {
             const float *tb = tile + xb_buf * TILE_STRIDE;
             float *xb = xf + (e & 1) * XF_FLOATS;
             mbar_wait(&mbar[xb_buf], xb_par);
@@ -347,23 +365,22 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
                         *reinterpret_cast<float4 *>(xb + offD[k]) = make_float4(0.f, 0.f, 0.f, 0.f);
                     continue;
                 }
-                float4 o = xrow<HW>(tb + offA[k], gg, xleft, xright, frx, scale, dv, P.taps);
+                float4 o = xrow<HW>(tb + offA[k], gg, xleft, xright, frx, P.taps);
                 if (offB[k] >= 0) {
-                    const float4 a = xrow<HW>(tb + offB[k], gg, xleft, xright, frx, scale, dv, P.taps);
+                    const float4 a = xrow<HW>(tb + offB[k], gg, xleft, xright, frx, P.taps);
                     const float fr = frI[k];
                     o = make_float4(lerp1(a.x, o.x, fr), lerp1(a.y, o.y, fr), lerp1(a.z, o.z, fr),
                                     lerp1(a.w, o.w, fr));
                 }
                 *reinterpret_cast<float4 *>(xb + offD[k]) = o;
             }
-        }
-        if (n >= 0) {
-            // ---- y pass: rows 4w .. 4w+3+2*HW of the x-filtered tile, column `lane`
+        };
+        // y pass of element n: rows 4w .. 4w+3+2*HW of the x-filtered tile, column `lane`
+        auto ypass = [&](const int n, float (&yv)[4]) {
             const float *xb = xf + (n & 1) * XF_FLOATS + (4 * w) * kFTX + lane;
             float in[NINY];
 #pragma unroll
             for (int j = 0; j < NINY; j++) in[j] = xb[j * kFTX];
-            float yv[4];
 #pragma unroll
             for (int c = 0; c < 4; c++) {
                 float a = 0.0f;
@@ -372,62 +389,70 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const FusedPara
                     a = __fadd_rn(a, __fmul_rn(P.taps.k[fold<HW>(t)], in[c + 2 * HW - t]));
                 yv[c] = a;
             }
+        };
+        auto plane_end = [&](const int n) {
+            __syncthreads();
+            // the tile buffer of element n+1 was consumed by xpass(n+1): refill it
+            if (tid == 0 && n + 1 + kNB < N) issue(n + 1 + kNB);
+        };
 
-            // ---- z pass
-            int q;
-            bool feed = true;
-            if (n < npro) {
-                const int m = HW + 1 - n;  // plane dez - m
-                q = dez + m;
-                if (n == 0) {
-                    feed = false;
-#pragma unroll
-                    for (int c = 0; c < 4; c++) prev[c] = yv[c];
-                } else {
-                    const float fr = right_frac(dez + P.zorg, m);
+        xpass(0);
+        plane_end(-1);
+        int n = 0;
+        if (top) {
+            // ---- prologue (top chunk): y-filtered planes dez-HW-1 .. dez, ascending; from the
+            // second one on, the virtual plane dez + m = lerp(plane dez-m-1, plane dez-m) is fed
+            float prev[4] = {0.f, 0.f, 0.f, 0.f};
+            for (; n < npro; n++) {
+                xpass(n + 1);  // the main stream is never empty
+                float yv[4];
+                ypass(n, yv);
+                if (n > 0) {
+                    const float fr = right_frac(dez + P.zorg, HW + 1 - n);
 #pragma unroll
                     for (int c = 0; c < 4; c++) {
-                        const float cur = yv[c];
-                        yv[c] = lerp1(prev[c], cur, fr);
-                        prev[c] = cur;
+                        const float v = lerp1(prev[c], yv[c], fr);
+                        (void) zfeed<HW>(A[c], v, P.taps);  // outputs beyond the volume
                     }
                 }
-            } else {
-                q = qstart - (n - npro);
-            }
-            if (feed) {
-                float o[4];
 #pragma unroll
-                for (int c = 0; c < 4; c++) o[c] = zfeed<HW>(A[c], yv[c], P.taps);
-                const int z = q + HW;
-                if (z >= zb && z < ze) {
-                    // element offset of (z, ybase, x): 32-bit row steps keep the address math short
-                    const size_t base = (size_t) z * plane_stride + col_off;
-                    float *dp = P.dst + base;
+                for (int c = 0; c < 4; c++) prev[c] = yv[c];
+                plane_end(n);
+            }
+        }
+        // ---- main stream: the first fed planes only warm the window up (their outputs lie
+        // at or above ze); from then on every plane completes the output one plane lower
+        int zo = qstart + HW;  // output completed by element n
+        for (; n < N; n++, zo--) {
+            if (n + 1 < N) xpass(n + 1);
+            float yv[4];
+            ypass(n, yv);
+            float o[4];
+#pragma unroll
+            for (int c = 0; c < 4; c++) o[c] = zfeed<HW>(A[c], yv[c], P.taps);
+            if (zo < ze) {
+#pragma unroll
+                for (int c = 0; c < 4; c++)
+                    if (smask & (1u << c)) dp[c * nx] = o[c];
+                if (P.dogmax != nullptr) {
 #pragma unroll
                     for (int c = 0; c < 4; c++)
-                        if (smask & (1u << c)) dp[c * nx] = o[c];
-                    if (P.dogmax != nullptr) {
-                        const float *sp = P.src + base;
-#pragma unroll
-                        for (int c = 0; c < 4; c++)
-                            if (smask & (1u << c))
-                                vmax = fmaxf(vmax, fabsf(__fsub_rn(sp[c * nx], o[c])));
-                    }
-                    if (dmask != 0 && !(z & 1) && (z >> 1) < dnz) {
-                        float *qd = P.ds_dst + ((size_t) (z >> 1) * dny * dnx + ds_col);
-#pragma unroll
-                        for (int c = 0; c < 4; c++)
-                            if (dmask & (1u << c))
-                                qd[(((ybase + c) >> 1) - (ybase >> 1)) * dnx] = o[c];
-                    }
+                        if (smask & (1u << c))
+                            vmax = fmaxf(vmax, fabsf(__fsub_rn(sp[c * nx], o[c])));
                 }
+                if (dmask != 0 && !(zo & 1) && (zo >> 1) < dnz) {
+                    float *qd = P.ds_dst + ((size_t) (zo >> 1) * dny * dnx + ds_col);
+#pragma unroll
+                    for (int c = 0; c < 4; c++)
+                        if (dmask & (1u << c))
+                            qd[(((ybase + c) >> 1) - (ybase >> 1)) * dnx] = o[c];
+                }
+                dp -= plane_stride;
+                sp -= plane_stride;
             }
-        }  // n >= 0
-        __syncthreads();
-        // tile buffer (n+1) % kNB was consumed by xpass(n+1): refill it
-        if (tid == 0 && n + 1 + kNB < N) issue(n + 1 + kNB);
-    }
+            plane_end(n);
+        }
+    }  // chunks
 
     // ---- DoG max-abs: block reduce, one atomic per CTA (non-negative floats order as ints)
     if (P.dogmax != nullptr) {
