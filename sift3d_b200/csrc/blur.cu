@@ -375,6 +375,9 @@ static const ChunkTable &fused_chunk_table(int ncta, int tiles, int nzr, int hw,
     return e.t;
 }
 
+static thread_local int g_fused_sm_reserve = 0;
+void set_fused_sm_reserve(int sms) { g_fused_sm_reserve = sms < 0 ? 0 : (sms > kNumSMs - 1 ? kNumSMs - 1 : sms); }
+
 template <int HW, int TY>
 static int launch_fused_t(cudaStream_t st, const FusedParams &P, int occ) {
     using C = FusedCfg<HW>;
@@ -403,7 +406,7 @@ static int launch_fused_t(cudaStream_t st, const FusedParams &P, int occ) {
     const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
     const int nzr = P.z1 - P.z0;
     // one wave of CTAs, but no CTA with less than ~8 outputs of one tile
-    long ncta = (long) kNumSMs * occ;
+    long ncta = (long) (kNumSMs - g_fused_sm_reserve) * occ;
     const long most = (long) tiles * (nzr / (HW + 1 > 8 ? HW + 1 : 8) > 0 ? nzr / (HW + 1 > 8 ? HW + 1 : 8) : 1);
     if (ncta > most) ncta = most;
     if (ncta > kMaxFusedCtas) ncta = kMaxFusedCtas;
@@ -518,8 +521,11 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
 
     // Fused single-launch path: unit tap spacing on every axis, TMA-compatible rows, taps
     // symmetric bit for bit (the kernel shares the products of twin taps).
-    static const int ty_env = getenv("SIFT3D_CUDA_TY") ? atoi(getenv("SIFT3D_CUDA_TY")) : 64;
-    const int ty = (ty_env == 32 || ny < 64) ? 32 : 64;
+    // Tile height: 32-row tiles at 3 CTAs x 256 threads per SM (<= 85 registers, hw <= 4) are
+    // ~5 % faster than one 64-row CTA of 512 threads; the wider filters need the registers.
+    static const int ty_env = getenv("SIFT3D_CUDA_TY") ? atoi(getenv("SIFT3D_CUDA_TY")) : 0;
+    const int ty = (ty_env == 32 || ny < 64 || (ty_env != 64 && hw <= 4)) ? 32 : 64;
+    const int ty_half = (ty_env == 32 || ny < 64) ? 32 : 64;
     bool symmetric = true;
     for (int i = 0; i < hw; i++) symmetric = symmetric && f.taps[i] == f.taps[f.width - 1 - i];
     if (!force_generic && symmetric && ax.uf == 1.0f && ay.uf == 1.0f && az.uf == 1.0f && hw >= 1 &&
@@ -549,7 +555,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];
         for (int i = f.width; i < kMaxParamTaps; i++) P.taps.k[i] = 0.0f;
         if (d_dogmax_slot != nullptr) S3D_CK(cudaMemsetAsync(d_dogmax_slot, 0, sizeof(float), st));
-        const int r = ty == 64 ? launch_fused<64>(st, P, hw, 1) : launch_fused<32>(st, P, hw, 2);
+        const int r = ty == 64 ? launch_fused<64>(st, P, hw, 1) : launch_fused<32>(st, P, hw, hw <= 4 ? 3 : 2);
         if (r < 0) return -1;
         if (r == 0) {
             if (launches) *launches += 1;
@@ -560,7 +566,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
 
     // Fused single-launch path for tap spacing 1/2 on every axis (octave 1).
     if (!force_generic && symmetric && ax.uf == 0.5f && ay.uf == 0.5f && az.uf == 0.5f && hw >= 1 &&
-        hw <= 8 && d_divisor == nullptr && nx % 4 == 0 && nx >= kFTX && ny >= ty && nx < (1 << 20) &&
+        hw <= 8 && d_divisor == nullptr && nx % 4 == 0 && nx >= kFTX && ny >= ty_half && nx < (1 << 20) &&
         ny < (1 << 20) && nz < (1 << 20) && ny >= hw + 3 && nz >= hw + 3 &&
         ((uintptr_t) src & 15) == 0 && (d_dogmax_slot == nullptr || dog_prev == src)) {
         FusedParams P;
@@ -575,7 +581,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];
         for (int i = f.width; i < kMaxParamTaps; i++) P.taps.k[i] = 0.0f;
         if (d_dogmax_slot != nullptr) S3D_CK(cudaMemsetAsync(d_dogmax_slot, 0, sizeof(float), st));
-        const int r = ty == 64 ? launch_half<64>(st, P, hw, 1) : launch_half<32>(st, P, hw, 2);
+        const int r = ty_half == 64 ? launch_half<64>(st, P, hw, 1) : launch_half<32>(st, P, hw, 2);
         if (r < 0) return -1;
         if (r == 0) {
             if (launches) *launches += 1;

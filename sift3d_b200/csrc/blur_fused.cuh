@@ -186,7 +186,7 @@ __device__ __forceinline__ float zfeed(float (&A)[2 * HW], const float v, const 
 // output plane) space, tile-major: unit u is plane z0 + u % nzr of tile u / nzr. The host
 // cuts the space so that every CTA has the same cost (outputs + 2*HW halo planes per chunk,
 // a chunk being the part of a CTA's range inside one tile), see fused_chunk_table().
-constexpr int kMaxFusedCtas = 2 * kNumSMs;
+constexpr int kMaxFusedCtas = 3 * kNumSMs;
 struct ChunkTable {
     int b[kMaxFusedCtas + 1];
 };
@@ -194,7 +194,7 @@ struct ChunkTable {
 // Fused blur, unit tap spacing on all three axes. Block = 32 x TY/4 threads: thread
 // (lane, w) owns column x0 + lane, rows y0 + 4w .. 4w+3 in the y and z passes.
 template <int HW, int TY>
-__global__ void __launch_bounds__(8 * TY, TY == 64 ? 1 : 2)
+__global__ void __launch_bounds__(8 * TY, TY == 64 ? 1 : (HW <= 4 ? 3 : 2))
 blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ FusedParams P,
                        const __grid_constant__ ChunkTable tab) {
     using C = FusedCfg<HW>;

@@ -56,6 +56,10 @@ struct Cand {
 // ---- kernels / launchers implemented in the .cu files -----------------------------------
 
 // blur.cu
+// SMs the fused one-wave blur leaves free on this thread's following launches: while other
+// octaves work on their own (higher-priority) streams a 148-CTA persistent kernel could not
+// place all its CTAs at once and the stragglers would double its time.
+void set_fused_sm_reserve(int sms);
 int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, float *tmp_b,
                 int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
                 const float *d_taps, const float *d_divisor, float *d_dogmax_slot,

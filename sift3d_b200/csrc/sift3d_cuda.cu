@@ -583,10 +583,17 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     // one-wave kernels would otherwise occupy every SM while octave 1 still has to produce
     // the seed of octave 2, so octave 0 resumes only after octave 1's seed level.
     if (noct > 1 && !serial) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_seed[noct > 2 ? 1 : 0], 0));
+    // Octave 0's remaining levels share the device with the other octaves' streams: leave
+    // them some SMs (see set_fused_sm_reserve).
+    static const int reserve_env = getenv("SIFT3D_CUDA_RESERVE") ? atoi(getenv("SIFT3D_CUDA_RESERVE")) : 14;
+    if (noct > 1 && !serial) set_fused_sm_reserve(reserve_env);
     for (int o = 0; o < noct; o++) {
         const int sfirst = (o == 0 && !from_seed) ? -1 : 0;
-        for (int s = (ds_level + 1 > sfirst ? ds_level + 1 : sfirst); s < nlev - 1; s++)
-            if (run_level(o, s)) return -1;
+        int rc = 0;
+        for (int s = (ds_level + 1 > sfirst ? ds_level + 1 : sfirst); s < nlev - 1 && !rc; s++)
+            rc = run_level(o, s);
+        if (o == 0) set_fused_sm_reserve(0);
+        if (rc) return -1;
         if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_PYR], st));
     }
     if (slab) {  // DoG maxima are over whole levels
