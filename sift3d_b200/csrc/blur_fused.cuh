@@ -207,6 +207,8 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_co
     constexpr int XF_FLOATS = TROWS * kFTX;
     constexpr int NITEMS = TROWS * 8;
     constexpr int ROT = (TROWS - NT / 8 % TROWS) % TROWS;  // see the x-pass items
+    // the four extra live registers would spill in the two variants at their register cap
+    constexpr bool kPrefetchSrc = HW < 8 && !(TY == 32 && HW == 4);
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float *tile = reinterpret_cast<float *>(smem_raw);                 // [kNB][TROWS][BW]
@@ -424,6 +426,14 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_co
         // at or above ze); from then on every plane completes the output one plane lower
         int zo = qstart + HW;  // output completed by element n
         for (; n < N; n++, zo--) {
+            // source voxels of the DoG max: requested a whole plane step before they are
+            // used (an L2 round trip in front of the FMNMX chain cost 15 us per level)
+            float pv[4] = {0.f, 0.f, 0.f, 0.f};
+            if (kPrefetchSrc && P.dogmax != nullptr && zo < ze) {
+#pragma unroll
+                for (int c = 0; c < 4; c++)
+                    if (smask & (1u << c)) pv[c] = __ldg(sp + c * nx);
+            }
             if (n + 1 < N) xpass(n + 1);
             float yv[4];
             ypass(n, yv);
@@ -438,7 +448,7 @@ blur_fused_unit_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_co
 #pragma unroll
                     for (int c = 0; c < 4; c++)
                         if (smask & (1u << c))
-                            vmax = fmaxf(vmax, fabsf(__fsub_rn(sp[c * nx], o[c])));
+                            vmax = fmaxf(vmax, fabsf(__fsub_rn(kPrefetchSrc ? pv[c] : sp[c * nx], o[c])));
                 }
                 if (dmask != 0 && !(zo & 1) && (zo >> 1) < dnz) {
                     float *qd = P.ds_dst + ((size_t) (zo >> 1) * dny * dnx + ds_col);
