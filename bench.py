@@ -329,7 +329,8 @@ def run_product_arm(args):
                      "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": 8 * NVOX, "per_level": per_level},
-        "cpu_baseline": measure_cpu_baseline(),
+        # SIFT3D_BENCH_NO_CPU=1: tuning runs only (the line is then incomplete by contract)
+        "cpu_baseline": None if os.environ.get("SIFT3D_BENCH_NO_CPU") else measure_cpu_baseline(),
     }
     print(json.dumps(line), flush=True)
     if dist is not None:

@@ -582,7 +582,12 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     // Phase B, the bulk: remaining levels and the extrema scan of each octave. Octave 0's
     // one-wave kernels would otherwise occupy every SM while octave 1 still has to produce
     // the seed of octave 2, so octave 0 resumes only after octave 1's seed level.
-    if (noct > 1 && !serial) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_seed[noct > 2 ? 1 : 0], 0));
+    static const int wait_env = getenv("SIFT3D_CUDA_SEEDWAIT") ? atoi(getenv("SIFT3D_CUDA_SEEDWAIT")) : 1;
+    {
+        int wi = wait_env < noct - 2 ? wait_env : noct - 2;
+        if (wi < 0) wi = 0;
+        if (noct > 1 && !serial && wait_env >= 0) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_seed[wi], 0));
+    }
     // Octave 0's remaining levels share the device with the other octaves' streams: leave
     // them some SMs (see set_fused_sm_reserve).
     static const int reserve_env = getenv("SIFT3D_CUDA_RESERVE") ? atoi(getenv("SIFT3D_CUDA_RESERVE")) : 14;
