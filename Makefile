@@ -13,6 +13,10 @@ ARCH    := -gencode arch=compute_100a,code=sm_100a
 # kernels additionally use explicit __fmul_rn/__fadd_rn where bit parity is claimed.
 NVFLAGS := $(ARCH) -O3 -lineinfo --fmad=false -std=c++17 -ccbin $(HOSTCXX) \
            -Xcompiler -fPIC,-fvisibility=hidden,-Wall,-Wno-unused-function -Xptxas -v
+# descriptor.cu: bit parity is not claimed for descriptors (tolerance: cosine >= 0.999); the
+# expressions that decide voxel membership / cell / face use explicit __f*_rn intrinsics and
+# are unaffected, everything else may contract (later flag wins).
+NVFLAGS_descriptor := --fmad=true
 LIBDIR  := sift3d_b200/lib
 CSRC    := sift3d_b200/csrc
 CU_SRCS := $(CSRC)/sift3d_cuda.cu $(CSRC)/blur.cu $(CSRC)/extrema.cu $(CSRC)/orient.cu \
@@ -26,7 +30,7 @@ product: $(LIBDIR)/libsift3d_cuda.so $(LIBDIR)/libsift3D.so $(LIBDIR)/libsift3d_
 
 build/%.o: $(CSRC)/%.cu $(CU_HDRS)
 	@mkdir -p build
-	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> build/$*.ptxas.log || (cat build/$*.ptxas.log; false)
+	$(NVCC) $(NVFLAGS) $(NVFLAGS_$*) -c $< -o $@ 2> build/$*.ptxas.log || (cat build/$*.ptxas.log; false)
 
 $(LIBDIR)/libsift3d_cuda.so: $(CU_OBJS)
 	@mkdir -p $(LIBDIR)
