@@ -386,7 +386,30 @@ descriptor_rows_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
 // icos_hist_bin so that ties resolve exactly as in the reference.
 // ---------------------------------------------------------------------------------------
 
+// Continuous quantities of the cell kernel's per-voxel front end (rotations, the cross and dot
+// products of the barycentric solve) may use fused multiply-adds: descriptors are compared
+// within a tolerance (cosine >= 0.999), and an FMA only removes an intermediate rounding.
+// The quantities the reference DECIDES on exactly once per voxel (the sphere test on sq, the
+// literal first-hit face scan of the slow path) keep the reference's unfused operation order.
+// -DSIFT3D_DESC_EXACT restores the unfused order everywhere.
+#ifdef SIFT3D_DESC_EXACT
+constexpr bool kDescFma = false;
+#else
+constexpr bool kDescFma = true;
+#endif
+template <bool FMA>
+__device__ __forceinline__ float dot3(float a0, float b0, float a1, float b1, float a2, float b2) {
+    if (FMA) return fmaf(a2, b2, fmaf(a1, b1, __fmul_rn(a0, b0)));
+    return __fadd_rn(__fadd_rn(__fmul_rn(a0, b0), __fmul_rn(a1, b1)), __fmul_rn(a2, b2));
+}
+template <bool FMA>
+__device__ __forceinline__ float diff2(float a0, float b0, float a1, float b1) {  // a0*b0 - a1*b1
+    if (FMA) return fmaf(a0, b0, -__fmul_rn(a1, b1));
+    return __fsub_rn(__fmul_rn(a0, b0), __fmul_rn(a1, b1));
+}
+
 // cart2bary on a face held in shared memory: fm = {e1[3], e2[3], t[3], q[3], e2q}
+template <bool FMA = false>
 __device__ __forceinline__ bool face_hit_s(const float *__restrict__ fm, float gx, float gy,
                                            float gz, float &bx, float &by, float &bz) {
     const float4 m0 = *reinterpret_cast<const float4 *>(fm);       // e1.x e1.y e1.z e2.x
@@ -394,14 +417,14 @@ __device__ __forceinline__ bool face_hit_s(const float *__restrict__ fm, float g
     const float4 m2 = *reinterpret_cast<const float4 *>(fm + 8);   // t.z  q.x  q.y  q.z
     const float e2q = fm[12];
     const float e2x = m0.w, e2y = m1.x, e2z = m1.y;
-    const float px = __fsub_rn(__fmul_rn(gy, e2z), __fmul_rn(gz, e2y));
-    const float py = __fsub_rn(__fmul_rn(gz, e2x), __fmul_rn(gx, e2z));
-    const float pz = __fsub_rn(__fmul_rn(gx, e2y), __fmul_rn(gy, e2x));
-    const float det = __fadd_rn(__fadd_rn(__fmul_rn(m0.x, px), __fmul_rn(m0.y, py)), __fmul_rn(m0.z, pz));
+    const float px = diff2<FMA>(gy, e2z, gz, e2y);
+    const float py = diff2<FMA>(gz, e2x, gx, e2z);
+    const float pz = diff2<FMA>(gx, e2y, gy, e2x);
+    const float det = dot3<FMA>(m0.x, px, m0.y, py, m0.z, pz);
     if (fabsf(det) < kBaryEpsF) return false;
     const float det_inv = __frcp_rn(det);  // == 1.0f / det, correctly rounded
-    const float tp = __fadd_rn(__fadd_rn(__fmul_rn(m1.z, px), __fmul_rn(m1.w, py)), __fmul_rn(m2.x, pz));
-    const float cq = __fadd_rn(__fadd_rn(__fmul_rn(gx, m2.y), __fmul_rn(gy, m2.z)), __fmul_rn(gz, m2.w));
+    const float tp = dot3<FMA>(m1.z, px, m1.w, py, m2.x, pz);
+    const float cq = dot3<FMA>(gx, m2.y, gy, m2.z, gz, m2.w);
     by = __fmul_rn(det_inv, tp);
     bz = __fmul_rn(det_inv, cq);
     bx = __fsub_rn(__fsub_rn(1.0f, by), bz);
@@ -851,6 +874,8 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     const float sig2 = __fmul_rn(sigma, sigma);
     const float nhs = -0.5f / sig2;
     const float ixu = __fdiv_rn(1.0f, uxf), iyu = __fdiv_rn(1.0f, uyf), izu = __fdiv_rn(1.0f, uzf);
+    const float hixu = 0.5f * ixu, hiyu = 0.5f * iyu, hizu = 0.5f * izu;
+    const float hw_bf = half_w * bin_fctr;  // == 2: (k + half_w) * bin_fctr as one FMA
 
     // Window (sift.c:91-99), all-float here because win_radius is a float.
     const int x0 = (int) fmaxf(floorf(__fsub_rn(cx, __fdiv_rn(rad, uxf))), 1.0f);
@@ -1034,12 +1059,12 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
             bool ok = active && !(sq > rad2);
             // vkp = Rt * vim (SIFT3D_MUL_MAT_RM_CVEC, immacros.h:326-342)
-            const float kx = __fadd_rn(__fadd_rn(__fmul_rn(r00, dx), __fmul_rn(r10, dy)), __fmul_rn(r20, dz));
-            const float ky = __fadd_rn(__fadd_rn(__fmul_rn(r01, dx), __fmul_rn(r11, dy)), __fmul_rn(r21, dz));
-            const float kz = __fadd_rn(__fadd_rn(__fmul_rn(r02, dx), __fmul_rn(r12, dy)), __fmul_rn(r22, dz));
-            const float vbx = __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
-            const float vby = __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
-            const float vbz = __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
+            const float kx = dot3<kDescFma>(r00, dx, r10, dy, r20, dz);
+            const float ky = dot3<kDescFma>(r01, dx, r11, dy, r21, dz);
+            const float kz = dot3<kDescFma>(r02, dx, r12, dy, r22, dz);
+            const float vbx = kDescFma ? fmaf(kx, bin_fctr, hw_bf) : __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
+            const float vby = kDescFma ? fmaf(ky, bin_fctr, hw_bf) : __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
+            const float vbz = kDescFma ? fmaf(kz, bin_fctr, hw_bf) : __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
             ok = ok && !(vbx < 0.0f || vby < 0.0f || vbz < 0.0f || vbx >= (float) kHistPerDim ||
                          vby >= (float) kHistPerDim || vbz >= (float) kHistPerDim);
             // the voxel belongs to the cell its own indices name (the interval margins overlap)
@@ -1049,18 +1074,19 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             v.fz = __fsub_rn(vbz, floorf(vbz));
 
             const float *__restrict__ row = img + (size_t) z * zs + (size_t) y * ys;
-            float gx = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + 1], row[x - 1])), ixu);
-            float gy = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys])), iyu);
-            float gz = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + zs], row[(ptrdiff_t) x - (ptrdiff_t) zs])), izu);
+            // 0.5 * (a - b) / u: the halving is exact, so (a - b) * (0.5 / u) has the same bits
+            float gx = __fmul_rn(__fsub_rn(row[x + 1], row[x - 1]), hixu);
+            float gy = __fmul_rn(__fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys]), hiyu);
+            float gz = __fmul_rn(__fsub_rn(row[x + zs], row[(ptrdiff_t) x - (ptrdiff_t) zs]), hizu);
             const float w = __expf(sq * nhs);  // exp(-0.5 * sq / sigma^2), sift.c:1498
             gx = __fmul_rn(gx, w);
             gy = __fmul_rn(gy, w);
             gz = __fmul_rn(gz, w);
-            const float rx = __fadd_rn(__fadd_rn(__fmul_rn(r00, gx), __fmul_rn(r10, gy)), __fmul_rn(r20, gz));
-            const float ry2 = __fadd_rn(__fadd_rn(__fmul_rn(r01, gx), __fmul_rn(r11, gy)), __fmul_rn(r21, gz));
-            const float rz2 = __fadd_rn(__fadd_rn(__fmul_rn(r02, gx), __fmul_rn(r12, gy)), __fmul_rn(r22, gz));
+            const float rx = dot3<kDescFma>(r00, gx, r10, gy, r20, gz);
+            const float ry2 = dot3<kDescFma>(r01, gx, r11, gy, r21, gz);
+            const float rz2 = dot3<kDescFma>(r02, gx, r12, gy, r22, gz);
             // icos_hist_bin (sift.c:1254-1291)
-            const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry2, ry2)), __fmul_rn(rz2, rz2));
+            const float n2 = dot3<kDescFma>(rx, rx, ry2, ry2, rz2, rz2);
             ok = ok && !(n2 < kBaryEpsF);
             // nearest face centre among the 4 candidates of this octant (selection only)
             const float ax = fabsf(rx), ay = fabsf(ry2), az = fabsf(rz2);
@@ -1077,7 +1103,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             const int oct = (rx < 0.0f ? 1 : 0) | (ry2 < 0.0f ? 2 : 0) | (rz2 < 0.0f ? 4 : 0);
             const int best = slut[oct * 4 + which];
             float bx, by, bz;
-            const bool hit = face_hit_s(smesh + best * 16, rx, ry2, rz2, bx, by, bz) && bx > 1e-5f &&
+            const bool hit = face_hit_s<kDescFma>(smesh + best * 16, rx, ry2, rz2, bx, by, bz) && bx > 1e-5f &&
                              by > 1e-5f && bz > 1e-5f;
             v.valid = ok;
             v.slow = ok && !hit;  // near an edge: the literal first-hit scan decides
