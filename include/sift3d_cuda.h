@@ -178,6 +178,12 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_blur(sift3d_cuda_ctx *ctx, const float *host_
                                         float *host_dst, int nx, int ny, int nz,
                                         const double units[3], const sift3d_cuda_filter *f,
                                         int force_generic);
+/* Host-only: the work table of the fused unit-spacing blur (no device needed). `tiles` column
+ * tiles of `nzr` output planes each are cut into `ncta` contiguous ranges of the flattened
+ * tile-major space; bounds[0..ncta] receives the range limits. Returns the cost (output planes
+ * + warm-up planes) of the most expensive range, or -1 on invalid arguments. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_chunk_table(int ncta, int tiles, int nzr, int hw,
+                                                    int top_is_volume_top, int *bounds);
 SIFT3D_CUDA_EXPORT int sift3d_cuda_get_timings(sift3d_cuda_ctx *ctx, sift3d_cuda_timings *t);
 /* Number of kernel launches issued by this context since creation. */
 SIFT3D_CUDA_EXPORT uint64_t sift3d_cuda_launch_count(sift3d_cuda_ctx *ctx);

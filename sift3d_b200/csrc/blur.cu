@@ -378,6 +378,30 @@ static const ChunkTable &fused_chunk_table(int ncta, int tiles, int nzr, int hw,
 static thread_local int g_fused_sm_reserve = 0;
 void set_fused_sm_reserve(int sms) { g_fused_sm_reserve = sms < 0 ? 0 : (sms > kNumSMs - 1 ? kNumSMs - 1 : sms); }
 
+}  // namespace s3d
+extern "C" SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_chunk_table(int ncta, int tiles, int nzr, int hw,
+                                                              int top_is_volume_top, int *bounds) {
+    using namespace s3d;
+    if (ncta < 1 || ncta > kMaxFusedCtas || tiles < 1 || nzr < 1 || hw < 1 || !bounds ||
+        (long) tiles * nzr > 0x7fffffffL)
+        return -1;
+    const ChunkTable &t = fused_chunk_table(ncta, tiles, nzr, hw, top_is_volume_top != 0);
+    int worst = 0;
+    for (int i = 0; i <= ncta; i++) bounds[i] = t.b[i];
+    for (int i = 0; i < ncta; i++) {
+        int cost = 0;
+        for (long pos = t.b[i]; pos < t.b[i + 1];) {
+            const int rem = nzr - (int) (pos % nzr);
+            const int take = (int) (t.b[i + 1] - pos < rem ? t.b[i + 1] - pos : rem);
+            cost += take + 2 * hw + ((take == rem && top_is_volume_top) ? hw + 2 : 0);
+            pos += take;
+        }
+        if (cost > worst) worst = cost;
+    }
+    return worst;
+}
+namespace s3d {
+
 template <int HW, int TY>
 static int launch_fused_t(cudaStream_t st, const FusedParams &P, int occ) {
     using C = FusedCfg<HW>;

@@ -125,3 +125,41 @@ def test_synth_shapes():
     v = s3.synth_volume(20, 12, 9, num_blobs=3, seed=1)
     assert v.shape == (9, 12, 20) and v.dtype == np.float32 and np.isfinite(v).all()
     assert np.abs(v).max() > 0
+
+
+@pytest.mark.parametrize("tiles,nzr,hw,ncta,top", [
+    (32, 256, 3, 148, 1), (64, 256, 2, 444, 1), (32, 256, 8, 134, 1), (128, 300, 5, 148, 1),
+    (512, 1024, 8, 148, 1), (4, 40, 2, 20, 1), (2, 17, 8, 2, 1), (1, 9, 4, 1, 0), (6, 96, 6, 40, 0),
+    (3, 23, 1, 8, 1),
+])
+def test_fused_blur_chunk_table(tiles, nzr, hw, ncta, top):
+    """Host logic of the fused blur's work table (blur.cu: fused_chunk_table): the ranges tile
+    the flattened (tile, plane) space in order, no piece of a range inside one tile is shorter
+    than hw + 1 outputs (a chunk below the top of the volume must not reach the virtual planes
+    of the right-boundary mirror, imutil.c:846-849), and the cost is balanced."""
+    L = api.libcuda()
+    L.sift3d_cuda_blur_chunk_table.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int)]
+    L.sift3d_cuda_blur_chunk_table.restype = C.c_int
+    b = (C.c_int * (ncta + 1))()
+    worst = L.sift3d_cuda_blur_chunk_table(ncta, tiles, nzr, hw, top, b)
+    b = list(b)
+    total = tiles * nzr
+    assert worst > 0 and b[0] == 0 and b[-1] == total
+    assert all(b[i] <= b[i + 1] for i in range(ncta))
+    minlen = min(hw + 1, nzr)
+    costs = []
+    for i in range(ncta):
+        pos, cost = b[i], 0
+        while pos < b[i + 1]:
+            rem = nzr - pos % nzr
+            take = min(rem, b[i + 1] - pos)
+            assert take >= minlen, (i, pos, take)
+            cost += take + 2 * hw + (hw + 2 if (take == rem and top) else 0)
+            pos += take
+        costs.append(cost)
+    assert max(costs) == worst
+    # balance: the most expensive range is within one tile-crossing of the mean
+    busy = [c for c in costs if c > 0]
+    mean = sum(busy) / len(busy)
+    assert worst <= mean + 3 * (2 * hw + minlen) + hw + 2, (worst, mean)
+    assert L.sift3d_cuda_blur_chunk_table(0, tiles, nzr, hw, top, b and (C.c_int * 2)()) == -1
