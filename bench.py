@@ -146,10 +146,23 @@ def cpu_threads():
     return int(n) if n else (os.cpu_count() or 1)
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 into every rank when the variable is unset; the CPU
+    legs run on rank 0 alone and are meant to use every host thread (the reference's OpenMP
+    path). Must run before the oracle library (libgomp) is loaded."""
+    if os.environ.get("TORCHELASTIC_RUN_ID") is not None and os.environ.get("OMP_NUM_THREADS") == "1":
+        try:
+            n = len(os.sched_getaffinity(0))
+        except AttributeError:
+            n = os.cpu_count() or 1
+        os.environ["OMP_NUM_THREADS"] = str(n)
+
+
 def run_reference_arm(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return
+    use_all_host_threads()
     os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
     kind, Run = cpu_oracle()
     sample = cpu_sample_volume()
@@ -330,7 +343,8 @@ def run_product_arm(args):
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": 8 * NVOX, "per_level": per_level},
         # SIFT3D_BENCH_NO_CPU=1: tuning runs only (the line is then incomplete by contract)
-        "cpu_baseline": None if os.environ.get("SIFT3D_BENCH_NO_CPU") else measure_cpu_baseline(),
+        # (rank 0 at N=1 only: at N>1 the reference arm carries the CPU number)
+        "cpu_baseline": None if (os.environ.get("SIFT3D_BENCH_NO_CPU") or world > 1) else measure_cpu_baseline(),
     }
     print(json.dumps(line), flush=True)
     if dist is not None:
