@@ -162,6 +162,13 @@ SIFT3D_CUDA_EXPORT float *sift3d_cuda_level_ptr(sift3d_cuda_ctx *ctx, int o, int
  * orientation result (valid flag + R). out has room for max entries. */
 SIFT3D_CUDA_EXPORT int sift3d_cuda_fetch_candidates(sift3d_cuda_ctx *ctx,
                                                     sift3d_cuda_keypoint *out, int max);
+/* Zero-copy view of the same records, octave by octave (octave_index = 0 .. num_octaves-1 of
+ * this context, ascending = scan order): when the candidate regions live in page-locked
+ * host memory (the orientation kernel writes them there directly) *records points at the
+ * octave's records and the count is returned; valid until the next detect on this context.
+ * Returns -1 when the records are device resident (use sift3d_cuda_fetch_candidates). */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_candidates_view(sift3d_cuda_ctx *ctx, int octave_index,
+                                                   const sift3d_cuda_keypoint **records);
 
 /* Descriptors for num keypoints on the pyramid left by the last detect.
  * desc: num * 768 float32 on the host (or device if desc_on_device). */

@@ -69,7 +69,16 @@ struct sift3d_cuda_ctx {
     DevBuf scalars;                     // [0] image max-abs; [1 + o*MAX_FILTERS + s] DoG max
     DevBuf cand_raw, cand_sorted;       // Cand regions, one per octave
     DevBuf counts;                      // int per octave
-    DevBuf kps;                         // sift3d_cuda_keypoint, compact across octaves
+    DevBuf kps;                         // sift3d_cuda_keypoint regions, one per octave (device)
+    // ... or, when they fit kKpsHostMax, in page-locked host memory that the orientation
+    // kernel writes directly (88 B per candidate over PCIe, under the kernel): the host reads
+    // the records in place after the one synchronisation of detect -- no device-to-host copy
+    // and no second synchronisation (48 us + ~30 us per 256^3 volume).
+    sift3d_cuda_keypoint *kps_host = nullptr;
+    size_t kps_host_bytes = 0;
+    sift3d_cuda_keypoint *kps_dev() const {
+        return kps_host ? kps_host : (sift3d_cuda_keypoint *) kps.p;  // UVA: same address on the device
+    }
     std::vector<int> cand_base, cand_cap, cand_min;
     int *h_counts = nullptr;            // pinned
     bool have_pyramid = false;
@@ -180,6 +189,8 @@ void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx) {
     ctx->cand_sorted.release();
     ctx->counts.release();
     ctx->kps.release();
+    if (ctx->kps_host) cudaFreeHost(ctx->kps_host);
+    ctx->kps_host = nullptr;
     ctx->desc_jobs.release();
     ctx->desc_out.release();
     for (int i = 0; i < 8; i++)
@@ -210,6 +221,8 @@ void sift3d_cuda_host_free(void *p) {
 
 // Candidate regions, one per octave: room for 1/32 of the octave's voxels (typical images
 // yield 0.04 - 0.4 %), or for what an earlier detect on this plan was seen to need.
+static void detect_timings(sift3d_cuda_ctx *ctx);
+
 static int plan_candidates(sift3d_cuda_ctx *ctx) {
     const int noct = ctx->desc.num_octaves;
     ctx->cand_base.assign(noct, 0);
@@ -228,9 +241,38 @@ static int plan_candidates(sift3d_cuda_ctx *ctx) {
     }
     if (ctx->cand_raw.ensure(cand_total * sizeof(Cand)) ||
         ctx->cand_sorted.ensure(cand_total * sizeof(Cand)) ||
-        ctx->counts.ensure(sizeof(int) * 64) ||
-        ctx->kps.ensure(cand_total * sizeof(sift3d_cuda_keypoint)))
+        ctx->counts.ensure(sizeof(int) * 64))
         return -1;
+    static const bool no_host_kps = getenv("SIFT3D_CUDA_NO_HOST_KPS") != nullptr;
+    const size_t kbytes = cand_total * sizeof(sift3d_cuda_keypoint);
+    constexpr size_t kKpsHostMax = (size_t) 256 << 20;
+    if (!no_host_kps && kbytes <= kKpsHostMax) {
+        if (kbytes > ctx->kps_host_bytes) {
+            if (ctx->kps_host) cudaFreeHost(ctx->kps_host);
+            ctx->kps_host = nullptr;
+            ctx->kps_host_bytes = 0;
+            void *hp = nullptr;
+            if (cudaHostAlloc(&hp, kbytes, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess) {
+                void *dp = nullptr;
+                if (cudaHostGetDevicePointer(&dp, hp, 0) == cudaSuccess && dp == hp) {
+                    ctx->kps_host = (sift3d_cuda_keypoint *) hp;
+                    ctx->kps_host_bytes = kbytes;
+                } else {
+                    cudaFreeHost(hp);
+                }
+            }
+            cudaGetLastError();
+        }
+        if (ctx->kps_host) {
+            ctx->kps.release();
+            return 0;
+        }
+    } else if (ctx->kps_host) {
+        cudaFreeHost(ctx->kps_host);
+        ctx->kps_host = nullptr;
+        ctx->kps_host_bytes = 0;
+    }
+    if (ctx->kps.ensure(kbytes)) return -1;
     return 0;
 }
 
@@ -623,7 +665,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_ORDER], st));
         if (launch_orient_all(so, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
                               (const int *) ctx->counts.p, (int *) ctx->work.p + o, corner_thresh,
-                              (sift3d_cuda_keypoint *) ctx->kps.p, &ctx->launches, o, o + 1))
+                              ctx->kps_dev(), &ctx->launches, o, o + 1))
             return -1;
         if (so != st) S3D_CK(cudaEventRecord(ctx->ev_done[o], so));
     }
@@ -632,6 +674,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     S3D_CK(cudaMemcpyAsync(ctx->h_counts, ctx->counts.p, sizeof(int) * noct,
                            cudaMemcpyDeviceToHost, st));
     S3D_CK(cudaEventRecord(ctx->ev[EV_ORIENT], st));
+    if (ctx->kps_host) S3D_CK(cudaEventRecord(ctx->ev[EV_D2H], st));  // results are already in host memory
     S3D_CK(cudaStreamSynchronize(st));
     int total = 0;
     bool overflow = false;
@@ -658,6 +701,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     }
     ctx->total_candidates = total;
     ctx->have_pyramid = true;
+    if (ctx->kps_host) detect_timings(ctx);
     if (num_candidates) *num_candidates = total;
     return 0;
 }
@@ -701,27 +745,7 @@ float *sift3d_cuda_level_ptr(sift3d_cuda_ctx *ctx, int o, int s) {
     return ctx->level(o, s).d;
 }
 
-int sift3d_cuda_fetch_candidates(sift3d_cuda_ctx *ctx, sift3d_cuda_keypoint *out, int max) {
-    if (!ctx || !ctx->have_pyramid || (!out && max > 0)) return -1;
-    if (set_device(ctx)) return -1;
-    int n = ctx->total_candidates < max ? ctx->total_candidates : max;
-    {
-        // results live in per-octave regions on the device; the caller gets them packed in
-        // scan order (octave-major)
-        int done = 0;
-        for (size_t o = 0; o < ctx->cand_base.size() && done < n; o++) {
-            int c = ctx->h_counts[o];
-            if (c > n - done) c = n - done;
-            if (c > 0)
-                S3D_CK(cudaMemcpyAsync(out + done,
-                                       (const sift3d_cuda_keypoint *) ctx->kps.p + ctx->cand_base[o],
-                                       sizeof(sift3d_cuda_keypoint) * (size_t) c, cudaMemcpyDeviceToHost,
-                                       ctx->stream));
-            done += c;
-        }
-    }
-    S3D_CK(cudaEventRecord(ctx->ev[EV_D2H], ctx->stream));
-    S3D_CK(cudaStreamSynchronize(ctx->stream));
+static void detect_timings(sift3d_cuda_ctx *ctx) {
     float ms;
     sift3d_cuda_timings &t = ctx->tm;
     cudaEventElapsedTime(&ms, ctx->ev[EV_START], ctx->ev[EV_H2D]); t.h2d = ms;
@@ -733,7 +757,43 @@ int sift3d_cuda_fetch_candidates(sift3d_cuda_ctx *ctx, sift3d_cuda_keypoint *out
     cudaEventElapsedTime(&ms, ctx->ev[EV_ORDER], ctx->ev[EV_ORIENT]); t.orient = ms;
     cudaEventElapsedTime(&ms, ctx->ev[EV_ORIENT], ctx->ev[EV_D2H]); t.d2h = ms;
     cudaEventElapsedTime(&ms, ctx->ev[EV_START], ctx->ev[EV_D2H]); t.total_detect = ms;
+}
+
+int sift3d_cuda_fetch_candidates(sift3d_cuda_ctx *ctx, sift3d_cuda_keypoint *out, int max) {
+    if (!ctx || !ctx->have_pyramid || (!out && max > 0)) return -1;
+    if (set_device(ctx)) return -1;
+    int n = ctx->total_candidates < max ? ctx->total_candidates : max;
+    {
+        // results live in per-octave regions on the device; the caller gets them packed in
+        // scan order (octave-major)
+        int done = 0;
+        for (size_t o = 0; o < ctx->cand_base.size() && done < n; o++) {
+            int c = ctx->h_counts[o];
+            if (c > n - done) c = n - done;
+            if (c > 0 && ctx->kps_host)  // already in host memory (detect synchronised)
+                memcpy(out + done, ctx->kps_host + ctx->cand_base[o], sizeof(sift3d_cuda_keypoint) * (size_t) c);
+            else if (c > 0)
+                S3D_CK(cudaMemcpyAsync(out + done,
+                                       (const sift3d_cuda_keypoint *) ctx->kps.p + ctx->cand_base[o],
+                                       sizeof(sift3d_cuda_keypoint) * (size_t) c, cudaMemcpyDeviceToHost,
+                                       ctx->stream));
+            done += c;
+        }
+    }
+    if (ctx->kps_host) return n;  // timings were closed by detect itself
+    S3D_CK(cudaEventRecord(ctx->ev[EV_D2H], ctx->stream));
+    S3D_CK(cudaStreamSynchronize(ctx->stream));
+    detect_timings(ctx);
     return n;
+}
+
+int sift3d_cuda_candidates_view(sift3d_cuda_ctx *ctx, int octave_index,
+                                const sift3d_cuda_keypoint **records) {
+    if (!ctx || !ctx->have_pyramid || !records || !ctx->kps_host || octave_index < 0 ||
+        (size_t) octave_index >= ctx->cand_base.size())
+        return -1;
+    *records = ctx->kps_host + ctx->cand_base[octave_index];
+    return ctx->h_counts[octave_index];
 }
 
 int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys, int num,
@@ -788,9 +848,22 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
     const int max_rows = jobs[0].max_rows;
     if (ctx->desc_jobs.ensure(sizeof(DescJob) * (size_t) num)) return -1;
     float *d_out = desc;
+    // Page-locked result buffer (the descriptor store of libsift3D.so is one): every CTA
+    // writes its 768 floats straight into host memory as it finishes (posted PCIe writes under
+    // the kernel) instead of a 4.4 MB device-to-host copy after it (86 us at 256^3).
+    bool direct = false;
     if (!desc_on_device) {
-        if (ctx->desc_out.ensure(sizeof(float) * SIFT3D_CUDA_DESC_NUMEL * (size_t) num)) return -1;
-        d_out = (float *) ctx->desc_out.p;
+        static const bool no_direct = getenv("SIFT3D_CUDA_NO_DIRECT_DESC") != nullptr;
+        cudaPointerAttributes at;
+        if (!no_direct && cudaPointerGetAttributes(&at, desc) == cudaSuccess &&
+            at.type == cudaMemoryTypeHost && at.devicePointer != nullptr) {
+            d_out = (float *) at.devicePointer;
+            direct = true;
+        } else {
+            cudaGetLastError();
+            if (ctx->desc_out.ensure(sizeof(float) * SIFT3D_CUDA_DESC_NUMEL * (size_t) num)) return -1;
+            d_out = (float *) ctx->desc_out.p;
+        }
     }
     S3D_CK(cudaEventRecord(ctx->dv[DV_START], st));
     memcpy(ctx->h_jobs, jobs.data(), sizeof(DescJob) * (size_t) num);
@@ -801,7 +874,7 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
     if (launch_descriptors(st, (const DescJob *) ctx->desc_jobs.p, num, max_rows, d_out, &ctx->launches))
         return -1;
     S3D_CK(cudaEventRecord(ctx->dv[DV_KERNEL], st));
-    if (!desc_on_device)
+    if (!desc_on_device && !direct)
         S3D_CK(cudaMemcpyAsync(desc, d_out, sizeof(float) * SIFT3D_CUDA_DESC_NUMEL * (size_t) num,
                                cudaMemcpyDeviceToHost, st));
     S3D_CK(cudaEventRecord(ctx->dv[DV_D2H], st));

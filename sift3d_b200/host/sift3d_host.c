@@ -858,20 +858,6 @@ int sift3d_detect_keypoints(sift3d_detector *const d, const sift3d_image *const 
             return SIFT3D_FAILURE;
     }
 
-    if ((size_t) num_cand > d->scratch_cap) {
-        /* page-locked, so the candidate download runs at PCIe speed */
-        sift3d_cuda_host_free(d->scratch);
-        d->scratch_cap = (size_t) num_cand * 2 + 1024;
-        d->scratch = (sift3d_cuda_keypoint *)
-            sift3d_cuda_host_alloc(d->scratch_cap * sizeof(sift3d_cuda_keypoint));
-        if (d->scratch == NULL) {
-            d->scratch_cap = 0;
-            return SIFT3D_FAILURE;
-        }
-    }
-    n = sift3d_cuda_fetch_candidates(d->ctx, d->scratch, num_cand);
-    if (n != num_cand)
-        return SIFT3D_FAILURE;
     d->have_gpyr = 1;
 
     /* detect_extrema records the dims of the first octave (sift.c:756-759) */
@@ -886,6 +872,64 @@ int sift3d_detect_keypoints(sift3d_detector *const d, const sift3d_image *const 
     if (kp_reserve(kp, (size_t) num_cand))
         return SIFT3D_FAILURE;
     num = 0;
+    {
+        const sift3d_cuda_keypoint *rec = NULL;
+        if (sift3d_cuda_candidates_view(d->ctx, 0, &rec) >= 0) {
+            /* The records are already in host memory (written there by the orientation
+             * kernel), one region per octave in scan order: read them in place. `sc`/`sj`
+             * walk the same sequence a second time, `num` records behind, for the strength
+             * of candidate number `num`. */
+            const sift3d_cuda_keypoint *srec = rec;
+            int o = 0, so = 0, j, sj = 0, cnt, scnt, seen = 0;
+            cnt = scnt = sift3d_cuda_candidates_view(d->ctx, 0, &rec);
+            while (seen < num_cand) {
+                while (cnt == 0) {
+                    cnt = sift3d_cuda_candidates_view(d->ctx, ++o, &rec);
+                    if (cnt < 0)
+                        return SIFT3D_FAILURE;
+                }
+                for (j = 0; j < cnt; j++) {
+                    const sift3d_cuda_keypoint *c = rec + j;
+                    keypoint_rec *dst;
+                    if (!c->valid)
+                        continue;
+                    while (sj >= scnt) {
+                        scnt = sift3d_cuda_candidates_view(d->ctx, ++so, &srec);
+                        sj = 0;
+                    }
+                    dst = kp->buf + num;
+                    dst->xd = c->x;
+                    dst->yd = c->y;
+                    dst->zd = c->z;
+                    dst->sd = c->sd;
+                    dst->o = c->o;
+                    dst->s = c->s;
+                    memcpy(dst->R, c->R, sizeof(dst->R));
+                    dst->strength = srec[sj++].strength;
+                    num++;
+                }
+                seen += cnt;
+                cnt = 0;
+            }
+            kp->num = num;
+            return SIFT3D_SUCCESS;
+        }
+    }
+
+    if ((size_t) num_cand > d->scratch_cap) {
+        /* page-locked, so the candidate download runs at PCIe speed */
+        sift3d_cuda_host_free(d->scratch);
+        d->scratch_cap = (size_t) num_cand * 2 + 1024;
+        d->scratch = (sift3d_cuda_keypoint *)
+            sift3d_cuda_host_alloc(d->scratch_cap * sizeof(sift3d_cuda_keypoint));
+        if (d->scratch == NULL) {
+            d->scratch_cap = 0;
+            return SIFT3D_FAILURE;
+        }
+    }
+    n = sift3d_cuda_fetch_candidates(d->ctx, d->scratch, num_cand);
+    if (n != num_cand)
+        return SIFT3D_FAILURE;
     for (i = 0; i < num_cand; i++) {
         const sift3d_cuda_keypoint *c = d->scratch + i;
         keypoint_rec *dst;
