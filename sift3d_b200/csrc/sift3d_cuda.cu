@@ -821,7 +821,10 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
         S3D_CK(cudaMallocHost((void **) &ctx->h_jobs, cap * sizeof(DescJob)));
         ctx->h_jobs_cap = cap;
     }
-    std::vector<DescJob> jobs((size_t) num);
+    // largest windows first: the grid drains in launch order, so the long CTAs start early.
+    // The order is a stable sort on the row bound; only (index, rows) pairs are moved and the
+    // 96-byte jobs are written once, in their final order, into the page-locked list.
+    std::vector<std::pair<int, int>> ord((size_t) num);  // (rows, index)
     for (int i = 0; i < num; i++) {
         const sift3d_cuda_keypoint &k = keys[i];
         // any Gaussian level may be addressed (the reference indexes gpyr by key->o, key->s)
@@ -832,7 +835,20 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
             return -1;
         }
         const Level &L = ctx->level(ko, k.s);
-        DescJob &J = jobs[(size_t) i];
+        DescJob J;
+        J.ny = L.ny; J.nz = L.nz;
+        J.uy = (float) L.uy; J.uz = (float) L.uz;
+        J.sigma = (float) (k.sd * 7.071067812);
+        ord[(size_t) i] = std::make_pair(desc_job_rows(J), i);
+    }
+    std::stable_sort(ord.begin(), ord.end(),
+                     [](const std::pair<int, int> &a, const std::pair<int, int> &b) { return a.first > b.first; });
+    DescJob *jobs = ctx->h_jobs;
+    for (int r = 0; r < num; r++) {
+        const int i = ord[(size_t) r].second;
+        const sift3d_cuda_keypoint &k = keys[i];
+        const Level &L = ctx->level(k.o - ctx->base_octave, k.s);
+        DescJob &J = jobs[r];
         J.img = L.d;
         J.nx = L.nx; J.ny = L.ny; J.nz = L.nz;
         J.ux = (float) L.ux; J.uy = (float) L.uy; J.uz = (float) L.uz;
@@ -840,11 +856,8 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
         J.sigma = (float) (k.sd * 7.071067812);                        // sift.c:43,1453
         for (int j = 0; j < 9; j++) J.R[j] = k.R[j];
         J.out_index = i;
-        J.max_rows = desc_job_rows(J);
+        J.max_rows = ord[(size_t) r].first;
     }
-    // largest windows first: the grid drains in launch order, so the long CTAs start early
-    std::stable_sort(jobs.begin(), jobs.end(),
-                     [](const DescJob &a, const DescJob &b) { return a.max_rows > b.max_rows; });
     const int max_rows = jobs[0].max_rows;
     if (ctx->desc_jobs.ensure(sizeof(DescJob) * (size_t) num)) return -1;
     float *d_out = desc;
@@ -866,7 +879,6 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
         }
     }
     S3D_CK(cudaEventRecord(ctx->dv[DV_START], st));
-    memcpy(ctx->h_jobs, jobs.data(), sizeof(DescJob) * (size_t) num);
     if (launch_pull_words(st, ctx->h_jobs, ctx->desc_jobs.p, sizeof(DescJob) * (size_t) num / 4,
                           &ctx->launches))
         return -1;
