@@ -634,9 +634,18 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     // them some SMs (see set_fused_sm_reserve).
     static const int reserve_env = getenv("SIFT3D_CUDA_RESERVE") ? atoi(getenv("SIFT3D_CUDA_RESERVE")) : 14;
     if (noct > 1 && !serial) set_fused_sm_reserve(reserve_env);
+    // The bulk levels of octave o >= 1 are not on the seed chain; held back until the chain is
+    // `bulk_wait` octaves further on they do not take the reserved SMs from it.
+    static const int bulk_wait = getenv("SIFT3D_CUDA_BULKWAIT") ? atoi(getenv("SIFT3D_CUDA_BULKWAIT")) : 0;
+    const int last_seed_ev = (tiny_from >= 0 ? tiny_from : noct_plan) - 1 < noct - 2
+                                 ? (tiny_from >= 0 ? tiny_from : noct_plan) - 1 : noct - 2;
     for (int o = 0; o < noct; o++) {
         const int sfirst = (o == 0 && !from_seed) ? -1 : 0;
         int rc = 0;
+        if (o >= 1 && bulk_wait > 0 && !serial && !slab && !(tiny_from >= 0 && o >= tiny_from)) {
+            const int we = o + bulk_wait < last_seed_ev ? o + bulk_wait : last_seed_ev;
+            if (we > o) S3D_CK(cudaStreamWaitEvent(stream_of(o), ctx->ev_seed[we], 0));
+        }
         for (int s = (ds_level + 1 > sfirst ? ds_level + 1 : sfirst); s < nlev - 1 && !rc; s++)
             rc = run_level(o, s);
         if (o == 0) set_fused_sm_reserve(0);
