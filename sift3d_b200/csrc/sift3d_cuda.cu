@@ -506,9 +506,11 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     // kernel on the stream of the first of them.
     int tiny_from = -1;
     static const bool no_tiny = getenv("SIFT3D_CUDA_NO_TINY") != nullptr;
+    static const int tiny_vox_env = getenv("SIFT3D_CUDA_TINY_VOX") ? atoi(getenv("SIFT3D_CUDA_TINY_VOX")) : kTinyMaxVox;
+    const int tiny_vox = tiny_vox_env < kTinyMaxVox ? tiny_vox_env : kTinyMaxVox;
     if (!slab && !no_tiny) {
         for (int o = from_seed ? 0 : 1; o < noct; o++)
-            if (ctx->level(o, 0).nvox() <= (size_t) kTinyMaxVox) {
+            if (ctx->level(o, 0).nvox() <= (size_t) tiny_vox) {
                 if (noct - o <= kTinyMaxOct) tiny_from = o;
                 break;
             }
