@@ -421,11 +421,10 @@ static int launch_fused_t(cudaStream_t st, const FusedParams &P, int occ) {
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return 1;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_once;
+    if (attr_once.first()) {
         S3D_CK(cudaFuncSetAttribute(blur_fused_unit_kernel<HW, TY>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int) SMEM));
-        attr_set = true;
     }
     const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
     const int nzr = P.z1 - P.z0;
@@ -478,11 +477,10 @@ static int launch_half_t(cudaStream_t st, const FusedParams &P, int nzc) {
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return 1;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceOnce attr_once;
+    if (attr_once.first()) {
         S3D_CK(cudaFuncSetAttribute(blur_fused_half_kernel<HW, TY>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int) SMEM));
-        attr_set = true;
     }
     dim3 grid((unsigned) ((P.nx + kFTX - 1) / kFTX), (unsigned) ((P.ny + TY - 1) / TY), (unsigned) nzc);
     blur_fused_half_kernel<HW, TY><<<grid, 8 * TY, SMEM, st>>>(tmap, P);
@@ -726,11 +724,10 @@ tiny_octaves_kernel(const TinyChainParams P) {
 
 int launch_tiny_octaves(cudaStream_t st, const TinyChainParams &P, uint64_t *launches) {
     const size_t dyn = (size_t) (4 * kTinyMaxVox + kTinyMaxVox / 8 + 64) * sizeof(float);
-    static bool attr = false;
-    if (!attr) {
+    static PerDeviceOnce attr_once;
+    if (attr_once.first()) {
         S3D_CK(cudaFuncSetAttribute(tiny_octaves_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int) dyn));
-        attr = true;
     }
     tiny_octaves_kernel<<<1, kTinyThreads, dyn, st>>>(P);
     if (launches) *launches += 1;

@@ -33,6 +33,20 @@ struct Level {
 };
 
 // Taps passed by value in the kernel parameter bank (constant memory).
+// Function attributes and __constant__ symbols belong to a device: one-time set-up is done once
+// PER DEVICE (a process may hold detectors on several GPUs, sift3d_detector_set_device).
+constexpr int kMaxDevices = 64;
+struct PerDeviceOnce {
+    bool done[kMaxDevices] = {};
+    bool first() {  // true the first time it is called on the current device
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return true;
+        if (done[dev]) return false;
+        done[dev] = true;
+        return true;
+    }
+};
+
 constexpr int kMaxParamTaps = 33;  // half-width <= 16
 struct TapsParam {
     float k[kMaxParamTaps];

@@ -800,8 +800,8 @@ constexpr int kCellBins = 8 * kVerts;  // bins one floor cell can touch
 __constant__ unsigned char c_cell_order[64];
 
 static int upload_cell_order() {
-    static bool done = false;
-    if (done) return 0;
+    static PerDeviceOnce once;
+    if (!once.first()) return 0;
     unsigned char order[64];
     int key[64];
     for (int c = 0; c < 64; c++) {
@@ -818,7 +818,6 @@ static int upload_cell_order() {
                 order[j] = t;
             }
     S3D_CK(cudaMemcpyToSymbol(c_cell_order, order, sizeof(order)));
-    done = true;
     return 0;
 }
 
@@ -1262,12 +1261,11 @@ int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_ro
     static const bool force_v3 = getenv("SIFT3D_CUDA_DESC_V3") != nullptr;
     if (!force_rows && !force_v3) {
         const size_t dyn4 = (size_t) (kDescThreads / 32) * kCellBins * 32 * sizeof(float);
-        static bool attr4 = false;
-        if (!attr4) {
+        static PerDeviceOnce attr4;
+        if (attr4.first()) {
             if (upload_cell_order()) return -1;
             S3D_CK(cudaFuncSetAttribute(descriptor_cell_kernel,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int) dyn4));
-            attr4 = true;
         }
         descriptor_cell_kernel<<<(unsigned) n, kDescThreads, dyn4, st>>>(d_jobs, n, d_desc);
         if (launches) *launches += 1;
@@ -1277,12 +1275,10 @@ int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_ro
     const size_t dyn = ((size_t) max_rows + 1) * 4 + (size_t) max_rows * 2 + 16;
     const size_t kMaxDyn = 96 * 1024;
     if (!force_rows && max_rows >= 1 && dyn <= kMaxDyn) {
-        static size_t attr = 0;
-        if (dyn > attr) {
+        static PerDeviceOnce attr_flat;
+        if (attr_flat.first())
             S3D_CK(cudaFuncSetAttribute(descriptor_flat_kernel,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kMaxDyn));
-            attr = kMaxDyn;
-        }
         descriptor_flat_kernel<<<(unsigned) n, kDescThreads, dyn, st>>>(d_jobs, n, d_desc, max_rows);
     } else {
         descriptor_rows_kernel<<<(unsigned) n, kDescThreads, 0, st>>>(d_jobs, n, d_desc);
