@@ -31,7 +31,8 @@ namespace s3d {
 template <typename T> struct Samp;
 template <> struct Samp<float> {
     static __device__ __forceinline__ float zero() { return 0.0f; }
-    static __device__ __forceinline__ float ld(const float *p) { return *p; }
+    template <bool ROWS>
+    static __device__ __forceinline__ float ld(const float *p, size_t) { return *p; }
     static __device__ __forceinline__ float div(float a, float dv) { return __fdiv_rn(a, dv); }
     static __device__ __forceinline__ float lerp(float fr, float a, float b) {
         return __fadd_rn(__fmul_rn(__fsub_rn(1.0f, fr), a), __fmul_rn(fr, b));
@@ -42,7 +43,13 @@ template <> struct Samp<float> {
 };
 template <> struct Samp<float4> {
     static __device__ __forceinline__ float4 zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
-    static __device__ __forceinline__ float4 ld(const float *p) { return *reinterpret_cast<const float4 *>(p); }
+    // ROWS: the four voxels are the same column of four lines `ls` apart (x pass over four
+    // rows); else four adjacent columns (16-byte load)
+    template <bool ROWS>
+    static __device__ __forceinline__ float4 ld(const float *p, size_t ls) {
+        if (ROWS) return make_float4(p[0], p[ls], p[2 * ls], p[3 * ls]);
+        return *reinterpret_cast<const float4 *>(p);
+    }
     static __device__ __forceinline__ float4 div(float4 a, float dv) {
         return make_float4(__fdiv_rn(a.x, dv), __fdiv_rn(a.y, dv), __fdiv_rn(a.z, dv), __fdiv_rn(a.w, dv));
     }
@@ -59,16 +66,16 @@ template <> struct Samp<float4> {
     }
 };
 
-template <typename T = float>
+template <typename T = float, bool ROWS = false>
 __device__ __forceinline__ T samp(const float *__restrict__ line, size_t stride, float c,
-                                  int n, bool scale, float dv, int org) {
+                                  int n, bool scale, float dv, int org, size_t ls = 0) {
     int lo = (int) c;  // truncation toward zero, as the C cast
     const float fr = __fsub_rn(c, (float) lo);
     // Only reachable with lo outside [0, n-2] where the reference itself reads out of
     // bounds (single mirror on lines shorter than the kernel); keep the access legal.
     lo = max(org, min(lo, n - 2)) - org;
-    T a = Samp<T>::ld(line + (size_t) lo * stride);
-    T b = Samp<T>::ld(line + (size_t) (lo + 1) * stride);
+    T a = Samp<T>::template ld<ROWS>(line + (size_t) lo * stride, ls);
+    T b = Samp<T>::template ld<ROWS>(line + (size_t) (lo + 1) * stride, ls);
     if (scale) {
         a = Samp<T>::div(a, dv);
         b = Samp<T>::div(b, dv);
@@ -77,12 +84,12 @@ __device__ __forceinline__ T samp(const float *__restrict__ line, size_t stride,
 }
 
 // One output sample of convolve_sep_gen along a line (imutil.c:798-856).
-template <typename T = float>
+template <typename T = float, bool ROWS = false>
 __device__ __forceinline__ T conv_point_generic(const float *__restrict__ line,
                                                 size_t stride, int p, int n,
                                                 const float *__restrict__ taps, int hw,
                                                 float uf, int uhw, bool scale, float dv,
-                                                int sh = -1, int org = 0) {
+                                                int sh = -1, int org = 0, size_t ls = 0) {
     using S = Samp<T>;
     const int start = uhw;
     const int end = n - 2 - uhw;
@@ -99,11 +106,11 @@ __device__ __forceinline__ T conv_point_generic(const float *__restrict__ line,
             const float tap = taps[d + hw];
             const int off = (-d) >> sh;
             const int fi = (-d) & ((1 << sh) - 1);
-            T a = S::ld(q + (ptrdiff_t) off * st);
+            T a = S::template ld<ROWS>(q + (ptrdiff_t) off * st, ls);
             if (scale) a = S::div(a, dv);
             T sv = a;
             if (fi != 0) {  // uniform across the block
-                T b = S::ld(q + (ptrdiff_t) (off + 1) * st);
+                T b = S::template ld<ROWS>(q + (ptrdiff_t) (off + 1) * st, ls);
                 if (scale) b = S::div(b, dv);
                 const float fr = __fmul_rn((float) fi, uf);
                 sv = S::lerp(fr, a, b);
@@ -128,7 +135,7 @@ __device__ __forceinline__ T conv_point_generic(const float *__restrict__ line,
             }
             T sv[4];
 #pragma unroll
-            for (int j = 0; j < 4; j++) sv[j] = samp<T>(line, stride, cs[j], n, scale, dv, org);
+            for (int j = 0; j < 4; j++) sv[j] = samp<T, ROWS>(line, stride, cs[j], n, scale, dv, org, ls);
 #pragma unroll
             for (int j = 0; j < 4; j++) acc = S::acc(acc, taps[d + j + hw], sv[j]);
         }
@@ -136,7 +143,7 @@ __device__ __forceinline__ T conv_point_generic(const float *__restrict__ line,
             const float tap = taps[d + hw];
             const float step = __fmul_rn((float) d, uf);
             c = __fsub_rn(c, step);
-            acc = S::acc(acc, tap, samp<T>(line, stride, c, n, scale, dv, org));
+            acc = S::acc(acc, tap, samp<T, ROWS>(line, stride, c, n, scale, dv, org, ls));
             c = __fadd_rn(c, step);
         }
     } else {
@@ -150,7 +157,7 @@ __device__ __forceinline__ T conv_point_generic(const float *__restrict__ line,
             } else if ((int) c >= dim_end) {
                 c = __fsub_rn(__fsub_rn(__fmul_rn(2.0f, (float) dim_end), c), 0.1f);
             }
-            acc = S::acc(acc, tap, samp<T>(line, stride, c, n, scale, dv, org));
+            acc = S::acc(acc, tap, samp<T, ROWS>(line, stride, c, n, scale, dv, org, ls));
         }
     }
     return acc;
@@ -199,6 +206,30 @@ blur_axis_generic_kernel(const float *__restrict__ src, float *__restrict__ dst,
     if (EPI) {
         if (dogmax != nullptr) block_atomic_max(vmax, dogmax);
     }
+}
+
+// x pass with the same column of four rows per thread (ny % 4 == 0): the sample coordinates
+// depend on x only, so one coordinate chain serves four voxels (scalar loads, coalesced
+// across the warp as before).
+__global__ void __launch_bounds__(256)
+blur_axis_generic_rows4_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny,
+                               int nz, const float *__restrict__ taps, int hw, float uf, int uhw,
+                               const float *__restrict__ divisor, int sh, int zoff) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = 4 * (blockIdx.y * blockDim.y + threadIdx.y);
+    const int z = blockIdx.z + zoff;
+    if (x >= nx || y >= ny) return;
+    const size_t row = ((size_t) z * ny + (size_t) y) * nx;
+    float dv = 0.0f;
+    if (divisor != nullptr) dv = *divisor;
+    const bool scale = dv != 0.0f;
+    const float4 o = conv_point_generic<float4, true>(src + row, 1, x, nx, taps, hw, uf, uhw, scale, dv, sh, 0,
+                                                      (size_t) nx);
+    float *q = dst + row + x;
+    q[0] = o.x;
+    q[(size_t) nx] = o.y;
+    q[2 * (size_t) nx] = o.z;
+    q[3 * (size_t) nx] = o.w;
 }
 
 // y or z pass with four x-adjacent voxels per thread (nx % 4 == 0, 16-byte aligned arrays):
@@ -714,9 +745,18 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         xsrc = dst;
         d_divisor = nullptr;
     }
-    blur_axis_generic_kernel<0, false><<<ggrid_xy, gblock, 0, st>>>(
-        xsrc, tmp_a, nx, ny, nz, d_taps, hw, ax.uf, ax.uhw, d_divisor, nullptr, nullptr, nullptr, ax.sh, zlo, 0);
     static const bool no_vec = getenv("SIFT3D_CUDA_NO_VEC4") != nullptr;
+    if (!no_vec && ny % 4 == 0) {
+        const unsigned by4 = gblock.y < (unsigned) (ny / 4) ? gblock.y : (unsigned) (ny / 4);
+        const dim3 rblock((unsigned) bx, by4 > 0 ? by4 : 1, 1);
+        const dim3 rgrid((unsigned) ((nx + bx - 1) / bx), (unsigned) ((ny / 4 + rblock.y - 1) / rblock.y),
+                         (unsigned) (zhi - zlo));
+        blur_axis_generic_rows4_kernel<<<rgrid, rblock, 0, st>>>(xsrc, tmp_a, nx, ny, nz, d_taps, hw, ax.uf,
+                                                             ax.uhw, d_divisor, ax.sh, zlo);
+    } else {
+        blur_axis_generic_kernel<0, false><<<ggrid_xy, gblock, 0, st>>>(
+            xsrc, tmp_a, nx, ny, nz, d_taps, hw, ax.uf, ax.uhw, d_divisor, nullptr, nullptr, nullptr, ax.sh, zlo, 0);
+    }
     const bool vec4 = !no_vec && nx % 4 == 0 && nx >= 16 &&
                       (((uintptr_t) tmp_a | (uintptr_t) tmp_b | (uintptr_t) dst | (uintptr_t) dog_prev |
                         (uintptr_t) 0) & 15) == 0;
