@@ -624,9 +624,11 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         if (o == 0 && early_levels > 0 && run_extrema(0, 0, early_levels)) return -1;
     }
     // Phase B, the bulk: remaining levels and the extrema scan of each octave. Octave 0's
-    // one-wave kernels would otherwise occupy every SM while octave 1 still has to produce
-    // the seed of octave 2, so octave 0 resumes only after octave 1's seed level.
-    static const int wait_env = getenv("SIFT3D_CUDA_SEEDWAIT") ? atoi(getenv("SIFT3D_CUDA_SEEDWAIT")) : 1;
+    // one-wave kernels would occupy every SM while octave 1 still has to produce the seed of
+    // octave 2; instead of waiting for that seed (SIFT3D_CUDA_SEEDWAIT >= 0: wait for the seed
+    // event of that octave) its first bulk level starts at once on 148 - 40 SMs and the later
+    // ones on 148 - 14 (sweeps in DESIGN.md section 3.5).
+    static const int wait_env = getenv("SIFT3D_CUDA_SEEDWAIT") ? atoi(getenv("SIFT3D_CUDA_SEEDWAIT")) : -1;
     {
         int wi = wait_env < noct - 2 ? wait_env : noct - 2;
         if (wi < 0) wi = 0;
@@ -635,6 +637,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     // Octave 0's remaining levels share the device with the other octaves' streams: leave
     // them some SMs (see set_fused_sm_reserve).
     static const int reserve_env = getenv("SIFT3D_CUDA_RESERVE") ? atoi(getenv("SIFT3D_CUDA_RESERVE")) : 14;
+    static const int reserve_first = getenv("SIFT3D_CUDA_RESERVE_FIRST") ? atoi(getenv("SIFT3D_CUDA_RESERVE_FIRST")) : 40;
     if (noct > 1 && !serial) set_fused_sm_reserve(reserve_env);
     // The bulk levels of octave o >= 1 are not on the seed chain; held back until the chain is
     // `bulk_wait` octaves further on they do not take the reserved SMs from it.
@@ -648,8 +651,13 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             const int we = o + bulk_wait < last_seed_ev ? o + bulk_wait : last_seed_ev;
             if (we > o) S3D_CK(cudaStreamWaitEvent(stream_of(o), ctx->ev_seed[we], 0));
         }
-        for (int s = (ds_level + 1 > sfirst ? ds_level + 1 : sfirst); s < nlev - 1 && !rc; s++)
+        for (int s = (ds_level + 1 > sfirst ? ds_level + 1 : sfirst); s < nlev - 1 && !rc; s++) {
+            // the first bulk level of octave 0 may start while octave 1 still works on its seed
+            // chain (wait_env < 0): it then leaves more SMs free than the later ones
+            if (o == 0 && noct > 1 && !serial)
+                set_fused_sm_reserve(s == ds_level + 1 ? reserve_first : reserve_env);
             rc = run_level(o, s);
+        }
         if (o == 0) set_fused_sm_reserve(0);
         if (rc) return -1;
         if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_PYR], st));
