@@ -123,8 +123,17 @@ struct OctaveInfo {  // what the per-candidate kernels need to know about one oc
     int nx, ny, nz;
     float ux, uy, uz;  // level units narrowed to float (sift.c:88-90)
 };
+// One voxel of an orientation window: integer offset from the candidate and its weight. The
+// window of a candidate is a sphere around INTEGER coordinates (sift.c:1124), so offsets and
+// weights are the same for every candidate of a keypoint level and are tabulated once.
+struct OrientEntry {
+    int dx, dy, dz;
+    float w;
+};
 // Everything the orientation kernel needs to walk the candidate regions of all octaves.
 struct OrientPlan {
+    const OrientEntry *tab[SIFT3D_CUDA_MAX_OCTAVES][SIFT3D_CUDA_MAX_FILTERS];  // window tables, or all NULL
+    const int *ntab;  // entries of tab[o][s] at [o * SIFT3D_CUDA_MAX_FILTERS + s]
     OctaveInfo oct[SIFT3D_CUDA_MAX_OCTAVES];
     int base[SIFT3D_CUDA_MAX_OCTAVES];  // first slot of the octave's candidate region
     int cap[SIFT3D_CUDA_MAX_OCTAVES];
@@ -133,6 +142,11 @@ struct OrientPlan {
 // One persistent launch over the candidates of every octave (counts read on the device,
 // work handed out through *d_work, which must be zero). Output slot = rank of the
 // candidate in the concatenated (o, s, z, y, x) order.
+// Fill the window tables of plan `h` (host copy: octave geometry and level scales filled in):
+// `d_entries` has room for orient_table_capacity(h, kp) entries; sets h.tab / h.ntab.
+size_t orient_table_capacity(const OrientPlan &h, int kp, size_t off[SIFT3D_CUDA_MAX_OCTAVES][SIFT3D_CUDA_MAX_FILTERS]);
+int launch_orient_tables(cudaStream_t st, OrientPlan &h, int kp, OrientEntry *d_entries, int *d_counts,
+                         uint64_t *launches);
 int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d_plan,
                       const int *d_counts, int *d_work, double corner_thresh,
                       sift3d_cuda_keypoint *d_out, uint64_t *launches,

@@ -158,8 +158,42 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
     // One (y, z) row of the window per thread at a time; within a row only the chord that
     // can pass the sphere test is walked (the exact test stays per voxel).
     (void) total;
+    const OrientEntry *__restrict__ tab = plan->tab[oi][s];
+    if (tab != nullptr) {
+        // Tabulated window: the sphere around integer coordinates is the same set of offsets,
+        // with the same weights, for every candidate of this level (build_orient_tables_kernel
+        // evaluates the reference's test and weight once per offset). Flat list: every lane has
+        // work, no distance or exp arithmetic per voxel.
+        const int ne = plan->ntab[oi * SIFT3D_CUDA_MAX_FILTERS + s];
+        for (int e = threadIdx.x; e < ne; e += kOrientThreads) {
+            const int4 E = *reinterpret_cast<const int4 *>(tab + e);
+            const int x = kx + E.x, y = ky + E.y, z = kz + E.z;
+            // window clamps of IM_LOOP_SPHERE_START (sift.c:91-99)
+            if (x < 1 || x > nx - 2 || y < 1 || y > ny - 2 || z < 1 || z > nz - 2) continue;
+            const float w = __int_as_float(E.w);
+            const float *__restrict__ q = img + (size_t) z * zs + (size_t) y * ys + (size_t) x;
+            float vx = __fmul_rn(0.5f, __fsub_rn(q[1], q[-1]));
+            float vy = __fmul_rn(0.5f, __fsub_rn(q[ys], q[-(ptrdiff_t) ys]));
+            float vz = __fmul_rn(0.5f, __fsub_rn(q[zs], q[-(ptrdiff_t) zs]));
+            vx = __fmul_rn(vx, ixu);
+            vy = __fmul_rn(vy, iyu);
+            vz = __fmul_rn(vz, izu);
+            const double wd = (double) w;
+            const double dvx = (double) vx, dvy = (double) vy, dvz = (double) vz;
+            const double wx = dvx * wd, wy = dvy * wd, wz = dvz * wd;
+            a00 = fma(dvx, wx, a00);
+            a01 = fma(dvx, wy, a01);
+            a02 = fma(dvx, wz, a02);
+            a11 = fma(dvy, wy, a11);
+            a12 = fma(dvy, wz, a12);
+            a22 = fma(dvz, wz, a22);
+            gx += (double) __fmul_rn(vx, w);
+            gy += (double) __fmul_rn(vy, w);
+            gz += (double) __fmul_rn(vz, w);
+        }
+    }
     const float rad2f_hi = (float) rad2 * 1.0001f;
-    const int nrows = wx > 0 ? wy * wz : 0;
+    const int nrows = (tab == nullptr && wx > 0) ? wy * wz : 0;
     for (int r = threadIdx.x; r < nrows; r += kOrientThreads) {
         const int y = y0 + r % wy, z = z0 + r / wy;
         const float dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);
@@ -270,6 +304,120 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
     // oriented independently, as each finishes, without knowing the counts of the others
     out[plan->base[oi] + (ci - s_first[oi])] = kp;
   }  // candidates
+}
+
+// One CTA per (octave, keypoint level): offsets (z, y, x ascending, the reference's loop order)
+// of the voxels inside the sphere, with their weights -- the same expressions as the per-voxel
+// path of orient_all_kernel, evaluated for a candidate at the origin ((float) x - cx is the
+// exact integer offset).
+struct OrientTableJob {
+    OrientEntry *out;
+    int *count;
+    int rx, ry, rz;  // half extents of the box that is scanned
+    float ux, uy, uz;
+    double sd;
+};
+struct OrientTableJobs {
+    OrientTableJob job[64];
+};
+constexpr int kTabThreads = 256;
+__global__ void __launch_bounds__(kTabThreads)
+build_orient_tables_kernel(const OrientTableJobs J) {
+    const OrientTableJob &T = J.job[blockIdx.x];
+    __shared__ int wcount[kTabThreads / 32];
+    __shared__ int base_sh;
+    const double sigma = kOriSigFctr * T.sd;
+    const double rad = sigma * kOriRadFctr;
+    const double rad2 = rad * rad;
+    const double nhs = -0.5 / (sigma * sigma);
+    const int bx = 2 * T.rx + 1, by = 2 * T.ry + 1, bz = 2 * T.rz + 1;
+    const int total = bx * by * bz;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) base_sh = 0;
+    __syncthreads();
+    for (int i0 = 0; i0 < total; i0 += kTabThreads) {
+        const int i = i0 + threadIdx.x;
+        bool in = false;
+        int dxi = 0, dyi = 0, dzi = 0;
+        float w = 0.0f;
+        if (i < total) {
+            dxi = i % bx - T.rx;
+            dyi = (i / bx) % by - T.ry;
+            dzi = i / (bx * by) - T.rz;
+            const float dx = __fmul_rn((float) dxi, T.ux);
+            const float dy = __fmul_rn((float) dyi, T.uy);
+            const float dz = __fmul_rn((float) dzi, T.uz);
+            const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+            in = !((double) sq > rad2);
+            w = expf((float) ((double) sq * nhs));
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, in);
+        if (lane == 0) wcount[warp] = __popc(m);
+        __syncthreads();
+        int before = base_sh;
+        for (int k = 0; k < warp; k++) before += wcount[k];
+        if (in) {
+            OrientEntry e;
+            e.dx = dxi; e.dy = dyi; e.dz = dzi; e.w = w;
+            T.out[before + __popc(m & ((1u << lane) - 1u))] = e;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int tot = 0;
+            for (int k = 0; k < kTabThreads / 32; k++) tot += wcount[k];
+            base_sh += tot;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *T.count = base_sh;
+}
+
+static void orient_box(const OctaveInfo &info, int s, int r[3]) {
+    const double rad = kOriSigFctr * info.sd[s] * kOriRadFctr;
+    r[0] = (int) ceil(rad / (double) info.ux) + 1;
+    r[1] = (int) ceil(rad / (double) info.uy) + 1;
+    r[2] = (int) ceil(rad / (double) info.uz) + 1;
+}
+
+size_t orient_table_capacity(const OrientPlan &h, int kp,
+                             size_t off[SIFT3D_CUDA_MAX_OCTAVES][SIFT3D_CUDA_MAX_FILTERS]) {
+    size_t total = 0;
+    if (h.noct * kp > 64) return 0;  // OrientTableJobs holds 64 tables
+    for (int o = 0; o < h.noct; o++)
+        for (int s = 0; s < kp; s++) {
+            int r[3];
+            orient_box(h.oct[o], s, r);
+            const double vol = (2.0 * r[0] + 1) * (2.0 * r[1] + 1) * (2.0 * r[2] + 1);
+            if (vol > 4.0e6) return 0;  // absurd units / scales: keep the per-voxel path
+            off[o][s] = total;
+            total += ((size_t) vol + 3) & ~(size_t) 3;  // 16-byte aligned tables
+        }
+    return total;
+}
+
+int launch_orient_tables(cudaStream_t st, OrientPlan &h, int kp, OrientEntry *d_entries, int *d_counts,
+                         uint64_t *launches) {
+    size_t off[SIFT3D_CUDA_MAX_OCTAVES][SIFT3D_CUDA_MAX_FILTERS];
+    if (orient_table_capacity(h, kp, off) == 0) return 1;
+    OrientTableJobs J;
+    int nj = 0;
+    for (int o = 0; o < h.noct; o++)
+        for (int s = 0; s < kp; s++) {
+            OrientTableJob &T = J.job[nj++];
+            int r[3];
+            orient_box(h.oct[o], s, r);
+            T.out = d_entries + off[o][s];
+            T.count = d_counts + o * SIFT3D_CUDA_MAX_FILTERS + s;
+            T.rx = r[0]; T.ry = r[1]; T.rz = r[2];
+            T.ux = h.oct[o].ux; T.uy = h.oct[o].uy; T.uz = h.oct[o].uz;
+            T.sd = h.oct[o].sd[s];
+            h.tab[o][s] = T.out;
+        }
+    h.ntab = d_counts;
+    build_orient_tables_kernel<<<nj, kTabThreads, 0, st>>>(J);
+    if (launches) *launches += 1;
+    S3D_CK(cudaGetLastError());
+    return 0;
 }
 
 int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d_plan,

@@ -62,6 +62,10 @@ struct sift3d_cuda_ctx {
     cudaEvent_t ev_done[SIFT3D_CUDA_MAX_OCTAVES] = {};
     bool serial = false;                // $SIFT3D_CUDA_SERIAL: everything on one stream
     DevBuf orient_plan;                 // OrientPlan on the device
+    DevBuf orient_tab, orient_ntab;     // orientation window tables (OrientEntry) and their sizes
+    double orient_key[8] = {};          // geometry the tables were built for
+    bool orient_tab_ok = false;
+    const OrientEntry *orient_tab_ptr[SIFT3D_CUDA_MAX_OCTAVES][SIFT3D_CUDA_MAX_FILTERS] = {};
     OrientPlan *h_plan = nullptr;       // pinned staging copy
     DevBuf work;                        // work counter of the persistent orientation kernel
     DevBuf taps;                        // (1 + filters) * SIFT3D_CUDA_MAX_TAPS floats
@@ -172,6 +176,8 @@ void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx) {
     ctx->tmp_b.release();
     ctx->tmp_side.release();
     ctx->orient_plan.release();
+    ctx->orient_tab.release();
+    ctx->orient_ntab.release();
     ctx->work.release();
     for (int o = 0; o < SIFT3D_CUDA_MAX_OCTAVES; o++) {
         if (ctx->oct_stream[o]) {
@@ -493,6 +499,39 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             info.ux = (float) L.ux; info.uy = (float) L.uy; info.uz = (float) L.uz;
             H.base[o] = ctx->cand_base[o];
             H.cap[o] = ctx->cand_cap[o];
+        }
+        // Orientation window tables: rebuilt only when the geometry they depend on changes
+        // (units and level scales; one tiny launch), otherwise the cached pointers are reused.
+        static const bool no_tab = getenv("SIFT3D_CUDA_NO_ORIENT_TABLES") != nullptr;
+        if (!no_tab) {
+            const Level &L0 = ctx->level(0, 0);
+            const double key[8] = {(double) noct, (double) kp, L0.ux, L0.uy, L0.uz, L0.scale,
+                                   ctx->level(noct - 1, kp - 1).scale, (double) ctx->base_octave};
+            if (!ctx->orient_tab_ok || memcmp(key, ctx->orient_key, sizeof(key)) != 0) {
+                ctx->orient_tab_ok = false;
+                size_t off[SIFT3D_CUDA_MAX_OCTAVES][SIFT3D_CUDA_MAX_FILTERS];
+                const size_t cap = orient_table_capacity(H, kp, off);
+                if (cap > 0 && cap * sizeof(OrientEntry) <= ((size_t) 256 << 20)) {
+                    if (ctx->orient_tab.ensure(cap * sizeof(OrientEntry)) ||
+                        ctx->orient_ntab.ensure(sizeof(int) * SIFT3D_CUDA_MAX_OCTAVES * SIFT3D_CUDA_MAX_FILTERS))
+                        return -1;
+                    const int r = launch_orient_tables(st, H, kp, (OrientEntry *) ctx->orient_tab.p,
+                                                       (int *) ctx->orient_ntab.p, &ctx->launches);
+                    if (r < 0) return -1;
+                    if (r == 0) {
+                        memcpy(ctx->orient_tab_ptr, H.tab, sizeof(H.tab));
+                        memcpy(ctx->orient_key, key, sizeof(key));
+                        ctx->orient_tab_ok = true;
+                    }
+                }
+            }
+            if (ctx->orient_tab_ok) {
+                memcpy(H.tab, ctx->orient_tab_ptr, sizeof(H.tab));
+                H.ntab = (const int *) ctx->orient_ntab.p;
+            } else {
+                memset(H.tab, 0, sizeof(H.tab));
+                H.ntab = nullptr;
+            }
         }
         S3D_CK(cudaMemcpyAsync(ctx->orient_plan.p, &H, sizeof(H), cudaMemcpyHostToDevice, st));
     }
