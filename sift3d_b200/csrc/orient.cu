@@ -91,8 +91,9 @@ __device__ __forceinline__ T warp_sum(T v) {
     return v;
 }
 
-constexpr int kOrientThreads = 128;
 
+constexpr int kOrientBatch = 16;  // windows per CTA between two finishing steps (<= 32)
+template <int kOrientThreads>
 __global__ void __launch_bounds__(kOrientThreads)
 orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict__ plan,
                   const int *__restrict__ counts, int *__restrict__ work, double corner_thresh,
@@ -100,6 +101,7 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
     __shared__ int s_first[SIFT3D_CUDA_MAX_OCTAVES + 1];  // rank of each octave's first candidate
     __shared__ int s_ci;
     __shared__ double red[kOrientThreads / 32][9];
+    __shared__ double sums[kOrientBatch][9];
     const int noct = plan->noct;
     if (threadIdx.x == 0) {
         int acc = 0;
@@ -114,13 +116,21 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
     // candidates of octaves [o_begin, o_end): ranks [s_first[o_begin], s_first[o_end])
     const int total = s_first[min(o_end, noct)];
     const int first = s_first[min(o_begin, noct)];
+    // Candidates are taken in batches: the CTA sums the windows of a batch one after the other,
+    // then threads 0 .. nb-1 finish one candidate each (eigen-decomposition in double, tests,
+    // R) in lockstep. Finished by a single thread after every window, the serial part (~25 us
+    // of double divisions and square roots) was three quarters of the kernel.
+    const int batch = max(1, min(kOrientBatch, (total - first) / (int) gridDim.x));
   for (;;) {
     // dynamic hand-out: windows differ 4x in size between keypoint levels
     __syncthreads();
-    if (threadIdx.x == 0) s_ci = first + atomicAdd(work, 1);
+    if (threadIdx.x == 0) s_ci = first + atomicAdd(work, batch);
     __syncthreads();
-    const int ci = s_ci;
-    if (ci >= total) break;
+    const int ci0 = s_ci;
+    if (ci0 >= total) break;
+    const int nb = min(batch, total - ci0);
+   for (int b = 0; b < nb; b++) {
+    const int ci = ci0 + b;
     int oi = 0;
     while (ci >= s_first[oi + 1]) oi++;
     const OctaveInfo &info = plan->oct[oi];
@@ -165,16 +175,27 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
         // evaluates the reference's test and weight once per offset). Flat list: every lane has
         // work, no distance or exp arithmetic per voxel.
         const int ne = plan->ntab[oi * SIFT3D_CUDA_MAX_FILTERS + s];
-        for (int e = threadIdx.x; e < ne; e += kOrientThreads) {
-            const int4 E = *reinterpret_cast<const int4 *>(tab + e);
+        // Branch-free body, four entries in flight per thread: an entry outside the window
+        // clamps of IM_LOOP_SPHERE_START (sift.c:91-99), or past the end of the table, reads
+        // the candidate's own voxel with weight 0 (adds exactly +0), so that the compiler can
+        // issue the 4 x 6 loads of an unrolled step together -- the loop is bound by the
+        // latency of table entry -> voxel loads, not by arithmetic.
+        const float *__restrict__ q0 = img + (size_t) kz * zs + (size_t) ky * ys + (size_t) kx;
+        const ptrdiff_t pys = (ptrdiff_t) ys, pzs = (ptrdiff_t) zs;
+        const int nsteps = (ne + kOrientThreads - 1) / kOrientThreads;
+#pragma unroll 4
+        for (int k = 0; k < nsteps; k++) {
+            const int e = k * kOrientThreads + threadIdx.x;
+            int4 E = make_int4(0, 0, 0, 0);
+            if (e < ne) E = __ldg(reinterpret_cast<const int4 *>(tab + e));
             const int x = kx + E.x, y = ky + E.y, z = kz + E.z;
-            // window clamps of IM_LOOP_SPHERE_START (sift.c:91-99)
-            if (x < 1 || x > nx - 2 || y < 1 || y > ny - 2 || z < 1 || z > nz - 2) continue;
-            const float w = __int_as_float(E.w);
-            const float *__restrict__ q = img + (size_t) z * zs + (size_t) y * ys + (size_t) x;
+            const bool in = x >= 1 && x <= nx - 2 && y >= 1 && y <= ny - 2 && z >= 1 && z <= nz - 2;
+            const float w = in ? __int_as_float(E.w) : 0.0f;
+            const ptrdiff_t off = in ? (ptrdiff_t) E.z * pzs + (ptrdiff_t) E.y * pys + (ptrdiff_t) E.x : 0;
+            const float *__restrict__ q = q0 + off;
             float vx = __fmul_rn(0.5f, __fsub_rn(q[1], q[-1]));
-            float vy = __fmul_rn(0.5f, __fsub_rn(q[ys], q[-(ptrdiff_t) ys]));
-            float vz = __fmul_rn(0.5f, __fsub_rn(q[zs], q[-(ptrdiff_t) zs]));
+            float vy = __fmul_rn(0.5f, __fsub_rn(q[pys], q[-pys]));
+            float vz = __fmul_rn(0.5f, __fsub_rn(q[pzs], q[-pzs]));
             vx = __fmul_rn(vx, ixu);
             vy = __fmul_rn(vy, iyu);
             vz = __fmul_rn(vz, izu);
@@ -242,13 +263,28 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
         if (lane == 0) red[warp][k] = r;
     }
     __syncthreads();
-    if (threadIdx.x != 0) continue;
-#pragma unroll
-    for (int k = 0; k < 9; k++) {
+    if (threadIdx.x < 9) {
         double r = 0;
-        for (int wv = 0; wv < kOrientThreads / 32; wv++) r += red[wv][k];
-        vals[k] = r;
+        for (int wv = 0; wv < kOrientThreads / 32; wv++) r += red[wv][threadIdx.x];
+        sums[b][threadIdx.x] = r;
     }
+    __syncthreads();  // red is reused by the next window
+   }  // windows of the batch
+    if (threadIdx.x >= nb) continue;
+    // ---- one candidate per thread from here on
+    const int ci = ci0 + threadIdx.x;
+    int oi = 0;
+    while (ci >= s_first[oi + 1]) oi++;
+    const OctaveInfo &info = plan->oct[oi];
+    const Cand cd = sorted[plan->base[oi] + (ci - s_first[oi])];
+    const int s = (int) (cd.key >> 60);
+    const int kz = (int) ((cd.key >> 40) & 0xFFFFF);
+    const int ky = (int) ((cd.key >> 20) & 0xFFFFF);
+    const int kx = (int) (cd.key & 0xFFFFF);
+    const double sd = info.sd[s];
+    double vals[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) vals[k] = sums[threadIdx.x][k];
 
     sift3d_cuda_keypoint kp;
     kp.o = info.o;
@@ -429,9 +465,16 @@ int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d
     // Octave 0 on the main stream: persistent grid (148 SMs x the CTAs that fit). Other octaves
     // run on side streams while octave 0's one-wave blurs still need whole SMs: many short
     // CTAs (about one candidate each) so that an SM is never held for long.
-    const int grid = o_begin == 0 ? kNumSMs * 5 : kNumSMs * 8;
-    orient_all_kernel<<<grid, kOrientThreads, 0, st>>>(d_sorted, d_plan, d_counts, d_work, corner_thresh,
-                                                   d_out, o_begin, o_end);
+    // The small octaves are the tail of detect and hold few candidates: there the time of ONE
+    // candidate counts (6.3k window voxels over 128 threads = 50 dependent load steps, 40 us),
+    // so their CTAs are four times as wide.
+    static const int wide_env = getenv("SIFT3D_CUDA_ORIENT_WIDE") ? atoi(getenv("SIFT3D_CUDA_ORIENT_WIDE")) : 0;
+    if (o_begin == 0 || !wide_env)
+        orient_all_kernel<128><<<o_begin == 0 ? kNumSMs * 5 : kNumSMs * 8, 128, 0, st>>>(
+            d_sorted, d_plan, d_counts, d_work, corner_thresh, d_out, o_begin, o_end);
+    else
+        orient_all_kernel<512><<<kNumSMs * 2, 512, 0, st>>>(d_sorted, d_plan, d_counts, d_work, corner_thresh,
+                                                           d_out, o_begin, o_end);
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
     return 0;
