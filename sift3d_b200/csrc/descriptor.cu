@@ -34,6 +34,7 @@ struct MeshConst {
     float q[kFaces][3];    // t x e1
     float e2q[kFaces];     // e2 . q
     float ctr[kFaces][3];  // v0 + v1 + v2 (direction of the face centre; selection only)
+    float minv[kFaces][12];  // rows of [v0 v1 v2]^-1, padded to 4 (fast-path barycentric solve)
     int idx[kFaces][3];    // histogram bin of each barycentric weight
     // face whose centre is nearest to a direction, by octant (bit 0: x < 0, bit 1: y < 0,
     // bit 2: z < 0) and by which of the 4 candidate centres of that octant wins
@@ -91,6 +92,22 @@ int upload_mesh(void) {
         }
         cross3(m.t[i], m.e1[i], m.q[i]);
         m.e2q[i] = dot3(m.e2[i], m.q[i]);
+        // [v0 v1 v2]^-1 (double, then narrowed): b' = Minv g is proportional to the barycentric
+        // coordinates of the point where the ray g leaves the face, b = b' / sum(b')
+        {
+            const double A[3][3] = {{v0[0], v1[0], v2[0]}, {v0[1], v1[1], v2[1]}, {v0[2], v1[2], v2[2]}};
+            const double det = A[0][0] * (A[1][1] * A[2][2] - A[1][2] * A[2][1]) -
+                               A[0][1] * (A[1][0] * A[2][2] - A[1][2] * A[2][0]) +
+                               A[0][2] * (A[1][0] * A[2][1] - A[1][1] * A[2][0]);
+            for (int r = 0; r < 3; r++) {
+                for (int c = 0; c < 3; c++) {
+                    const int r1 = (r + 1) % 3, r2 = (r + 2) % 3, c1 = (c + 1) % 3, c2 = (c + 2) % 3;
+                    // inverse = adjugate / det; entry (r, c) is the cofactor of (c, r)
+                    m.minv[i][4 * r + c] = (float) ((A[c1][r1] * A[c2][r2] - A[c1][r2] * A[c2][r1]) / det);
+                }
+                m.minv[i][4 * r + 3] = 0.0f;
+            }
+        }
     }
     // Nearest-centre lookup. By symmetry a direction in the octant with signs (sx, sy, sz)
     // is nearest to one of 4 face centres: the octant's own face (1,1,1) and the three
@@ -827,6 +844,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     __shared__ unsigned hlo[kPadNumel];
     __shared__ int hhi[kPadNumel];
     __shared__ __align__(16) float smesh[kFaces * 16];
+    __shared__ __align__(16) float sminv[kFaces * 12];
     __shared__ int sidx[kFaces * 3];
     __shared__ unsigned char slut[32];
     __shared__ double red[kDescThreads / 32];
@@ -854,6 +872,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         }
         fm[12] = c_mesh.e2q[tid];
         fm[13] = fm[14] = fm[15] = 0.0f;
+        for (int k = 0; k < 12; k++) sminv[tid * 12 + k] = c_mesh.minv[tid][k];
     }
     if (tid < 32) slut[tid] = c_mesh.lut[tid >> 2][tid & 3];
     if (tid == 0) next_cell = 0;
@@ -1102,8 +1121,25 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             const int oct = (rx < 0.0f ? 1 : 0) | (ry2 < 0.0f ? 2 : 0) | (rz2 < 0.0f ? 4 : 0);
             const int best = slut[oct * 4 + which];
             float bx, by, bz;
-            const bool hit = face_hit_s<kDescFma>(smesh + best * 16, rx, ry2, rz2, bx, by, bz) && bx > 1e-5f &&
-                             by > 1e-5f && bz > 1e-5f;
+            bool hit;
+            if (kDescFma) {
+                // b' = [v0 v1 v2]^-1 r, b = b' / sum(b'): 9 multiply-adds and one reciprocal instead
+                // of the cross products of Moeller-Trumbore (same point, a few ulp apart); a
+                // direction within 1e-5 of an edge goes to the literal scan as before
+                const float4 m0 = *reinterpret_cast<const float4 *>(sminv + best * 12);
+                const float4 m1 = *reinterpret_cast<const float4 *>(sminv + best * 12 + 4);
+                const float4 m2 = *reinterpret_cast<const float4 *>(sminv + best * 12 + 8);
+                const float p0 = dot3<true>(m0.x, rx, m0.y, ry2, m0.z, rz2);
+                const float p1 = dot3<true>(m1.x, rx, m1.y, ry2, m1.z, rz2);
+                const float p2 = dot3<true>(m2.x, rx, m2.y, ry2, m2.z, rz2);
+                const float sum = p0 + p1 + p2;
+                const float inv = __frcp_rn(sum);
+                bx = p0 * inv; by = p1 * inv; bz = p2 * inv;
+                hit = sum > 0.0f && bx > 1e-5f && by > 1e-5f && bz > 1e-5f;
+            } else {
+                hit = face_hit_s<false>(smesh + best * 16, rx, ry2, rz2, bx, by, bz) && bx > 1e-5f &&
+                      by > 1e-5f && bz > 1e-5f;
+            }
             v.valid = ok;
             v.slow = ok && !hit;  // near an edge: the literal first-hit scan decides
             v.rx = rx; v.ry = ry2; v.rz = rz2; v.n2 = n2;
