@@ -844,7 +844,9 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     __shared__ unsigned hlo[kPadNumel];
     __shared__ int hhi[kPadNumel];
     __shared__ __align__(16) float smesh[kFaces * 16];
-    __shared__ __align__(16) float sminv[kFaces * 12];
+    // fast path, by (octant, which of its 4 candidate faces): rows of [v0 v1 v2]^-1 with the
+    // histogram bin of the row's vertex in .w -- one lookup instead of octant -> face -> rows / bins
+    __shared__ __align__(16) float sfast[32 * 12];
     __shared__ int sidx[kFaces * 3];
     __shared__ unsigned char slut[32];
     __shared__ double red[kDescThreads / 32];
@@ -872,9 +874,13 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         }
         fm[12] = c_mesh.e2q[tid];
         fm[13] = fm[14] = fm[15] = 0.0f;
-        for (int k = 0; k < 12; k++) sminv[tid * 12 + k] = c_mesh.minv[tid][k];
     }
-    if (tid < 32) slut[tid] = c_mesh.lut[tid >> 2][tid & 3];
+    if (tid < 32) {
+        const int f = c_mesh.lut[tid >> 2][tid & 3];
+        slut[tid] = (unsigned char) f;
+        for (int k = 0; k < 12; k++)
+            sfast[tid * 12 + k] = (k & 3) == 3 ? __int_as_float(c_mesh.idx[f][k >> 2] * 32) : c_mesh.minv[f][k];
+    }
     if (tid == 0) next_cell = 0;
 
     const float *__restrict__ img = J.img;
@@ -1066,7 +1072,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             bool valid, slow;
             float rx, ry, rz, n2;
             float b0, b1, b2;
-            int face;
+            int i0, i1, i2;  // float offsets of the three vertex bins in a lane's accumulators
             float fx, fy, fz;
         };
         auto eval_fast = [&](int x, int y, int z, bool active) -> Vox {
@@ -1119,16 +1125,17 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             if (d2 > dbest) { dbest = d2; which = 2; }
             if (d3 > dbest) { dbest = d3; which = 3; }
             const int oct = (rx < 0.0f ? 1 : 0) | (ry2 < 0.0f ? 2 : 0) | (rz2 < 0.0f ? 4 : 0);
-            const int best = slut[oct * 4 + which];
             float bx, by, bz;
             bool hit;
             if (kDescFma) {
                 // b' = [v0 v1 v2]^-1 r, b = b' / sum(b'): 9 multiply-adds and one reciprocal instead
                 // of the cross products of Moeller-Trumbore (same point, a few ulp apart); a
                 // direction within 1e-5 of an edge goes to the literal scan as before
-                const float4 m0 = *reinterpret_cast<const float4 *>(sminv + best * 12);
-                const float4 m1 = *reinterpret_cast<const float4 *>(sminv + best * 12 + 4);
-                const float4 m2 = *reinterpret_cast<const float4 *>(sminv + best * 12 + 8);
+                const float *fe = sfast + (oct * 4 + which) * 12;
+                const float4 m0 = *reinterpret_cast<const float4 *>(fe);
+                const float4 m1 = *reinterpret_cast<const float4 *>(fe + 4);
+                const float4 m2 = *reinterpret_cast<const float4 *>(fe + 8);
+                v.i0 = __float_as_int(m0.w); v.i1 = __float_as_int(m1.w); v.i2 = __float_as_int(m2.w);
                 const float p0 = dot3<true>(m0.x, rx, m0.y, ry2, m0.z, rz2);
                 const float p1 = dot3<true>(m1.x, rx, m1.y, ry2, m1.z, rz2);
                 const float p2 = dot3<true>(m2.x, rx, m2.y, ry2, m2.z, rz2);
@@ -1137,14 +1144,15 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
                 bx = p0 * inv; by = p1 * inv; bz = p2 * inv;
                 hit = sum > 0.0f && bx > 1e-5f && by > 1e-5f && bz > 1e-5f;
             } else {
+                const int best = slut[oct * 4 + which];
                 hit = face_hit_s<false>(smesh + best * 16, rx, ry2, rz2, bx, by, bz) && bx > 1e-5f &&
                       by > 1e-5f && bz > 1e-5f;
+                v.i0 = sidx[best * 3] * 32; v.i1 = sidx[best * 3 + 1] * 32; v.i2 = sidx[best * 3 + 2] * 32;
             }
             v.valid = ok;
             v.slow = ok && !hit;  // near an edge: the literal first-hit scan decides
             v.rx = rx; v.ry = ry2; v.rz = rz2; v.n2 = n2;
             v.b0 = bx; v.b1 = by; v.b2 = bz;
-            v.face = best;
             return v;
         };
         auto eval_slow = [&](Vox &v) {
@@ -1156,7 +1164,8 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             if (face < 0) {  // "unreachable" in the reference (sift.c:1288-1290)
                 v.valid = false;
             } else {
-                v.face = face; v.b0 = bx; v.b1 = by; v.b2 = bz;
+                v.i0 = sidx[face * 3] * 32; v.i1 = sidx[face * 3 + 1] * 32; v.i2 = sidx[face * 3 + 2] * 32;
+                v.b0 = bx; v.b1 = by; v.b2 = bz;
             }
         };
         // SIFT3D_desc_acc_interp (sift.c:1318-1397) into this lane's copy of the cell's
@@ -1166,7 +1175,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             const float m3[3] = {__fmul_rn(mag, v.b0), __fmul_rn(mag, v.b1), __fmul_rn(mag, v.b2)};
             float *a3[3];
 #pragma unroll
-            for (int k = 0; k < 3; k++) a3[k] = wacc + sidx[v.face * 3 + k] * 32 + lane;
+            for (int k = 0; k < 3; k++) a3[k] = wacc + (k == 0 ? v.i0 : (k == 1 ? v.i1 : v.i2)) + lane;
             const float wx[2] = {__fsub_rn(1.0f, v.fx), v.fx};
             const float wy2[2] = {__fsub_rn(1.0f, v.fy), v.fy};
             const float wz2[2] = {__fsub_rn(1.0f, v.fz), v.fz};
