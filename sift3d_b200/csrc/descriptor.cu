@@ -1070,7 +1070,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         // with 4 warps per scheduler a single chain leaves ~45 % of the issue slots empty.
         struct Vox {
             bool valid, slow;
-            float rx, ry, rz, n2;
+            float rx, ry, rz, n2, mag;
             float b0, b1, b2;
             int i0, i1, i2;  // float offsets of the three vertex bins in a lane's accumulators
             float fx, fy, fz;
@@ -1119,11 +1119,9 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             const float d1 = fmaf(kB, ax, kC * az);
             const float d2 = fmaf(kC, ay, kB * az);
             const float d3 = fmaf(kC, ax, kB * ay);
-            int which = 0;
-            float dbest = d0;
-            if (d1 > dbest) { dbest = d1; which = 1; }
-            if (d2 > dbest) { dbest = d2; which = 2; }
-            if (d3 > dbest) { dbest = d3; which = 3; }
+            // first maximum of (d0, d1, d2, d3), as a two-level tree (same ties as a serial scan)
+            const int w01 = d1 > d0 ? 1 : 0, w23 = d3 > d2 ? 3 : 2;
+            const int which = fmaxf(d2, d3) > fmaxf(d0, d1) ? w23 : w01;
             const int oct = (rx < 0.0f ? 1 : 0) | (ry2 < 0.0f ? 2 : 0) | (rz2 < 0.0f ? 4 : 0);
             float bx, by, bz;
             bool hit;
@@ -1152,6 +1150,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             v.valid = ok;
             v.slow = ok && !hit;  // near an edge: the literal first-hit scan decides
             v.rx = rx; v.ry = ry2; v.rz = rz2; v.n2 = n2;
+            v.mag = sqrtf(n2);  // here, not in accumulate(): off the LDS -> FMA -> STS chain
             v.b0 = bx; v.b1 = by; v.b2 = bz;
             return v;
         };
@@ -1171,7 +1170,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         // SIFT3D_desc_acc_interp (sift.c:1318-1397) into this lane's copy of the cell's
         // 8 x 12 bins: corner c = (ddx, ddy, ddz), bin (c, vertex)
         auto accumulate = [&](const Vox &v) {
-            const float mag = sqrtf(v.n2);
+            const float mag = v.mag;
             const float m3[3] = {__fmul_rn(mag, v.b0), __fmul_rn(mag, v.b1), __fmul_rn(mag, v.b2)};
             float *a3[3];
 #pragma unroll
