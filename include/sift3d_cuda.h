@@ -169,6 +169,15 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_fetch_candidates(sift3d_cuda_ctx *ctx,
  * Returns -1 when the records are device resident (use sift3d_cuda_fetch_candidates). */
 SIFT3D_CUDA_EXPORT int sift3d_cuda_candidates_view(sift3d_cuda_ctx *ctx, int octave_index,
                                                    const sift3d_cuda_keypoint **records);
+/* Companion of the view: 8 bytes per candidate (same order) with what the survivor compaction
+ * needs from EVERY candidate -- its strength and whether it survived -- so that the host reads
+ * the 88-byte records of the survivors only (a quarter of the candidates). */
+typedef struct {
+    float strength;
+    int valid;
+} sift3d_cuda_candidate_flag;
+SIFT3D_CUDA_EXPORT int sift3d_cuda_candidates_flags(sift3d_cuda_ctx *ctx, int octave_index,
+                                                    const sift3d_cuda_candidate_flag **flags);
 
 /* Descriptors for num keypoints on the pyramid left by the last detect.
  * desc: num * 768 float32 on the host (or device if desc_on_device). */

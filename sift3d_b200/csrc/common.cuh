@@ -150,7 +150,8 @@ int launch_orient_tables(cudaStream_t st, OrientPlan &h, int kp, OrientEntry *d_
 int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d_plan,
                       const int *d_counts, int *d_work, double corner_thresh,
                       sift3d_cuda_keypoint *d_out, uint64_t *launches,
-                      int o_begin = 0, int o_end = -1);  // octaves [o_begin, o_end); own d_work slot
+                      int o_begin = 0, int o_end = -1,   // octaves [o_begin, o_end); own d_work slot
+                      sift3d_cuda_candidate_flag *d_flags = nullptr);  // (strength, valid) per slot, or NULL
 
 // descriptor.cu
 struct DescJob {

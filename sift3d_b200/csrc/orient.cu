@@ -97,7 +97,8 @@ template <int kOrientThreads>
 __global__ void __launch_bounds__(kOrientThreads)
 orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict__ plan,
                   const int *__restrict__ counts, int *__restrict__ work, double corner_thresh,
-                  sift3d_cuda_keypoint *__restrict__ out, int o_begin, int o_end) {
+                  sift3d_cuda_keypoint *__restrict__ out, int o_begin, int o_end,
+                  sift3d_cuda_candidate_flag *__restrict__ flags) {
     __shared__ int s_first[SIFT3D_CUDA_MAX_OCTAVES + 1];  // rank of each octave's first candidate
     __shared__ int s_ci;
     __shared__ double red[kOrientThreads / 32][9];
@@ -339,6 +340,12 @@ orient_all_kernel(const Cand *__restrict__ sorted, const OrientPlan *__restrict_
     // results stay in the octave's own region (slot = rank within the octave): octaves are
     // oriented independently, as each finishes, without knowing the counts of the others
     out[plan->base[oi] + (ci - s_first[oi])] = kp;
+    if (flags != nullptr) {
+        sift3d_cuda_candidate_flag f;
+        f.strength = kp.strength;
+        f.valid = kp.valid;
+        flags[plan->base[oi] + (ci - s_first[oi])] = f;
+    }
   }  // candidates
 }
 
@@ -458,7 +465,8 @@ int launch_orient_tables(cudaStream_t st, OrientPlan &h, int kp, OrientEntry *d_
 
 int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d_plan,
                       const int *d_counts, int *d_work, double corner_thresh,
-                      sift3d_cuda_keypoint *d_out, uint64_t *launches, int o_begin, int o_end) {
+                      sift3d_cuda_keypoint *d_out, uint64_t *launches, int o_begin, int o_end,
+                      sift3d_cuda_candidate_flag *d_flags) {
     if (o_end < 0) o_end = SIFT3D_CUDA_MAX_OCTAVES;
     if (o_end <= o_begin) return 0;
     // persistent grid: 148 SMs x the CTAs that fit (94 registers x 128 threads -> 5 per SM)
@@ -471,10 +479,10 @@ int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d
     static const int wide_env = getenv("SIFT3D_CUDA_ORIENT_WIDE") ? atoi(getenv("SIFT3D_CUDA_ORIENT_WIDE")) : 0;
     if (o_begin == 0 || !wide_env)
         orient_all_kernel<128><<<o_begin == 0 ? kNumSMs * 5 : kNumSMs * 8, 128, 0, st>>>(
-            d_sorted, d_plan, d_counts, d_work, corner_thresh, d_out, o_begin, o_end);
+            d_sorted, d_plan, d_counts, d_work, corner_thresh, d_out, o_begin, o_end, d_flags);
     else
         orient_all_kernel<512><<<kNumSMs * 2, 512, 0, st>>>(d_sorted, d_plan, d_counts, d_work, corner_thresh,
-                                                           d_out, o_begin, o_end);
+                                                           d_out, o_begin, o_end, d_flags);
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
     return 0;

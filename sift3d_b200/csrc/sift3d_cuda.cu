@@ -80,6 +80,7 @@ struct sift3d_cuda_ctx {
     // and no second synchronisation (48 us + ~30 us per 256^3 volume).
     sift3d_cuda_keypoint *kps_host = nullptr;
     size_t kps_host_bytes = 0;
+    sift3d_cuda_candidate_flag *kflags_host = nullptr;  // behind the records in the same allocation
     sift3d_cuda_keypoint *kps_dev() const {
         return kps_host ? kps_host : (sift3d_cuda_keypoint *) kps.p;  // UVA: same address on the device
     }
@@ -250,7 +251,8 @@ static int plan_candidates(sift3d_cuda_ctx *ctx) {
         ctx->counts.ensure(sizeof(int) * 64))
         return -1;
     static const bool no_host_kps = getenv("SIFT3D_CUDA_NO_HOST_KPS") != nullptr;
-    const size_t kbytes = cand_total * sizeof(sift3d_cuda_keypoint);
+    const size_t rbytes = cand_total * sizeof(sift3d_cuda_keypoint);  // multiple of 8
+    const size_t kbytes = rbytes + cand_total * sizeof(sift3d_cuda_candidate_flag);
     constexpr size_t kKpsHostMax = (size_t) 256 << 20;
     if (!no_host_kps && kbytes <= kKpsHostMax) {
         if (kbytes > ctx->kps_host_bytes) {
@@ -270,6 +272,7 @@ static int plan_candidates(sift3d_cuda_ctx *ctx) {
             cudaGetLastError();
         }
         if (ctx->kps_host) {
+            ctx->kflags_host = (sift3d_cuda_candidate_flag *) ((char *) ctx->kps_host + rbytes);
             ctx->kps.release();
             return 0;
         }
@@ -278,7 +281,8 @@ static int plan_candidates(sift3d_cuda_ctx *ctx) {
         ctx->kps_host = nullptr;
         ctx->kps_host_bytes = 0;
     }
-    if (ctx->kps.ensure(kbytes)) return -1;
+    ctx->kflags_host = nullptr;
+    if (ctx->kps.ensure(rbytes)) return -1;
     return 0;
 }
 
@@ -723,7 +727,8 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_ORDER], st));
         if (launch_orient_all(so, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
                               (const int *) ctx->counts.p, (int *) ctx->work.p + o, corner_thresh,
-                              ctx->kps_dev(), &ctx->launches, o, o + 1))
+                              ctx->kps_dev(), &ctx->launches, o, o + 1,
+                              ctx->kps_host ? ctx->kflags_host : nullptr))
             return -1;
         if (so != st) S3D_CK(cudaEventRecord(ctx->ev_done[o], so));
     }
@@ -851,6 +856,15 @@ int sift3d_cuda_candidates_view(sift3d_cuda_ctx *ctx, int octave_index,
         (size_t) octave_index >= ctx->cand_base.size())
         return -1;
     *records = ctx->kps_host + ctx->cand_base[octave_index];
+    return ctx->h_counts[octave_index];
+}
+
+int sift3d_cuda_candidates_flags(sift3d_cuda_ctx *ctx, int octave_index,
+                                 const sift3d_cuda_candidate_flag **flags) {
+    if (!ctx || !ctx->have_pyramid || !flags || !ctx->kps_host || !ctx->kflags_host || octave_index < 0 ||
+        (size_t) octave_index >= ctx->cand_base.size())
+        return -1;
+    *flags = ctx->kflags_host + ctx->cand_base[octave_index];
     return ctx->h_counts[octave_index];
 }
 

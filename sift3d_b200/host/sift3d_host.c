@@ -874,29 +874,33 @@ int sift3d_detect_keypoints(sift3d_detector *const d, const sift3d_image *const 
     num = 0;
     {
         const sift3d_cuda_keypoint *rec = NULL;
-        if (sift3d_cuda_candidates_view(d->ctx, 0, &rec) >= 0) {
+        const sift3d_cuda_candidate_flag *flg = NULL;
+        if (sift3d_cuda_candidates_view(d->ctx, 0, &rec) >= 0 &&
+            sift3d_cuda_candidates_flags(d->ctx, 0, &flg) >= 0) {
             /* The records are already in host memory (written there by the orientation
-             * kernel), one region per octave in scan order: read them in place. `sc`/`sj`
-             * walk the same sequence a second time, `num` records behind, for the strength
-             * of candidate number `num`. */
-            const sift3d_cuda_keypoint *srec = rec;
+             * kernel), one region per octave in scan order. The 8-byte flags say which
+             * candidates survived and carry every candidate's strength, so only the
+             * survivors' 88-byte records are read. `sflg`/`sj` walk the flags a second time,
+             * `num` entries behind, for the strength of candidate number `num`. */
+            const sift3d_cuda_candidate_flag *sflg = flg;
             int o = 0, so = 0, j, sj = 0, cnt, scnt, seen = 0;
-            cnt = scnt = sift3d_cuda_candidates_view(d->ctx, 0, &rec);
+            cnt = scnt = sift3d_cuda_candidates_flags(d->ctx, 0, &flg);
             while (seen < num_cand) {
                 while (cnt == 0) {
-                    cnt = sift3d_cuda_candidates_view(d->ctx, ++o, &rec);
-                    if (cnt < 0)
+                    cnt = sift3d_cuda_candidates_flags(d->ctx, ++o, &flg);
+                    if (cnt < 0 || sift3d_cuda_candidates_view(d->ctx, o, &rec) != cnt)
                         return SIFT3D_FAILURE;
                 }
                 for (j = 0; j < cnt; j++) {
-                    const sift3d_cuda_keypoint *c = rec + j;
+                    const sift3d_cuda_keypoint *c;
                     keypoint_rec *dst;
-                    if (!c->valid)
+                    if (!flg[j].valid)
                         continue;
                     while (sj >= scnt) {
-                        scnt = sift3d_cuda_candidates_view(d->ctx, ++so, &srec);
+                        scnt = sift3d_cuda_candidates_flags(d->ctx, ++so, &sflg);
                         sj = 0;
                     }
+                    c = rec + j;
                     dst = kp->buf + num;
                     dst->xd = c->x;
                     dst->yd = c->y;
@@ -905,7 +909,7 @@ int sift3d_detect_keypoints(sift3d_detector *const d, const sift3d_image *const 
                     dst->o = c->o;
                     dst->s = c->s;
                     memcpy(dst->R, c->R, sizeof(dst->R));
-                    dst->strength = srec[sj++].strength;
+                    dst->strength = sflg[sj++].strength;
                     num++;
                 }
                 seen += cnt;
