@@ -118,6 +118,19 @@ class RefRun:
         self.candidates = None
         self.times = None
 
+    def set_image(self, vol: np.ndarray, units=(1.0, 1.0, 1.0)):
+        """Replace the image; the detector (and whatever it caches between images,
+        sift.c:651-656) is kept, so detector reuse can be replayed."""
+        L = self.L
+        vol = np.ascontiguousarray(vol, dtype=np.float32)
+        nz, ny, nx = vol.shape
+        L.sift3d_free_image(self.im)
+        self.im = L.sift3d_make_image(nx, ny, nz, 1)
+        assert self.im
+        self.shape = (nx, ny, nz)
+        np.ctypeslib.as_array(L.sift3d_image_data(self.im), shape=(vol.size,))[:] = vol.ravel()
+        L.refstage_image_set_units(self.im, *[float(u) for u in units])
+
     def detect(self, max_cand=1 << 22):
         L = self.L
         cand = np.zeros(max_cand, dtype=CAND_DTYPE)

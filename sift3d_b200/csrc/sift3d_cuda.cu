@@ -63,7 +63,7 @@ struct sift3d_cuda_ctx {
     bool serial = false;                // $SIFT3D_CUDA_SERIAL: everything on one stream
     DevBuf orient_plan;                 // OrientPlan on the device
     DevBuf orient_tab, orient_ntab;     // orientation window tables (OrientEntry) and their sizes
-    double orient_key[8] = {};          // geometry the tables were built for
+    double orient_key[11] = {};         // geometry the tables were built for
     bool orient_tab_ok = false;
     const OrientEntry *orient_tab_ptr[SIFT3D_CUDA_MAX_OCTAVES][SIFT3D_CUDA_MAX_FILTERS] = {};
     OrientPlan *h_plan = nullptr;       // pinned staging copy
@@ -301,6 +301,7 @@ int sift3d_cuda_plan(sift3d_cuda_ctx *ctx, const sift3d_cuda_plan_desc *d) {
     S3D_CK(cudaStreamSynchronize(ctx->stream));
     ctx->planned = false;
     ctx->have_pyramid = false;
+    ctx->orient_tab_ok = false;  // the window tables depend on the plan's units and scales
     ctx->desc = *d;
     ctx->nlev = d->num_kp_levels + 3;
     const int nlev = ctx->nlev, noct = d->num_octaves;
@@ -509,8 +510,12 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         static const bool no_tab = getenv("SIFT3D_CUDA_NO_ORIENT_TABLES") != nullptr;
         if (!no_tab) {
             const Level &L0 = ctx->level(0, 0);
-            const double key[8] = {(double) noct, (double) kp, L0.ux, L0.uy, L0.uz, L0.scale,
-                                   ctx->level(noct - 1, kp - 1).scale, (double) ctx->base_octave};
+            // octave 0 takes the image's units, octaves >= 1 the plan's (see above): both are
+            // part of the key, or a detect with new units on unchanged dims followed by a
+            // re-plan would reuse tables built for the old octave >= 1 spacing
+            const double key[11] = {(double) noct, (double) kp, L0.ux, L0.uy, L0.uz, L0.scale,
+                                    ctx->level(noct - 1, kp - 1).scale, (double) ctx->base_octave,
+                                    D.units[0], D.units[1], D.units[2]};
             if (!ctx->orient_tab_ok || memcmp(key, ctx->orient_key, sizeof(key)) != 0) {
                 ctx->orient_tab_ok = false;
                 size_t off[SIFT3D_CUDA_MAX_OCTAVES][SIFT3D_CUDA_MAX_FILTERS];

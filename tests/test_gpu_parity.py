@@ -195,3 +195,32 @@ def test_detector_reuse_and_replan():
         keys = kp.records()
         assert len(parity.match_keypoints(want["keys"], keys)) >= 0.99 * len(want["keys"])
     d.close()
+
+
+def test_detector_reuse_mixed_units():
+    """Octaves >= 1 keep the units of the last re-plan (sift.c:651-656): dims X / units u1,
+    then dims X / u2 (no re-plan: octaves >= 1 stay at u1 * 2^o), then dims Y / u2 (re-plan).
+    Every step must match a reference detector driven through the same sequence, so cached
+    per-plan state (orientation window tables) may not survive a change of units."""
+    import sift3d_b200 as s3
+    refstage = _ref()
+    u1, u2 = (1.0, 1.0, 1.0), (0.8, 0.8, 1.6)
+    seq = [((48, 48, 48), u1, 27), ((48, 48, 48), u2, 28), ((40, 56, 32), u2, 20)]
+    d = s3.Detector()
+    r = None
+    for dims, units, blobs in seq:
+        vol = synth_volume(*dims, num_blobs=blobs, seed=4321 + blobs)
+        if r is None:
+            r = refstage.RefRun(vol, units)
+        else:
+            r.set_image(vol, units)
+        want_keys = r.detect()
+        kp = d.detect(s3.Image.from_array(vol, units))
+        assert parity.cand_tuple_list(d.candidates()) == parity.cand_tuple_list(r.candidates)
+        keys = kp.records()
+        pairs = parity.match_keypoints(want_keys, keys)
+        assert len(pairs) >= 0.99 * len(want_keys), (dims, units, len(pairs), len(want_keys))
+        iw = [i for i, _ in pairs]
+        ig = [j for _, j in pairs]
+        np.testing.assert_allclose(keys["R"][ig], want_keys["R"][iw], atol=2e-5)
+    d.close()
