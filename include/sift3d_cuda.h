@@ -87,6 +87,18 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_device_count(void);
 SIFT3D_CUDA_EXPORT sift3d_cuda_ctx *sift3d_cuda_ctx_create(int device);
 SIFT3D_CUDA_EXPORT void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx);
 
+/* Arithmetic of the Gaussian blurs (apply_Sep_FIR_filter imutil.c:1127-1206).
+ *   exact != 0  every tap is a separate fp32 multiply and add in the reference's order and
+ *               im_scale (imutil.c:699-713) is a true division: pyramid levels are
+ *               bit-identical (0 ULP) to the reference build (x86-64 without FMA);
+ *   exact == 0  (default) one fused multiply-add per tap in the fused unit-spacing kernel and
+ *               im_scale folded into the first blur as a multiply by 1 / max: ~1e-7
+ *               relative to the level's max-abs, inside the 1e-5 voxel tolerance of the
+ *               parity contract, at half the FP32 instructions per voxel.
+ * Default: $SIFT3D_CUDA_EXACT (unset or 0: fast). Takes effect at the next detect. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_set_exact(sift3d_cuda_ctx *ctx, int exact);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_get_exact(sift3d_cuda_ctx *ctx);
+
 /* Pinned host memory for image buffers (so the H2D copy in detect runs at PCIe
  * speed). Works without a context. */
 SIFT3D_CUDA_EXPORT void *sift3d_cuda_host_alloc(size_t bytes);

@@ -140,6 +140,8 @@ def libcuda():
     L.sift3d_cuda_mark.argtypes = [vp, C.c_int]
     L.sift3d_cuda_elapsed_ms.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float)]
     L.sift3d_cuda_set_profiling.argtypes = [vp, C.c_int]
+    L.sift3d_cuda_set_exact.argtypes = [vp, C.c_int]
+    L.sift3d_cuda_get_exact.argtypes = [vp]
     L.sift3d_cuda_blur_ms.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_float),
                                       C.POINTER(C.c_int)]
     L._typed = True
@@ -452,6 +454,15 @@ class Detector:
         if self._C.sift3d_cuda_elapsed_ms(self.ctx, int(a), int(b), C.byref(ms)):
             raise Sift3DError("sift3d_cuda_elapsed_ms failed")
         return ms.value
+
+    def set_exact(self, exact=True):
+        """0-ULP blur arithmetic (True) or one FFMA per tap (False, the default unless
+        $SIFT3D_CUDA_EXACT is set); see include/sift3d_cuda.h."""
+        if self._C.sift3d_cuda_set_exact(self.ctx, int(bool(exact))):
+            raise Sift3DError("sift3d_cuda_set_exact failed")
+
+    def exact(self) -> bool:
+        return self._C.sift3d_cuda_get_exact(self.ctx) == 1
 
     def set_profiling(self, on=True):
         self._C.sift3d_cuda_set_profiling(self.ctx, int(bool(on)))

@@ -372,7 +372,7 @@ absdiffmax_kernel(const float *__restrict__ a, const float *__restrict__ b, size
 
 }  // namespace s3d
 
-#include "blur_fused.cuh"
+#include "blur_zmarch.cuh"
 #include "blur_fused_half.cuh"
 
 namespace s3d {
@@ -516,14 +516,13 @@ extern "C" SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_chunk_table(int ncta, int til
 }
 namespace s3d {
 
-template <int HW, int TY>
+template <int HW, int TY, bool EXACT>
 static int launch_fused_t(cudaStream_t st, const FusedParams &P, int occ) {
     using C = FusedCfg<HW>;
-    constexpr int TROWS = TY + 2 * HW;
-    constexpr int TILE_FLOATS = TROWS * C::BW;
-    constexpr int TILE_STRIDE = (TILE_FLOATS + 31) / 32 * 32;
-    constexpr size_t SMEM = (size_t) (kNB * TILE_STRIDE + 2 * TROWS * kFTX) * 4 + kNB * 8 +
-                            2 * (HW + 1) * 4 + 16;
+    using L = ZmarchLayout<HW, TY>;
+    constexpr int TROWS = L::TROWS;
+    constexpr size_t SMEM = L::SMEM;
+    if ((size_t) P.nx * P.ny * P.nz >= ((size_t) 1 << 31)) return 1;  // 32-bit voxel offsets in the kernel
     EncodeTiledFn enc = encode_tiled_fn();
     if (enc == nullptr) return 1;
     CUtensorMap tmap;
@@ -537,7 +536,7 @@ static int launch_fused_t(cudaStream_t st, const FusedParams &P, int occ) {
         return 1;
     static PerDeviceOnce attr_once;
     if (attr_once.first()) {
-        S3D_CK(cudaFuncSetAttribute(blur_fused_unit_kernel<HW, TY>,
+        S3D_CK(cudaFuncSetAttribute(blur_zmarch_kernel<HW, TY, EXACT>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int) SMEM));
     }
     const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
@@ -549,24 +548,24 @@ static int launch_fused_t(cudaStream_t st, const FusedParams &P, int occ) {
     if (ncta > kMaxFusedCtas) ncta = kMaxFusedCtas;
     if ((long) tiles * nzr > 0x7fffffffL) return 1;
     const ChunkTable &tab = fused_chunk_table((int) ncta, tiles, nzr, HW, P.z1 == P.nz);
-    blur_fused_unit_kernel<HW, TY><<<(unsigned) ncta, 8 * TY, SMEM, st>>>(tmap, P, tab);
+    blur_zmarch_kernel<HW, TY, EXACT><<<(unsigned) ncta, 8 * TY, SMEM, st>>>(tmap, P, tab);
     S3D_CK(cudaGetLastError());
     return 0;
 }
 
 // Returns 0 if launched, 1 if this blur is not eligible for the fused kernel, -1 on error.
-template <int TY>
+template <int TY, bool EXACT>
 static int launch_fused(cudaStream_t st, FusedParams &P, int hw, int occ) {
     P.zchunk = P.z1 - P.z0;
     switch (hw) {
-    case 1: return launch_fused_t<1, TY>(st, P, occ);
-    case 2: return launch_fused_t<2, TY>(st, P, occ);
-    case 3: return launch_fused_t<3, TY>(st, P, occ);
-    case 4: return launch_fused_t<4, TY>(st, P, occ);
-    case 5: return launch_fused_t<5, TY>(st, P, occ);
-    case 6: return launch_fused_t<6, TY>(st, P, occ);
-    case 7: return launch_fused_t<7, TY>(st, P, occ);
-    case 8: return launch_fused_t<8, TY>(st, P, occ);
+    case 1: return launch_fused_t<1, TY, EXACT>(st, P, occ);
+    case 2: return launch_fused_t<2, TY, EXACT>(st, P, occ);
+    case 3: return launch_fused_t<3, TY, EXACT>(st, P, occ);
+    case 4: return launch_fused_t<4, TY, EXACT>(st, P, occ);
+    case 5: return launch_fused_t<5, TY, EXACT>(st, P, occ);
+    case 6: return launch_fused_t<6, TY, EXACT>(st, P, occ);
+    case 7: return launch_fused_t<7, TY, EXACT>(st, P, occ);
+    case 8: return launch_fused_t<8, TY, EXACT>(st, P, occ);
     default: return 1;
     }
 }
@@ -636,7 +635,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
                 int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
                 const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
                 const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches,
-                int z0, int z1, int zorg) {
+                int z0, int z1, int zorg, bool exact) {
     const int hw = f.width / 2;
     if (z1 < 0) {  // whole volume
         z0 = 0;
@@ -674,8 +673,8 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         P.dst = dst;
         P.ds_dst = ds_dst;
         P.dogmax = d_dogmax_slot;
-        P.divisor = nullptr;
-        if (d_divisor != nullptr) {
+        P.out_scale = nullptr;
+        if (d_divisor != nullptr && exact) {
             // im_scale (imutil.c:699-713) as its own streaming pass: inside the blur every
             // voxel would be divided once per register window that holds it (3x for this
             // filter) and the reciprocal's latency stalls the tile pipeline (145 us against
@@ -683,7 +682,10 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
             scale_kernel<<<kNumSMs * 8, 256, 0, st>>>(src, tmp_a, total, d_divisor);
             if (launches) *launches += 1;
             P.src = tmp_a;
-            P.divisor = nullptr;
+        } else if (d_divisor != nullptr) {
+            // fast mode: the blur is linear, so v / max is applied to the OUTPUT as one multiply
+            // by 1 / max (one more rounding, ~6e-8 relative) and the streaming pass disappears
+            P.out_scale = d_divisor;
         }
         P.nx = nx; P.ny = ny; P.nz = nz;
         P.z0 = z0; P.z1 = z1; P.zorg = zorg;
@@ -691,7 +693,10 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];
         for (int i = f.width; i < kMaxParamTaps; i++) P.taps.k[i] = 0.0f;
         if (d_dogmax_slot != nullptr) S3D_CK(cudaMemsetAsync(d_dogmax_slot, 0, sizeof(float), st));
-        const int r = ty == 64 ? launch_fused<64>(st, P, hw, 1) : launch_fused<32>(st, P, hw, hw <= 4 ? 3 : 2);
+        const int occ = zmarch_occupancy(hw, ty);
+        int r;
+        if (exact) r = ty == 64 ? launch_fused<64, true>(st, P, hw, occ) : launch_fused<32, true>(st, P, hw, occ);
+        else r = ty == 64 ? launch_fused<64, false>(st, P, hw, occ) : launch_fused<32, false>(st, P, hw, occ);
         if (r < 0) return -1;
         if (r == 0) {
             if (launches) *launches += 1;
@@ -710,7 +715,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         P.dst = dst;
         P.ds_dst = ds_dst;
         P.dogmax = d_dogmax_slot;
-        P.divisor = nullptr;
+        P.out_scale = nullptr;
         P.nx = nx; P.ny = ny; P.nz = nz;
         P.z0 = z0; P.z1 = z1; P.zorg = zorg;
         P.zchunk = nz;

@@ -21,7 +21,7 @@
 //   z: by the plane stream: each loaded plane p yields the pair (U[2p+1], U[2p]).
 #pragma once
 
-#include "blur_fused.cuh"
+#include "blur_zmarch.cuh"
 
 namespace s3d {
 

@@ -61,6 +61,7 @@ struct sift3d_cuda_ctx {
     cudaEvent_t ev_seed[SIFT3D_CUDA_MAX_OCTAVES] = {};
     cudaEvent_t ev_done[SIFT3D_CUDA_MAX_OCTAVES] = {};
     bool serial = false;                // $SIFT3D_CUDA_SERIAL: everything on one stream
+    bool exact = false;                 // 0-ULP blur arithmetic (sift3d_cuda_set_exact, $SIFT3D_CUDA_EXACT)
     DevBuf orient_plan;                 // OrientPlan on the device
     DevBuf orient_tab, orient_ntab;     // orientation window tables (OrientEntry) and their sizes
     double orient_key[11] = {};         // geometry the tables were built for
@@ -151,6 +152,10 @@ sift3d_cuda_ctx *sift3d_cuda_ctx_create(int device) {
     }
     for (int i = 0; i < EV_COUNT; i++) cudaEventCreate(&ctx->ev[i]);
     ctx->serial = getenv("SIFT3D_CUDA_SERIAL") != nullptr;
+    {
+        const char *e = getenv("SIFT3D_CUDA_EXACT");
+        ctx->exact = e != nullptr && atoi(e) != 0;
+    }
     for (int o = 0; o < SIFT3D_CUDA_MAX_OCTAVES; o++) {
         cudaEventCreateWithFlags(&ctx->ev_seed[o], cudaEventDisableTiming);
         cudaEventCreateWithFlags(&ctx->ev_done[o], cudaEventDisableTiming);
@@ -622,7 +627,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             const double u[3] = {L.ux, L.uy, L.uz};
             rc = launch_blur(so, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
                              ctx->d_scalar(0), nullptr, nullptr, ds_dst, false, &ctx->launches,
-                             zr0(o), zr1(o), zorg(o));
+                             zr0(o), zr1(o), zorg(o), ctx->exact);
         } else {
             Level &P = ctx->level(o, s - 1);
             const double u[3] = {P.ux, P.uy, P.uz};
@@ -631,7 +636,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             if (s - 1 >= 0 && s - 1 < kp) slot = ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (s - 1));
             rc = launch_blur(so, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
                              nullptr, slot, P.d, ds_dst, false, &ctx->launches, zr0(o), zr1(o),
-                             zorg(o));
+                             zorg(o), ctx->exact);
         }
         if (rc) return -1;
         if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], so));
@@ -799,6 +804,14 @@ int sift3d_cuda_detect_from_seed(sift3d_cuda_ctx *ctx, const float *seed, int se
     return detect_impl(ctx, seed, seed_on_device, units, peak_thresh, corner_thresh,
                        num_candidates, true, nullptr, nullptr);
 }
+
+int sift3d_cuda_set_exact(sift3d_cuda_ctx *ctx, int exact) {
+    if (!ctx) return -1;
+    ctx->exact = exact != 0;
+    return 0;
+}
+
+int sift3d_cuda_get_exact(sift3d_cuda_ctx *ctx) { return ctx ? (ctx->exact ? 1 : 0) : -1; }
 
 int sift3d_cuda_set_base_octave(sift3d_cuda_ctx *ctx, int base_octave) {
     if (!ctx || base_octave < 0) return -1;
@@ -1063,7 +1076,7 @@ int sift3d_cuda_blur(sift3d_cuda_ctx *ctx, const float *host_src, float *host_ds
         goto done;
     if (launch_blur(ctx->stream, (const float *) a.p, (float *) b.p, (float *) c.p, (float *) d.p,
                     nx, ny, nz, units, *f, (const float *) t.p, nullptr, nullptr, nullptr, nullptr,
-                    force_generic != 0, &ctx->launches))
+                    force_generic != 0, &ctx->launches, 0, -1, 0, ctx->exact))
         goto done;
     if (cudaMemcpyAsync(host_dst, b.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
         cudaStreamSynchronize(ctx->stream) != cudaSuccess) {

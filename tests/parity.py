@@ -54,11 +54,14 @@ def cosine_rows(a: np.ndarray, b: np.ndarray) -> np.ndarray:
     return num / np.maximum(den, 1e-300)
 
 
-def run_product(vol, units=(1.0, 1.0, 1.0), params=None, limit=None):
-    """Full detect(+sort)+extract through the drop-in C API. Returns a dict."""
+def run_product(vol, units=(1.0, 1.0, 1.0), params=None, limit=None, exact=None):
+    """Full detect(+sort)+extract through the drop-in C API. Returns a dict.
+    exact: True = 0-ULP blur arithmetic, False = fast (FFMA), None = the library default."""
     import sift3d_b200 as s3
 
     det = s3.Detector()
+    if exact is not None:
+        det.set_exact(exact)
     for k, v in (params or {}).items():
         assert getattr(det, f"set_{k}")(v) == 0
     im = s3.Image.from_array(vol, units)
@@ -109,3 +112,37 @@ def compare_pyramids(det, ref_run, report=None):
                 report.append((o, s, rel, nb))
             worst = (max(worst[0], rel), max(worst[1], nb))
     return worst
+
+
+def compare_runs(got, want, exact, r_atol=2e-5):
+    """The parity gates of BASELINE.json's north_star between a product run and a reference
+    run (dicts of run_product / run_reference). Exact mode additionally demands bit-identical
+    pyramids and identical candidate lists; fast mode (FFMA blur) the stated tolerances:
+    voxels within 1e-5 of the level's max-abs, >= 99 % of the candidates and keypoints
+    matched (unmatched ones are marginal extrema flipped by float reordering), descriptor
+    cosine >= 0.999. Returns a dict of the measured figures."""
+    report = []
+    rel, nbits = compare_pyramids(got["det"], want["run"], report)
+    assert rel <= VOXEL_REL_TOL, report
+    gc, wc = cand_tuple_list(got["candidates"]), cand_tuple_list(want["candidates"])
+    if exact:
+        assert nbits == 0, [r for r in report if r[3]]
+        assert gc == wc
+        np.testing.assert_array_equal(got["candidates"]["strength"], want["candidates"]["strength"])
+    else:
+        common = len(set(gc) & set(wc))
+        assert common >= KP_MATCH_FRACTION * len(wc), (common, len(wc))
+        assert common >= KP_MATCH_FRACTION * len(gc), (common, len(gc))
+    pairs = match_keypoints(want["keys"], got["keys"])
+    assert len(want["keys"]) > 0
+    assert len(pairs) >= KP_MATCH_FRACTION * len(want["keys"]), (len(pairs), len(want["keys"]))
+    assert len(got["keys"]) <= len(want["keys"]) / KP_MATCH_FRACTION + 1
+    iw = [i for i, _ in pairs]
+    ig = [j for _, j in pairs]
+    np.testing.assert_allclose(got["keys"]["R"][ig], want["keys"]["R"][iw], atol=r_atol)
+    cos = cosine_rows(got["desc"][ig, 3:], want["desc"][iw, 3:])
+    assert cos.min() >= DESC_COS_MIN, cos.min()
+    np.testing.assert_array_equal(got["desc"][ig, :3], want["desc"][iw, :3])
+    return {"voxel_rel": rel, "voxels_differing": nbits, "candidates": (len(gc), len(wc)),
+            "keypoints": (len(got["keys"]), len(want["keys"]), len(pairs)),
+            "min_cosine": float(cos.min())}

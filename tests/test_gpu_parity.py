@@ -50,24 +50,44 @@ def test_blur_bit_exact(det, units, sigma):
     assert nbits == 0, f"{nbits} voxels differ (max rel err {rel:.3g})"
 
 
+# Tolerance of the fast (one FFMA per tap) arithmetic mode on ONE blur of unit-variance noise:
+# one rounding instead of two per tap, measured ~1e-7 of the level's max-abs; the contract
+# (BASELINE.json north_star) is 1e-5.
+FAST_BLUR_REL_TOL = 2e-6
+
+
+@pytest.mark.parametrize("exact", [True, False], ids=["exact", "fast"])
 @pytest.mark.parametrize("dims", [(64, 64, 40), (96, 70, 45), (36, 33, 50), (128, 64, 37),
-                                  (32, 32, 36), (260, 100, 41)])
+                                  (32, 32, 36), (260, 100, 41), (64, 160, 150)])
 @pytest.mark.parametrize("sigma", [0.3, 0.5387, 0.9733, 1.2263, 1.5450, 1.9466, 2.2, 2.4525])
-def test_fused_blur_bit_exact(det, dims, sigma):
+def test_fused_blur_vs_reference(det, dims, sigma, exact):
     """The fused single-launch kernel (unit tap spacing, TMA-staged tiles, register z
-    window) == apply_Sep_FIR_filter bit for bit: half-widths 1..8, full / shifted /
-    overlapping tiles, z-chunked and single-chunk volumes, all six boundary faces."""
+    window) against apply_Sep_FIR_filter: half-widths 1..8, full / shifted / overlapping
+    tiles, z-chunked and single-chunk volumes, all six boundary faces. Exact mode: bit for
+    bit; fast mode (FFMA): within FAST_BLUR_REL_TOL of the level's max-abs."""
     ref = _ref()
     nx, ny, nz = dims
     rng = np.random.default_rng(int(sigma * 1000) + nx)
     vol = rng.standard_normal((nz, ny, nx)).astype(np.float32)
     taps = _gauss_taps(sigma)
     want = ref.ref_blur(vol, (1, 1, 1), taps)
-    got = det.blur(vol, (1, 1, 1), taps)
-    rel, nbits = parity.level_error(got, want)
-    assert nbits == 0, f"{nbits} voxels differ (max rel err {rel:.3g})"
-    gen = det.blur(vol, (1, 1, 1), taps, force_generic=True)
-    assert parity.level_error(gen, want)[1] == 0
+    det.set_exact(exact)
+    try:
+        l0 = det.launch_count()
+        got = det.blur(vol, (1, 1, 1), taps)
+        # the fused TMA kernel really ran: one launch, not the three generic passes
+        assert det.launch_count() - l0 == 1
+        rel, nbits = parity.level_error(got, want)
+        if exact:
+            assert nbits == 0, f"{nbits} voxels differ (max rel err {rel:.3g})"
+        else:
+            assert rel <= FAST_BLUR_REL_TOL, f"max rel err {rel:.3g}"
+        l0 = det.launch_count()
+        gen = det.blur(vol, (1, 1, 1), taps, force_generic=True)
+        assert det.launch_count() - l0 == 3
+        assert parity.level_error(gen, want)[1] == 0
+    finally:
+        det.set_exact(False)
 
 
 @pytest.mark.parametrize("dims", [(64, 64, 40), (96, 70, 45), (36, 33, 50), (128, 64, 37),
@@ -83,7 +103,9 @@ def test_fused_half_blur_bit_exact(det, dims, sigma):
     vol = rng.standard_normal((nz, ny, nx)).astype(np.float32)
     taps = _gauss_taps(sigma)
     want = ref.ref_blur(vol, (2, 2, 2), taps)
+    l0 = det.launch_count()
     got = det.blur(vol, (2, 2, 2), taps)
+    assert det.launch_count() - l0 == 1  # the fused spacing-1/2 kernel, not the generic passes
     rel, nbits = parity.level_error(got, want)
     assert nbits == 0, f"{nbits} voxels differ (max rel err {rel:.3g})"
     gen = det.blur(vol, (2, 2, 2), taps, force_generic=True)
@@ -99,37 +121,37 @@ CASES = [
 ]
 
 
+@pytest.mark.parametrize("exact", [True, False], ids=["exact", "fast"])
 @pytest.mark.parametrize("name,dims,units,blobs,flags", CASES)
-def test_full_pipeline_vs_reference(name, dims, units, blobs, flags):
+def test_full_pipeline_vs_reference(name, dims, units, blobs, flags, exact):
     _ref()
     vol = synth_volume(*dims, num_blobs=blobs, flags=flags)
     want = parity.run_reference(vol, units)
-    got = parity.run_product(vol, units)
+    got = parity.run_product(vol, units, exact=exact)
+    parity.compare_runs(got, want, exact)
+    iw, ig = zip(*parity.match_keypoints(want["keys"], got["keys"]))
+    np.testing.assert_allclose(got["kp_matrix"][list(ig)], want["kp_matrix"][list(iw)],
+                               atol=parity.KP_POS_TOL)
 
-    # pyramid: every Gaussian level of every octave
-    report = []
-    rel, nbits = parity.compare_pyramids(got["det"], want["run"], report)
-    assert rel <= parity.VOXEL_REL_TOL, report
-    assert nbits == 0, [r for r in report if r[3]]
 
-    # candidates: identical list, identical order, identical strength
-    assert parity.cand_tuple_list(got["candidates"]) == parity.cand_tuple_list(want["candidates"])
-    np.testing.assert_array_equal(got["candidates"]["strength"], want["candidates"]["strength"])
+# Non-default detector parameters (setters sift.h:40-78) against the reference.
+PARAM_CASES = [
+    ("thresholds", dict(peak_thresh=0.05, corner_thresh=0.3)),
+    ("levels_sigma", dict(num_kp_levels=2, sigma0=2.0, sigma_n=0.9)),
+    ("four_levels", dict(num_kp_levels=4, peak_thresh=0.08)),
+]
 
-    # keypoints after orientation
-    pairs = parity.match_keypoints(want["keys"], got["keys"])
-    assert len(want["keys"]) > 0
-    assert len(pairs) >= parity.KP_MATCH_FRACTION * len(want["keys"])
-    assert len(got["keys"]) <= len(want["keys"]) / parity.KP_MATCH_FRACTION + 1
-    iw = [i for i, _ in pairs]
-    ig = [j for _, j in pairs]
-    np.testing.assert_allclose(got["keys"]["R"][ig], want["keys"]["R"][iw], atol=2e-5)
-    np.testing.assert_allclose(got["kp_matrix"][ig], want["kp_matrix"][iw], atol=parity.KP_POS_TOL)
 
-    # descriptors
-    cos = parity.cosine_rows(got["desc"][ig, 3:], want["desc"][iw, 3:])
-    assert cos.min() >= parity.DESC_COS_MIN, cos.min()
-    np.testing.assert_array_equal(got["desc"][ig, :3], want["desc"][iw, :3])
+@pytest.mark.parametrize("exact", [True, False], ids=["exact", "fast"])
+@pytest.mark.parametrize("name,params", PARAM_CASES)
+def test_non_default_parameters_vs_reference(name, params, exact):
+    """peak_thresh / corner_thresh / num_kp_levels / sigma0 / sigma_n set through the public
+    setters on both sides: same pyramid geometry, candidates, keypoints, descriptors."""
+    _ref()
+    vol = synth_volume(72, 64, 56, num_blobs=60, flags=3, seed=99)
+    want = parity.run_reference(vol, (1.0, 1.0, 1.0), params)
+    got = parity.run_product(vol, (1.0, 1.0, 1.0), params, exact=exact)
+    parity.compare_runs(got, want, exact)
 
 
 def test_cli_sequence_128_top100():
@@ -139,7 +161,9 @@ def test_cli_sequence_128_top100():
     _ref()
     vol = synth_volume(128, 128, 128)
     want = parity.run_reference(vol, limit=100)
-    got = parity.run_product(vol, limit=100)
+    # exact arithmetic: the 'strongest 100' are picked by strengths that belong to OTHER
+    # candidates (D8), so one flipped marginal extremum would shift every later slot
+    got = parity.run_product(vol, limit=100, exact=True)
     assert parity.cand_tuple_list(got["candidates"]) == parity.cand_tuple_list(want["candidates"])
     assert len(got["keys"]) == len(want["keys"]) == 100
     pairs = parity.match_keypoints(want["keys"], got["keys"])
