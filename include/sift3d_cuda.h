@@ -206,6 +206,29 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_blur(sift3d_cuda_ctx *ctx, const float *host_
                                         float *host_dst, int nx, int ny, int nz,
                                         const double units[3], const sift3d_cuda_filter *f,
                                         int force_generic);
+/* One blur that allocates NOTHING. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it). Same kernels and same dispatch as
+ * sift3d_cuda_blur (fused single-launch kernel where eligible, else the generic x / y / z
+ * passes), but the two scratch volumes of the generic passes and the device copy of the taps
+ * live in a file-scope `static __device__` array of the library: 2 x
+ * SIFT3D_CUDA_STATIC_BLUR_MAX_VOXELS floats + 1 KiB = 8 MiB, held by every GPU that loads the
+ * library until the process exits. Volumes with more voxels are rejected (-1, message on
+ * stderr). The call issues no cudaMalloc / cudaFree / allocating library routine.
+ *   d_src, d_dst  nx*ny*nz float32, x fastest, DEVICE-ACCESSIBLE and distinct (device memory, or
+ *                 page-locked host memory of sift3d_cuda_host_alloc through its unified address)
+ *   exact         arithmetic mode as sift3d_cuda_set_exact
+ *   stream        a cudaStream_t passed as a plain pointer; NULL = the default stream
+ *   sync          != 0: wait for completion before returning; 0: return once enqueued
+ * Every call on a device shares the one scratch array, which keeps the last call's contents
+ * (nothing in it has to start at zero: each call rewrites what it reads): calls that overlap
+ * on the GPU -- different streams, threads or processes' worth of work on one device -- RACE.
+ * Serialise them on one stream or with events. */
+#define SIFT3D_CUDA_STATIC_BLUR_MAX_VOXELS (1 << 20)
+SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_static(int device, const float *d_src, float *d_dst,
+                                               int nx, int ny, int nz, const double units[3],
+                                               const sift3d_cuda_filter *f, int exact,
+                                               void *stream, int sync);
 /* Host-only: the work table of the fused unit-spacing blur (no device needed). `tiles` column
  * tiles of `nzr` output planes each are cut into `ncta` contiguous ranges of the flattened
  * tile-major space; bounds[0..ncta] receives the range limits. Returns the cost (output planes

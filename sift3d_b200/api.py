@@ -133,6 +133,11 @@ def libcuda():
     L.sift3d_cuda_blur.argtypes = [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double),
                                    C.POINTER(CudaFilter), C.c_int]
     L.sift3d_cuda_get_timings.argtypes = [vp, C.POINTER(CudaTimings)]
+    L.sift3d_cuda_blur_static.argtypes = [C.c_int, vp, vp, C.c_int, C.c_int, C.c_int,
+                                          C.POINTER(C.c_double), C.POINTER(CudaFilter), C.c_int, vp, C.c_int]
+    L.sift3d_cuda_device_upload.restype = vp
+    L.sift3d_cuda_device_upload.argtypes = [C.c_int, vp, C.c_size_t]
+    L.sift3d_cuda_device_free.argtypes = [C.c_int, vp]
     L.sift3d_cuda_launch_count.restype = C.c_uint64
     L.sift3d_cuda_launch_count.argtypes = [vp]
     L.sift3d_cuda_synchronize.argtypes = [vp]

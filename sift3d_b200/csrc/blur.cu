@@ -957,3 +957,85 @@ int launch_absdiffmax(cudaStream_t st, const float *a, const float *b, size_t n,
 }
 
 }  // namespace s3d
+
+// ---------------------------------------------------------------------------------------
+// One blur without any allocation (sift3d_cuda_blur_static, include/sift3d_cuda.h). It has
+// no counterpart in the reference; it was added for
+// callers that may not call cudaMalloc (code under CUDA graph capture, tight serving loops,
+// harnesses that forbid it). The scratch volumes of the generic 3-pass blur and the device
+// copy of the taps live in a file-scope __device__ array that every GPU loading this library
+// holds until exit. In host code the array's NAME is only a host-side stand-in: its device
+// address is taken once per device with cudaGetSymbolAddress (that device current) and it is
+// this address that goes to the kernels.
+// ---------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace s3d {
+
+constexpr size_t kStaticBlurMaxVox = (size_t) SIFT3D_CUDA_STATIC_BLUR_MAX_VOXELS;
+constexpr size_t kStaticTapsFloats = 256;  // >= SIFT3D_CUDA_MAX_TAPS, keeps the volumes 256-byte aligned
+static_assert(kStaticTapsFloats >= SIFT3D_CUDA_MAX_TAPS && kStaticTapsFloats % 64 == 0, "taps slot");
+// [taps | scratch volume A | scratch volume B]
+static __device__ __align__(256) float g_static_blur_scratch[kStaticTapsFloats + 2 * kStaticBlurMaxVox];
+
+__global__ void static_blur_taps_kernel(const sift3d_cuda_filter f, float *__restrict__ dst) {
+    const int i = threadIdx.x;
+    if (i < f.width) dst[i] = f.taps[i];
+}
+
+// Device address of the scratch array on `device` (which must be current), or nullptr.
+static float *static_blur_scratch(int device) {
+    static std::mutex mu;
+    static float *ptr[kMaxDevices] = {};
+    if (device < 0 || device >= kMaxDevices) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    if (ptr[device] == nullptr) {
+        float *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void **) &p, g_static_blur_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            S3D_ERR("sift3d_cuda_blur_static: cudaGetSymbolAddress failed on device %d: %s\n", device,
+                    cudaGetErrorString(e));
+            cudaGetLastError();
+            return nullptr;
+        }
+        ptr[device] = p;
+    }
+    return ptr[device];
+}
+
+}  // namespace s3d
+
+extern "C" SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_static(int device, const float *d_src, float *d_dst,
+                                                         int nx, int ny, int nz, const double units[3],
+                                                         const sift3d_cuda_filter *f, int exact,
+                                                         void *stream, int sync) {
+    using namespace s3d;
+    if (!d_src || !d_dst || !units || !f || nx < 2 || ny < 2 || nz < 2 || f->width < 1 ||
+        f->width > SIFT3D_CUDA_MAX_TAPS || !(f->width & 1) || d_src == d_dst) {
+        S3D_ERR("sift3d_cuda_blur_static: invalid argument\n");
+        return -1;
+    }
+    const size_t n = (size_t) nx * ny * nz;
+    if (n > kStaticBlurMaxVox) {
+        S3D_ERR("sift3d_cuda_blur_static: %d x %d x %d = %zu voxels exceed the static scratch of %zu voxels "
+                "(SIFT3D_CUDA_STATIC_BLUR_MAX_VOXELS); use sift3d_cuda_blur or a detector\n",
+                nx, ny, nz, n, kStaticBlurMaxVox);
+        return -1;
+    }
+    S3D_CK(cudaSetDevice(device));
+    float *base = static_blur_scratch(device);
+    if (base == nullptr) return -1;
+    float *d_taps = base;
+    float *tmp_a = base + kStaticTapsFloats;
+    float *tmp_b = tmp_a + kStaticBlurMaxVox;
+    cudaStream_t st = (cudaStream_t) stream;
+    // Nothing in the scratch has to start at zero: the taps slot and every scratch voxel the
+    // later passes read are rewritten by this call before they are read.
+    static_blur_taps_kernel<<<1, SIFT3D_CUDA_MAX_TAPS, 0, st>>>(*f, d_taps);
+    S3D_CK(cudaGetLastError());
+    if (launch_blur(st, d_src, d_dst, tmp_a, tmp_b, nx, ny, nz, units, *f, d_taps, nullptr, nullptr,
+                    nullptr, nullptr, false, nullptr, 0, -1, 0, exact != 0))
+        return -1;
+    if (sync) S3D_CK(cudaStreamSynchronize(st));
+    return 0;
+}
