@@ -14,6 +14,7 @@
 // to fp32 separately and accumulates taps in ascending d. All arithmetic below uses
 // __fmul_rn/__fadd_rn/__fsub_rn/__fdiv_rn so nvcc can never contract it into FMAs.
 #include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 
@@ -516,13 +517,16 @@ extern "C" SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_chunk_table(int ncta, int til
 }
 namespace s3d {
 
-template <int HW, int TY, bool EXACT>
-static int launch_fused_t(cudaStream_t st, const FusedParams &P, int occ) {
+template <int HW, int R, int NT, bool EXACT>
+static int launch_fused_t(cudaStream_t st, const FusedParams &P) {
     using C = FusedCfg<HW>;
-    using L = ZmarchLayout<HW, TY>;
+    using Z = ZCfg<HW, R, NT>;
+    using L = typename Z::L;
+    constexpr int TY = Z::TY;
     constexpr int TROWS = L::TROWS;
     constexpr size_t SMEM = L::SMEM;
     if ((size_t) P.nx * P.ny * P.nz >= ((size_t) 1 << 31)) return 1;  // 32-bit voxel offsets in the kernel
+    if (P.ny < TY) return 1;
     EncodeTiledFn enc = encode_tiled_fn();
     if (enc == nullptr) return 1;
     CUtensorMap tmap;
@@ -536,36 +540,63 @@ static int launch_fused_t(cudaStream_t st, const FusedParams &P, int occ) {
         return 1;
     static PerDeviceOnce attr_once;
     if (attr_once.first()) {
-        S3D_CK(cudaFuncSetAttribute(blur_zmarch_kernel<HW, TY, EXACT>,
+        S3D_CK(cudaFuncSetAttribute(blur_zmarch_kernel<HW, R, NT, EXACT>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int) SMEM));
     }
     const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
     const int nzr = P.z1 - P.z0;
     // one wave of CTAs, but no CTA with less than ~8 outputs of one tile
-    long ncta = (long) (kNumSMs - g_fused_sm_reserve) * occ;
+    long ncta = (long) (kNumSMs - g_fused_sm_reserve) * Z::OCC;
     const long most = (long) tiles * (nzr / (HW + 1 > 8 ? HW + 1 : 8) > 0 ? nzr / (HW + 1 > 8 ? HW + 1 : 8) : 1);
     if (ncta > most) ncta = most;
     if (ncta > kMaxFusedCtas) ncta = kMaxFusedCtas;
     if ((long) tiles * nzr > 0x7fffffffL) return 1;
     const ChunkTable &tab = fused_chunk_table((int) ncta, tiles, nzr, HW, P.z1 == P.nz);
-    blur_zmarch_kernel<HW, TY, EXACT><<<(unsigned) ncta, 8 * TY, SMEM, st>>>(tmap, P, tab);
+    blur_zmarch_kernel<HW, R, NT, EXACT><<<(unsigned) ncta, NT, SMEM, st>>>(tmap, P, tab);
     S3D_CK(cudaGetLastError());
     return 0;
 }
 
+// Thread / tile shape of the z-marching kernel per half-width:
+//   variant 0   one row of four voxels per thread, 256 threads (32 x 32 tiles)
+//   variant 1   two rows, 256 threads (32 x 64 tiles)
+//   variant 2   four rows, 128 threads (32 x 64 tiles; half-widths <= 3)
+//   variant 3   two rows, 128 threads (32 x 32 tiles)
+// More rows per thread amortise the per-plane fixed work; the running z sums (8 * R * HW
+// registers) bound R for the wide filters. $SIFT3D_CUDA_ZV = one digit per half-width 1..8.
+static int zmarch_variant(int hw, int ny) {
+    static const char *env = getenv("SIFT3D_CUDA_ZV");
+    int v = hw <= 4 ? 1 : (hw <= 6 ? 3 : 1);
+    if (env != nullptr && (int) strlen(env) >= hw && env[hw - 1] >= '0' && env[hw - 1] <= '3') v = env[hw - 1] - '0';
+    if (v == 2 && hw > 3) v = 1;
+    if ((v == 1 || v == 2) && ny < 64) v = 0;
+    return v;
+}
+
+template <int HW, bool EXACT>
+static int launch_fused_v(cudaStream_t st, const FusedParams &P, int variant) {
+    if (variant == 0) return launch_fused_t<HW, 1, 256, EXACT>(st, P);
+    if (variant == 3) return launch_fused_t<HW, 2, 128, EXACT>(st, P);
+    if constexpr (HW <= 3) {
+        if (variant == 2) return launch_fused_t<HW, 4, 128, EXACT>(st, P);
+    }
+    return launch_fused_t<HW, 2, 256, EXACT>(st, P);
+}
+
 // Returns 0 if launched, 1 if this blur is not eligible for the fused kernel, -1 on error.
-template <int TY, bool EXACT>
-static int launch_fused(cudaStream_t st, FusedParams &P, int hw, int occ) {
+template <bool EXACT>
+static int launch_fused(cudaStream_t st, FusedParams &P, int hw) {
     P.zchunk = P.z1 - P.z0;
+    const int v = zmarch_variant(hw, P.ny);
     switch (hw) {
-    case 1: return launch_fused_t<1, TY, EXACT>(st, P, occ);
-    case 2: return launch_fused_t<2, TY, EXACT>(st, P, occ);
-    case 3: return launch_fused_t<3, TY, EXACT>(st, P, occ);
-    case 4: return launch_fused_t<4, TY, EXACT>(st, P, occ);
-    case 5: return launch_fused_t<5, TY, EXACT>(st, P, occ);
-    case 6: return launch_fused_t<6, TY, EXACT>(st, P, occ);
-    case 7: return launch_fused_t<7, TY, EXACT>(st, P, occ);
-    case 8: return launch_fused_t<8, TY, EXACT>(st, P, occ);
+    case 1: return launch_fused_v<1, EXACT>(st, P, v);
+    case 2: return launch_fused_v<2, EXACT>(st, P, v);
+    case 3: return launch_fused_v<3, EXACT>(st, P, v);
+    case 4: return launch_fused_v<4, EXACT>(st, P, v);
+    case 5: return launch_fused_v<5, EXACT>(st, P, v);
+    case 6: return launch_fused_v<6, EXACT>(st, P, v);
+    case 7: return launch_fused_v<7, EXACT>(st, P, v);
+    case 8: return launch_fused_v<8, EXACT>(st, P, v);
     default: return 1;
     }
 }
@@ -659,13 +690,12 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
     // Tile height: 32-row tiles at 3 CTAs x 256 threads per SM (<= 85 registers, hw <= 4) are
     // ~5 % faster than one 64-row CTA of 512 threads; the wider filters need the registers.
     static const int ty_env = getenv("SIFT3D_CUDA_TY") ? atoi(getenv("SIFT3D_CUDA_TY")) : 0;
-    const int ty = (ty_env == 32 || ny < 64 || (ty_env != 64 && hw <= 4)) ? 32 : 64;
     const int ty_half = (ty_env == 32 || ny < 64) ? 32 : 64;
     bool symmetric = true;
     for (int i = 0; i < hw; i++) symmetric = symmetric && f.taps[i] == f.taps[f.width - 1 - i];
     if (!force_generic && symmetric && ax.uf == 1.0f && ay.uf == 1.0f && az.uf == 1.0f && hw >= 1 &&
-        hw <= 8 && f.width <= kMaxParamTaps && nx % 4 == 0 && nx >= kFTX && ny >= ty &&
-        ny >= 2 * hw + 2 && nz >= 2 * hw + 2 && ((uintptr_t) src & 15) == 0 &&
+        hw <= 8 && f.width <= kMaxParamTaps && nx % 4 == 0 && nx >= kFTX && ny >= 32 &&
+        ny >= 2 * hw + 2 && nz >= 2 * hw + 2 && (((uintptr_t) src | (uintptr_t) dst | (uintptr_t) ds_dst) & 15) == 0 &&
         (d_dogmax_slot == nullptr || dog_prev == src) &&
         (d_divisor == nullptr || (tmp_a != nullptr && tmp_a != src))) {
         FusedParams P;
@@ -693,10 +723,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         for (int i = 0; i < f.width; i++) P.taps.k[i] = f.taps[i];
         for (int i = f.width; i < kMaxParamTaps; i++) P.taps.k[i] = 0.0f;
         if (d_dogmax_slot != nullptr) S3D_CK(cudaMemsetAsync(d_dogmax_slot, 0, sizeof(float), st));
-        const int occ = zmarch_occupancy(hw, ty);
-        int r;
-        if (exact) r = ty == 64 ? launch_fused<64, true>(st, P, hw, occ) : launch_fused<32, true>(st, P, hw, occ);
-        else r = ty == 64 ? launch_fused<64, false>(st, P, hw, occ) : launch_fused<32, false>(st, P, hw, occ);
+        const int r = exact ? launch_fused<true>(st, P, hw) : launch_fused<false>(st, P, hw);
         if (r < 0) return -1;
         if (r == 0) {
             if (launches) *launches += 1;

@@ -187,11 +187,9 @@ __device__ __forceinline__ void xrow4_load(const uint32_t p, float (&in)[FusedCf
     }
 }
 template <int HW, bool EXACT>
-__device__ __forceinline__ float4 xrow4(const uint32_t p, const TapsParam &k) {
+__device__ __forceinline__ float4 xrow4_fir(const float (&in)[FusedCfg<HW>::NIN], const TapsParam &k) {
     using C = FusedCfg<HW>;
-    constexpr int NW = C::NW, HWP = C::HWP, NIN = C::NIN;
-    float in[NIN];
-    xrow4_load<HW, EXACT>(p, in);
+    constexpr int NW = C::NW, HWP = C::HWP;
     float o[4];
 #pragma unroll
     for (int c = 0; c < 4; c++) {
@@ -202,14 +200,11 @@ __device__ __forceinline__ float4 xrow4(const uint32_t p, const TapsParam &k) {
     }
     return make_float4(o[0], o[1], o[2], o[3]);
 }
-
-// y pass loads: rows j = 0 .. NINY-1 of one column of the x-filtered tile
-template <int HW, int J = 0>
-__device__ __forceinline__ void ycol_load(const uint32_t p, float (&in)[FusedCfg<HW>::NINY]) {
-    if constexpr (J < FusedCfg<HW>::NINY) {
-        in[J] = lds32<J * kFTX * 4>(p);
-        ycol_load<HW, J + 1>(p, in);
-    }
+template <int HW, bool EXACT>
+__device__ __forceinline__ float4 xrow4(const uint32_t p, const TapsParam &k) {
+    float in[FusedCfg<HW>::NIN];
+    xrow4_load<HW, EXACT>(p, in);
+    return xrow4_fir<HW, EXACT>(in, k);
 }
 
 // z pass, scatter form: feed one y-filtered value; returns the output that is now complete.
@@ -243,7 +238,6 @@ struct ChunkTable {
     int b[kMaxFusedCtas + 1];
 };
 
-constexpr int zmarch_occupancy(int HW, int TY) { return TY == 64 ? 1 : (HW <= 1 ? 3 : 2); }
 // mbarrier / TMA helpers on precomputed 32-bit shared addresses (the generic -> shared
 // conversion reads SR_CgaCtaId; done once per kernel, not once per plane)
 __device__ __forceinline__ uint32_t opaque_u32(uint32_t v) {
@@ -276,23 +270,114 @@ __device__ __forceinline__ void tma_load_3d_a(uint32_t dst, const CUtensorMap *t
         : "memory");
 }
 
-// Fused blur, unit tap spacing on all three axes. Block = 8*TY threads: thread
-// (lane, w) owns column x0 + lane, rows y0 + 4w .. 4w+3 in the y and z passes.
-template <int HW, int TY, bool EXACT>
-__global__ void __launch_bounds__(8 * TY, zmarch_occupancy(HW, TY))
+// Configuration of the z-marching kernel: R rows of 4 x-adjacent voxels per thread in the y / z
+// passes, NT threads (8 column groups x NT/8 row groups), hence 32 x TY tiles, TY = R * NT / 8.
+template <int HW, int R, int NT>
+struct ZCfg {
+    static constexpr int TY = R * NT / 8;
+    using L = ZmarchLayout<HW, TY>;
+    // CTAs per SM: by shared memory (227 KB usable) and by a register estimate (the running
+    // z sums, 4R * 2HW, plus ~64 for the x / y passes and addresses)
+    static constexpr int kRegs = 8 * R * HW + 64;
+    static constexpr int kOccS = (int) ((size_t) 227 * 1024 / (L::SMEM + 1024));
+    static constexpr int kOccR = 65536 / (NT * (kRegs > 255 ? 255 : kRegs));
+    static constexpr int kOcc0 = kOccS < kOccR ? kOccS : kOccR;
+    static constexpr int OCC = kOcc0 < 1 ? 1 : (kOcc0 > 4 ? 4 : kOcc0);
+};
+
+// y pass, streaming form: rows J = R-1+2HW .. 0 of the thread's 4 columns of the x-filtered
+// tile, descending, so that every output receives its taps in ascending order (tap t of output
+// c is row c + 2HW - t)
+template <int HW, int R, bool EXACT, int J>
+__device__ __forceinline__ void yrows(const uint32_t p, float (&a)[R][4], const TapsParam &k) {
+    if constexpr (J >= 0) {
+        const float4 v = lds128<J * kFTX * 4>(p);
+#pragma unroll
+        for (int c = 0; c < R; c++) {
+            const int t = c + 2 * HW - J;
+            if (t == 0) {
+                a[c][0] = tap_first<EXACT>(k.k[0], v.x);
+                a[c][1] = tap_first<EXACT>(k.k[0], v.y);
+                a[c][2] = tap_first<EXACT>(k.k[0], v.z);
+                a[c][3] = tap_first<EXACT>(k.k[0], v.w);
+            } else if (t > 0 && t <= 2 * HW) {
+                const float kt = k.k[fold<HW>(t)];
+                a[c][0] = tap_acc<EXACT>(a[c][0], kt, v.x);
+                a[c][1] = tap_acc<EXACT>(a[c][1], kt, v.y);
+                a[c][2] = tap_acc<EXACT>(a[c][2], kt, v.z);
+                a[c][3] = tap_acc<EXACT>(a[c][3], kt, v.w);
+            }
+        }
+        yrows<HW, R, EXACT, J - 1>(p, a, k);
+    }
+}
+
+// y pass in two phases. Loads: rows J = 0 .. R-1+2HW of the thread's 4 columns.
+template <int HW, int R, int J = 0>
+__device__ __forceinline__ void yload(const uint32_t p, float4 (&in)[R + 2 * HW]) {
+    if constexpr (J < R + 2 * HW) {
+        in[J] = lds128<J * kFTX * 4>(p);
+        yload<HW, R, J + 1>(p, in);
+    }
+}
+// FIR: every output receives its taps in ascending order (tap t of output c is row c + 2HW - t)
+template <int HW, int R, bool EXACT>
+__device__ __forceinline__ void yfir(const float4 (&in)[R + 2 * HW], float (&a)[R][4], const TapsParam &k) {
+#pragma unroll
+    for (int c = 0; c < R; c++) {
+        const float4 v0 = in[c + 2 * HW];
+        a[c][0] = tap_first<EXACT>(k.k[0], v0.x);
+        a[c][1] = tap_first<EXACT>(k.k[0], v0.y);
+        a[c][2] = tap_first<EXACT>(k.k[0], v0.z);
+        a[c][3] = tap_first<EXACT>(k.k[0], v0.w);
+    }
+#pragma unroll
+    for (int t = 1; t <= 2 * HW; t++) {
+        const float kt = k.k[fold<HW>(t)];
+#pragma unroll
+        for (int c = 0; c < R; c++) {
+            const float4 v = in[c + 2 * HW - t];
+            a[c][0] = tap_acc<EXACT>(a[c][0], kt, v.x);
+            a[c][1] = tap_acc<EXACT>(a[c][1], kt, v.y);
+            a[c][2] = tap_acc<EXACT>(a[c][2], kt, v.z);
+            a[c][3] = tap_acc<EXACT>(a[c][3], kt, v.w);
+        }
+    }
+}
+
+// Fused blur, unit tap spacing on all three axes. Thread (g = tid & 7, rg = tid >> 3) owns
+// the 4 columns x0 + 4g .. 4g+3 of the rows y0 + R*rg .. R*rg + R-1 in the y and z passes:
+// every shared-memory and global access of those passes is a 16-byte one.
+template <int HW, int R, int NT, bool EXACT>
+__global__ void __launch_bounds__(NT, ZCfg<HW, R, NT>::OCC)
 blur_zmarch_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ FusedParams P,
                    const __grid_constant__ ChunkTable tab) {
     using C = FusedCfg<HW>;
-    using L = ZmarchLayout<HW, TY>;
-    constexpr int NTM = 8 * TY;                   // main threads
-    constexpr int HWP = C::HWP, BW = C::BW, NINY = C::NINY;
+    using Z = ZCfg<HW, R, NT>;
+    using L = typename Z::L;
+    constexpr int TY = Z::TY;
+    constexpr int HWP = C::HWP, BW = C::BW, NIN = C::NIN;
     constexpr int TROWS = L::TROWS;               // staged rows (y halo)
     constexpr uint32_t TILE_BYTES = L::TILE_FLOATS * 4;
     constexpr int TILE_STRIDE = L::TILE_STRIDE;   // floats, 128-byte aligned TMA destinations
     constexpr int XF_STRIDE = L::XF_STRIDE;       // floats between the two x-filtered tiles
-    constexpr int NEXTRA = 2 * HW * 8;            // x-pass items of the halo rows (second items)
-    constexpr int FIXT = (TROWS + 31) / 32 * 32;  // threads (whole warps, the last ones) of the x-face fix-up
-    static_assert(32 + NEXTRA + FIXT <= NTM, "second x items (warps 1..) and fix-up rows (last warps) do not overlap");
+    constexpr int RPI = NT / 8;                   // tile rows covered by one round of x items
+    constexpr int kItems = (TROWS + RPI - 1) / RPI;
+    constexpr int NV = 4 * R;                     // voxels per thread
+    // Loads in flight: the shared-memory loads of a pass are issued before the arithmetic of the
+    // pass in front of it where the registers allow (a warp otherwise sits out one LDS latency
+    // per x item and one per y pass, with 4 warps per scheduler to cover it):
+#ifndef S3D_XMODE
+#define S3D_XMODE 0
+#endif
+#ifndef S3D_YFIRST
+#define S3D_YFIRST 0
+#endif
+    // x pass: 0 = inputs of an item right before its arithmetic, 1 = inputs of item k+1 before
+    // the arithmetic of item k, 2 = inputs of all items first
+    constexpr int XMODE = (S3D_XMODE == 2 && kItems * NIN > 36) ? 1 : S3D_XMODE;
+    constexpr bool XALL = XMODE == 2;
+    constexpr bool YFIRST = S3D_YFIRST && (R + 2 * HW) * 4 <= 40;  // y-pass inputs before the x pass
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float *tile = reinterpret_cast<float *>(smem_raw);                 // [kNB][TROWS][BW]
@@ -300,10 +385,10 @@ blur_zmarch_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
     uint64_t *mbar = reinterpret_cast<uint64_t *>(xf + 2 * XF_STRIDE); // [kNB]
     float *frx = reinterpret_cast<float *>(mbar + kNB);                // [HW + 1]
     float *fry = frx + (HW + 1);                                       // [HW + 1]
-    __shared__ float wmax_sh[NTM / 32];
+    __shared__ float wmax_sh[NT / 32];
 
     const int tid = threadIdx.x;
-    const int lane = tid & 31, w = tid >> 5;
+    const int g = tid & 7, rg = tid >> 3;
     const int nx = P.nx, ny = P.ny, nz = P.nz;
     const int dex = nx - 1, dey = ny - 1, dez = nz - 1;
     const int nzr = P.z1 - P.z0;
@@ -361,7 +446,7 @@ blur_zmarch_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
         const int qstart = top ? dez - 1 : ze - 1 + HW;
         const int N = npro + (qstart - (zb - HW) + 1);
 
-        // ---- TMA issue (thread 0) and x-face fix-up (the last warps, one tile row per thread)
+        // ---- TMA issue (thread 0) and x-face fix-up (one tile row per thread)
         auto issue = [&](int n) {  // stage stream element n
             const uint32_t s = (ebase + (uint32_t) n) & (kNB - 1);
             int pl;
@@ -375,24 +460,24 @@ blur_zmarch_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
             mbar_expect_tx_a(mbar0 + 8 * s, TILE_BYTES);
             tma_load_3d_a(tile0 + s * (TILE_STRIDE * 4), &tmap, x0 - HWP, y0 - HW, pl, mbar0 + 8 * s);
         };
-        // Extended line in x of element n: tile column c <-> x = x0 - HWP + c. Row frow of the
-        // staged tile is rewritten in place by its fixing thread, one plane ahead of the x pass.
-        const int frow = tid - (NTM - FIXT);
+        // Extended line in x of element n: tile column c <-> x = x0 - HWP + c. The rows of the
+        // staged tile are rewritten in place, one plane ahead of the x pass.
         auto fix = [&](int n) {
-            if (frow < 0 || frow >= TROWS) return;
             const uint32_t e = ebase + (uint32_t) n;
-            mbar_wait_a(mbar0 + 8 * (e & (kNB - 1)), (e >> 2) & 1u);
-            float *row = tile + (e & (kNB - 1)) * TILE_STRIDE + frow * BW;
-            if (x0 < HW) {  // E[-i] = E[i]
-                for (int c = HWP - HW; c < HWP - x0; c++) row[c] = row[2 * (HWP - x0) - c];
-            }
-            if (x0 + kFTX - 1 + HW >= dex) {
-                // E[dim_end + m] = lerp(E[dim_end-m-1], E[dim_end-m], fr_m); m = 0 last: it
-                // replaces E[dim_end] itself, the source of no other m
-                const int cd = dex - x0 + HWP;  // tile column of x = dim_end
-                for (int m = HW; m >= 0; m--)
-                    if (cd + m <= HWP + kFTX - 1 + HW)
-                        row[cd + m] = lerp1(row[cd - m - 1], row[cd - m], frx[m]);
+            if (tid < TROWS) mbar_wait_a(mbar0 + 8 * (e & (kNB - 1)), (e >> 2) & 1u);
+            for (int fr_ = tid; fr_ < TROWS; fr_ += NT) {
+                float *row = tile + (e & (kNB - 1)) * TILE_STRIDE + fr_ * BW;
+                if (x0 < HW) {  // E[-i] = E[i]
+                    for (int c = HWP - HW; c < HWP - x0; c++) row[c] = row[2 * (HWP - x0) - c];
+                }
+                if (x0 + kFTX - 1 + HW >= dex) {
+                    // E[dim_end + m] = lerp(E[dim_end-m-1], E[dim_end-m], fr_m); m = 0 last: it
+                    // replaces E[dim_end] itself, the source of no other m
+                    const int cd = dex - x0 + HWP;  // tile column of x = dim_end
+                    for (int m = HW; m >= 0; m--)
+                        if (cd + m <= HWP + kFTX - 1 + HW)
+                            row[cd + m] = lerp1(row[cd - m - 1], row[cd - m], frx[m]);
+                }
             }
             fence_proxy_async();  // these generic writes precede the TMA refill of the buffer
         };
@@ -400,106 +485,91 @@ blur_zmarch_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
             for (int n = 0; n < kNB && n < N; n++) issue(n);
         }
 
-        // ========================= main threads =========================
-        float A[4][2 * HW];
+        float A[NV][2 * HW];
 #pragma unroll
-        for (int c = 0; c < 4; c++)
+        for (int c = 0; c < NV; c++)
 #pragma unroll
             for (int t = 0; t < 2 * HW; t++) A[c][t] = 0.0f;
 
-        // ---- x-pass items of this thread (chunk invariant). Item 0: tile row HW + tid/8 (one
-        // of the tile's own TY rows), column group tid & 7. Item 1 (threads 32 .. 32+NEXTRA-1):
-        // one of the 2*HW halo rows. Source row(s) of tile row r, global row gy = y0 - HW + r:
-        //   gy < 0        mirror: row of -gy
+        // ---- x-pass items of this thread (chunk invariant): item k is tile row r = rg + k*RPI,
+        // column group g. Source row(s) of tile row r, global row gy = y0 - HW + r:
+        //   gy < 0        mirror: the row of -gy
         //   gy >= dey     virtual row dey + m = lerp(row dey-m-1, row dey-m, fry[m]) of the
         //                 x-FILTERED rows (the y pass of the reference reads x-filtered data)
-        uint32_t srcA[2], srcB[2], dstD[2];  // byte offsets inside a staged tile / an x-filtered tile
-        float frI[2];
-        const int j1 = tid - 32;
-        const bool has1 = j1 >= 0 && j1 < NEXTRA;
+        uint32_t srcA[kItems];  // byte offset of the (first) source row inside a staged tile
 #pragma unroll
-        for (int k = 0; k < 2; k++) {
-            int r, g;
-            if (k == 0) {
-                r = HW + (tid >> 3);
-                g = tid & 7;
-            } else {
-                const int hr = has1 ? (j1 >> 3) : 0;
-                r = hr < HW ? hr : hr + TY;
-                g = j1 & 7;
-            }
+        for (int k = 0; k < kItems; k++) {
+            const int r = rg + k * RPI;
             const int gy = y0 - HW + r;
-            int ra = r, rb = -1;
-            float fr = 0.0f;
-            if (gy < 0) {
-                ra = r - 2 * gy;
-            } else if (gy >= dey) {
-                const int m = gy - dey;
-                ra = r - 2 * m;
-                rb = ra - 1;
-                fr = fry[m];
-            }
+            int ra = r;
+            if (gy < 0) ra = r - 2 * gy;
+            else if (gy >= dey) ra = r - 2 * (gy - dey);
             srcA[k] = (uint32_t) (ra * BW + 4 * g) * 4u;
-            srcB[k] = rb >= 0 ? (uint32_t) (rb * BW + 4 * g) * 4u : 0xffffffffu;
-            dstD[k] = xf0 + (uint32_t) (r * kFTX + 4 * g) * 4u;
-            frI[k] = fr;
         }
+        const uint32_t xdst = xf0 + (uint32_t) (rg * kFTX + 4 * g) * 4u;
         // the tile holds virtual rows (uniform: it touches the high y face)
         const bool yvirt = y0 + TY - 1 + HW >= dey;
+        const bool last_item = rg + (kItems - 1) * RPI < TROWS;
 
-        const int x = x0 + lane;
-        const int ybase = y0 + 4 * w;
-        // decimation targets: even z, even rows, even x
+        const int x = x0 + 4 * g;
+        const int ybase = y0 + R * rg;
+        // decimation targets: even z, even rows, even x (components .x and .z)
         unsigned dmask = 0;
-        if (P.ds_dst != nullptr && !(x & 1) && (x >> 1) < dnx) {
+        if (P.ds_dst != nullptr) {
 #pragma unroll
-            for (int c = 0; c < 4; c++)
+            for (int c = 0; c < R; c++)
                 if (!((ybase + c) & 1) && ((ybase + c) >> 1) < dny) dmask |= 1u << c;
         }
-        const size_t ds_col = (size_t) (ybase >> 1) * dnx + (size_t) (x >> 1);
         // element (ze - 1, ybase, x): the first output stored; one plane down per stored plane
         unsigned goff = (unsigned) (ze - 1) * plane_stride + (unsigned) ybase * (unsigned) nx + (unsigned) x;
         const bool want_max = P.dogmax != nullptr;
-        const uint32_t ysrc = xf0 + (uint32_t) ((4 * w) * kFTX + lane) * 4u;  // y pass: rows 4w .. of column `lane`
+        const uint32_t ysrc = xf0 + (uint32_t) ((R * rg) * kFTX + 4 * g) * 4u;
 
         // x pass of stream element n into xf[n & 1]
         auto xpass = [&](const int n) {
             const uint32_t e = ebase + (uint32_t) n;
             const uint32_t s = e & (kNB - 1);
             const uint32_t tb = tile0 + s * (uint32_t) (TILE_STRIDE * 4);
-            const uint32_t xsel = (n & 1) ? (uint32_t) (XF_STRIDE * 4) : 0u;
+            const uint32_t xd = xdst + ((n & 1) ? (uint32_t) (XF_STRIDE * 4) : 0u);
             mbar_wait_a(mbar0 + 8 * s, (e >> 2) & 1u);
-            if (!yvirt) {
-                sts128(dstD[0] + xsel, xrow4<HW, EXACT>(tb + srcA[0], P.taps));
-                if (has1) sts128(dstD[1] + xsel, xrow4<HW, EXACT>(tb + srcA[1], P.taps));
-            } else {
-                // tiles at the high y face: the virtual row dey + m is the blend of two
-                // x-FILTERED rows
+            float xin[XALL ? kItems : 2][NIN];
+            if (XALL) {
 #pragma unroll
-                for (int k = 0; k < 2; k++) {
-                    if (k == 1 && !has1) break;
-                    float4 o = xrow4<HW, EXACT>(tb + srcA[k], P.taps);
-                    if (srcB[k] != 0xffffffffu) {
-                        const float4 a = xrow4<HW, EXACT>(tb + srcB[k], P.taps);
-                        const float fr = frI[k];
+                for (int k = 0; k < kItems; k++)
+                    if (k < kItems - 1 || last_item) xrow4_load<HW, EXACT>(tb + srcA[k], xin[k]);
+            } else if (XMODE == 1) {
+                xrow4_load<HW, EXACT>(tb + srcA[0], xin[0]);
+            }
+#pragma unroll
+            for (int k = 0; k < kItems; k++) {
+                if (k == kItems - 1 && !last_item) break;
+                if (XMODE == 1 && k + 1 < kItems && (k + 1 < kItems - 1 || last_item))
+                    xrow4_load<HW, EXACT>(tb + srcA[k + 1], xin[(k + 1) & 1]);
+                if (XMODE == 0) xrow4_load<HW, EXACT>(tb + srcA[k], xin[k & 1]);
+                float4 o = xrow4_fir<HW, EXACT>(xin[XALL ? k : (k & 1)], P.taps);
+                if (yvirt) {
+                    const int m = y0 - HW + rg + k * RPI - dey;
+                    if (m >= 0) {
+                        const float4 a = xrow4<HW, EXACT>(tb + srcA[k] - (uint32_t) (BW * 4), P.taps);
+                        const float fr = fry[m];
                         o = make_float4(lerp1(a.x, o.x, fr), lerp1(a.y, o.y, fr), lerp1(a.z, o.z, fr),
                                         lerp1(a.w, o.w, fr));
                     }
-                    sts128(dstD[k] + xsel, o);
                 }
+                sts128(xd + (uint32_t) (k * RPI * kFTX * 4), o);
             }
         };
-        // y pass of element n: rows 4w .. 4w+3+2*HW of the x-filtered tile, column `lane`
-        auto ypass = [&](const int n, float (&yv)[4]) {
-            float in[NINY];
-            ycol_load<HW>(ysrc + ((n & 1) ? (uint32_t) (XF_STRIDE * 4) : 0u), in);
-#pragma unroll
-            for (int c = 0; c < 4; c++) {
-                float a = tap_first<EXACT>(P.taps.k[0], in[c + 2 * HW]);  // tap d = t - HW samples row y - d
-#pragma unroll
-                for (int t = 1; t < 2 * HW + 1; t++)
-                    a = tap_acc<EXACT>(a, P.taps.k[fold<HW>(t)], in[c + 2 * HW - t]);
-                yv[c] = a;
+        // one stream element: x pass of element n+1 (if any), y pass of element n
+        auto plane = [&](const int n, const bool more, float (&yv)[R][4]) {
+            const uint32_t ya = ysrc + ((n & 1) ? (uint32_t) (XF_STRIDE * 4) : 0u);
+            if constexpr (YFIRST) {
+                float4 yin[R + 2 * HW];
+                yload<HW, R>(ya, yin);
+                if (more) xpass(n + 1);
+                yfir<HW, R, EXACT>(yin, yv, P.taps);
+            } else {
+                if (more) xpass(n + 1);
+                yrows<HW, R, EXACT, R - 1 + 2 * HW>(ya, yv, P.taps);
             }
         };
 
@@ -516,21 +586,28 @@ blur_zmarch_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
         if (top) {
             // ---- prologue (top chunk): y-filtered planes dez-HW-1 .. dez, ascending; from the
             // second one on, the virtual plane dez + m = lerp(plane dez-m-1, plane dez-m) is fed
-            float prev[4] = {0.f, 0.f, 0.f, 0.f};
+            float prev[R][4];
+#pragma unroll
+            for (int c = 0; c < R; c++)
+#pragma unroll
+                for (int i = 0; i < 4; i++) prev[c][i] = 0.0f;
             for (; n < npro; n++) {
-                xpass(n + 1);  // the main stream is never empty
-                float yv[4];
-                ypass(n, yv);
+                float yv[R][4];
+                plane(n, true, yv);  // (the main stream is never empty)
                 if (n > 0) {
                     const float fr = right_frac(dez + P.zorg, HW + 1 - n);
 #pragma unroll
-                    for (int c = 0; c < 4; c++) {
-                        const float v = lerp1(prev[c], yv[c], fr);
-                        (void) zfeed<HW, EXACT>(A[c], v, P.taps);  // outputs beyond the volume
-                    }
+                    for (int c = 0; c < R; c++)
+#pragma unroll
+                        for (int i = 0; i < 4; i++) {
+                            const float v = lerp1(prev[c][i], yv[c][i], fr);
+                            (void) zfeed<HW, EXACT>(A[4 * c + i], v, P.taps);  // outputs beyond the volume
+                        }
                 }
 #pragma unroll
-                for (int c = 0; c < 4; c++) prev[c] = yv[c];
+                for (int c = 0; c < R; c++)
+#pragma unroll
+                    for (int i = 0; i < 4; i++) prev[c][i] = yv[c][i];
                 if (xfix && n + 2 < N) fix(n + 2);
                 __syncthreads();
                 // the buffer of element n+1 was consumed by the x pass of this iteration
@@ -542,39 +619,46 @@ blur_zmarch_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
         int zo = qstart + HW;  // output completed by element n
         for (; n < N; n++, zo--) {
             const bool store = zo < ze;
-            const unsigned g1 = goff + (unsigned) nx, g2 = g1 + (unsigned) nx, g3 = g2 + (unsigned) nx;
             // source voxels of the DoG max: requested a whole plane step before they are used
-            float pv[4] = {0.f, 0.f, 0.f, 0.f};
+            float4 pv[R];
             if (want_max && store) {
-                pv[0] = __ldg(P.src + goff);
-                pv[1] = __ldg(P.src + g1);
-                pv[2] = __ldg(P.src + g2);
-                pv[3] = __ldg(P.src + g3);
-            }
-            if (n + 1 < N) xpass(n + 1);
-            float yv[4];
-            ypass(n, yv);
-            float o[4];
 #pragma unroll
-            for (int c = 0; c < 4; c++) o[c] = zfeed<HW, EXACT>(A[c], yv[c], P.taps);
+                for (int c = 0; c < R; c++)
+                    pv[c] = __ldg(reinterpret_cast<const float4 *>(P.src + (goff + (unsigned) (c * nx))));
+            }
+            float yv[R][4];
+            plane(n, n + 1 < N, yv);
+            float o[R][4];
+#pragma unroll
+            for (int c = 0; c < R; c++)
+#pragma unroll
+                for (int i = 0; i < 4; i++) o[c][i] = zfeed<HW, EXACT>(A[4 * c + i], yv[c][i], P.taps);
             if (store) {
                 if (!EXACT && P.out_scale != nullptr) {
 #pragma unroll
-                    for (int c = 0; c < 4; c++) o[c] = __fmul_rn(o[c], oscale);
+                    for (int c = 0; c < R; c++)
+#pragma unroll
+                        for (int i = 0; i < 4; i++) o[c][i] = __fmul_rn(o[c][i], oscale);
                 }
-                P.dst[goff] = o[0];
-                P.dst[g1] = o[1];
-                P.dst[g2] = o[2];
-                P.dst[g3] = o[3];
+#pragma unroll
+                for (int c = 0; c < R; c++)
+                    *reinterpret_cast<float4 *>(P.dst + (goff + (unsigned) (c * nx))) =
+                        make_float4(o[c][0], o[c][1], o[c][2], o[c][3]);
                 if (want_max) {
 #pragma unroll
-                    for (int c = 0; c < 4; c++) vmax = fmaxf(vmax, fabsf(__fsub_rn(pv[c], o[c])));
+                    for (int c = 0; c < R; c++) {
+                        const float m01 = fmaxf(fabsf(__fsub_rn(pv[c].x, o[c][0])), fabsf(__fsub_rn(pv[c].y, o[c][1])));
+                        const float m23 = fmaxf(fabsf(__fsub_rn(pv[c].z, o[c][2])), fabsf(__fsub_rn(pv[c].w, o[c][3])));
+                        vmax = fmaxf(vmax, fmaxf(m01, m23));
+                    }
                 }
                 if (dmask != 0 && !(zo & 1) && (zo >> 1) < dnz) {
-                    float *qd = P.ds_dst + ((size_t) (zo >> 1) * dny * dnx + ds_col);
+                    float *qd = P.ds_dst + ((size_t) (zo >> 1) * dny * dnx + (size_t) (x >> 1));
 #pragma unroll
-                    for (int c = 0; c < 4; c++)
-                        if (dmask & (1u << c)) qd[(((ybase + c) >> 1) - (ybase >> 1)) * dnx] = o[c];
+                    for (int c = 0; c < R; c++)
+                        if (dmask & (1u << c))
+                            *reinterpret_cast<float2 *>(qd + (size_t) ((ybase + c) >> 1) * dnx) =
+                                make_float2(o[c][0], o[c][2]);
                 }
                 goff -= plane_stride;
             }
@@ -588,10 +672,10 @@ blur_zmarch_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_consta
     // ---- DoG max-abs: block reduce, one atomic per CTA (non-negative floats order as ints)
     if (P.dogmax != nullptr) {
         for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
-        if (lane == 0) wmax_sh[w] = vmax;
+        if ((tid & 31) == 0) wmax_sh[tid >> 5] = vmax;
         __syncthreads();
         if (tid < 32) {
-            float m2 = tid < NTM / 32 ? wmax_sh[tid] : 0.0f;
+            float m2 = tid < NT / 32 ? wmax_sh[tid] : 0.0f;
             for (int o = 16; o > 0; o >>= 1) m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
             if (tid == 0) atomicMax(reinterpret_cast<int *>(P.dogmax), __float_as_int(m2));
         }
