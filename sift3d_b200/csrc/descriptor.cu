@@ -380,22 +380,12 @@ descriptor_rows_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
 }
 
 // ---------------------------------------------------------------------------------------
-// v3: flattened in-window work list.
-//
 // The window of a keypoint is the sphere of radius 2*sigma intersected with the rotated
 // cube of half-width rad/sqrt(2) (only voxels whose rotated coordinates fall into the
 // 4x4x4 cell grid contribute, sift.c:1488-1492) -- about a third of the bounding box the
-// reference loops over. Walking the bounding box (or one row per thread) leaves two thirds
-// of the lanes idle, so:
-//   phase 1  every (y, z) row of the bounding box gets a conservative x interval
-//            [xa, xa+len) covering sphere /\ cube (closed form: three slabs and a chord);
-//   phase 2  block-wide exclusive scan of len -> the flattened voxel list of T entries;
-//   phase 3  thread t walks entries [t*C, (t+1)*C), C = ceil(T/256): consecutive voxels of
-//            consecutive rows, so every lane runs the same trip count, and neighbouring
-//            voxels keep the (cell, face) key so the 8x3 contributions are summed in
-//            registers and flushed to shared memory only when the key changes.
-// The exact per-voxel tests of the reference are kept (the intervals are supersets), so
-// the set of contributing voxels is the reference's.
+// reference loops over. The exact per-voxel tests of the reference are kept (the closed-form
+// x intervals the kernel walks are supersets), so the set of contributing voxels is the
+// reference's.
 //
 // Face lookup: nearest face centre out of the 4 candidates of the direction's octant
 // (icosahedral symmetry), confirmed by the reference's own Moller-Trumbore test with a
@@ -465,327 +455,6 @@ __device__ __forceinline__ void fix_add2(unsigned *lo, int *hi, int i, float v) 
     const long long q = __float2ll_rn(v * kFix2Scale);
     atomicAdd(lo + i, (unsigned) q & ((1u << kFix2LoBits) - 1u));
     atomicAdd(hi + i, (int) (q >> kFix2LoBits));
-}
-
-__global__ void __launch_bounds__(kDescThreads)
-descriptor_flat_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ desc_out,
-                       int max_rows) {
-    extern __shared__ __align__(16) int dyn_smem[];
-    int *row_off = dyn_smem;                                            // [max_rows + 1]
-    short *row_xa = reinterpret_cast<short *>(dyn_smem + max_rows + 1);  // [max_rows]
-    // 5x5x5 cells: the 8 trilinear targets of any voxel exist, so the flush needs no range
-    // tests (cells with an index of 4 are never read back, sift.c:1346-1352 drops them)
-    __shared__ unsigned hlo[kPadNumel];
-    __shared__ int hhi[kPadNumel];
-    __shared__ float hist[kDescNumel];
-    __shared__ __align__(16) float smesh[kFaces * 16];
-    __shared__ int sidx[kFaces * 3];
-    __shared__ unsigned char slut[32];
-    __shared__ int part[kDescThreads / 32];
-    __shared__ double red[kDescThreads / 32];
-    __shared__ double norm_sh;
-    const int ki = blockIdx.x;
-    if (ki >= n) return;
-    const DescJob J = jobs[ki];
-    const int tid = threadIdx.x;
-    const int lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < kPadNumel; i += kDescThreads) {
-        hlo[i] = 0u;
-        hhi[i] = 0;
-    }
-    if (tid < kFaces) {
-        float *fm = smesh + tid * 16;
-        for (int k = 0; k < 3; k++) {
-            fm[k] = c_mesh.e1[tid][k];
-            fm[3 + k] = c_mesh.e2[tid][k];
-            fm[6 + k] = c_mesh.t[tid][k];
-            fm[9 + k] = c_mesh.q[tid][k];
-            sidx[tid * 3 + k] = c_mesh.idx[tid][k];
-        }
-        fm[12] = c_mesh.e2q[tid];
-        fm[13] = fm[14] = fm[15] = 0.0f;
-    }
-    if (tid < 32) slut[tid] = c_mesh.lut[tid >> 2][tid & 3];
-
-    const float *__restrict__ img = J.img;
-    const int nx = J.nx, ny = J.ny, nz = J.nz;
-    const float uxf = J.ux, uyf = J.uy, uzf = J.uz;
-    const float cx = J.cx, cy = J.cy, cz = J.cz;
-    // sift.c:1453-1458
-    const float sigma = J.sigma;
-    const float rad = (float) (kDescRadFctr * (double) sigma);
-    const float half_w = (float) ((double) rad / sqrt(2.0));
-    const float desc_w = __fmul_rn(2.0f, half_w);
-    const float hist_w = __fdiv_rn(desc_w, (float) kHistPerDim);
-    const float bin_fctr = __fdiv_rn(1.0f, hist_w);
-    const float rad2 = __fmul_rn(rad, rad);
-    const float sig2 = __fmul_rn(sigma, sigma);
-    const float ixu = __fdiv_rn(1.0f, uxf), iyu = __fdiv_rn(1.0f, uyf), izu = __fdiv_rn(1.0f, uzf);
-
-    // Window (sift.c:91-99), all-float here because win_radius is a float.
-    const int x0 = (int) fmaxf(floorf(__fsub_rn(cx, __fdiv_rn(rad, uxf))), 1.0f);
-    const int x1 = (int) fminf(ceilf(__fadd_rn(cx, __fdiv_rn(rad, uxf))), (float) (nx - 2));
-    const int y0 = (int) fmaxf(floorf(__fsub_rn(cy, __fdiv_rn(rad, uyf))), 1.0f);
-    const int y1 = (int) fminf(ceilf(__fadd_rn(cy, __fdiv_rn(rad, uyf))), (float) (ny - 2));
-    const int z0 = (int) fmaxf(floorf(__fsub_rn(cz, __fdiv_rn(rad, uzf))), 1.0f);
-    const int z1 = (int) fminf(ceilf(__fadd_rn(cz, __fdiv_rn(rad, uzf))), (float) (nz - 2));
-    const int wy = max(y1 - y0 + 1, 0), wz = max(z1 - z0 + 1, 0);
-    int nrows = (x1 >= x0) ? wy * wz : 0;
-    if (nrows > max_rows) nrows = max_rows;  // cannot happen: desc_job_rows() is an upper bound
-    const size_t ys = (size_t) nx, zs = (size_t) nx * ny;
-
-    // Rt = R^T (sift.c:1462-1464): Rt[i][j] = R[j][i]
-    const float r00 = J.R[0], r01 = J.R[1], r02 = J.R[2];
-    const float r10 = J.R[3], r11 = J.R[4], r12 = J.R[5];
-    const float r20 = J.R[6], r21 = J.R[7], r22 = J.R[8];
-
-    // ---- phase 1: conservative x interval of every row
-    const int rpt = (nrows + kDescThreads - 1) / kDescThreads;
-    const int rbeg = min(tid * rpt, nrows), rend = min(rbeg + rpt, nrows);
-    const float hwm = half_w * 1.001f + 1e-6f;
-    int mysum = 0;
-    for (int r = rbeg; r < rend; r++) {
-        const int y = y0 + r % wy, z = z0 + r / wy;
-        const float dy = ((float) y - cy) * uyf, dz = ((float) z - cz) * uzf;
-        int len = 0, xa = x0;
-        const float rem = rad2 * 1.0001f - dy * dy - dz * dz;
-        if (rem >= 0.0f) {
-            const float half = sqrtf(rem) * ixu + 0.01f;
-            float lo = cx - half, hi = cx + half;
-            bool empty = false;
-            const float av[3] = {r00 * uxf, r01 * uxf, r02 * uxf};
-            const float bv[3] = {r10 * dy + r20 * dz, r11 * dy + r21 * dz, r12 * dy + r22 * dz};
-#pragma unroll
-            for (int i = 0; i < 3; i++) {
-                if (fabsf(av[i]) > 1e-6f) {
-                    const float inv = 1.0f / av[i];
-                    const float t1 = (-hwm - bv[i]) * inv, t2 = (hwm - bv[i]) * inv;
-                    lo = fmaxf(lo, cx + fminf(t1, t2) - 0.01f);
-                    hi = fminf(hi, cx + fmaxf(t1, t2) + 0.01f);
-                } else if (fabsf(bv[i]) > hwm) {
-                    empty = true;
-                }
-            }
-            if (!empty) {
-                xa = max(x0, (int) ceilf(lo));
-                const int xb = min(x1, (int) floorf(hi));
-                len = max(0, xb - xa + 1);
-            }
-        }
-        row_off[r] = len;
-        row_xa[r] = (short) xa;
-        mysum += len;
-    }
-    // ---- phase 2: exclusive scan over threads, then over each thread's rows
-    int incl = mysum;
-    for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
-    }
-    if (lane == 31) part[warp] = incl;
-    __syncthreads();
-    int base = incl - mysum;
-    int total = 0;
-    for (int wv = 0; wv < kDescThreads / 32; wv++) {
-        const int p = part[wv];
-        if (wv < warp) base += p;
-        total += p;
-    }
-    for (int r = rbeg; r < rend; r++) {
-        const int len = row_off[r];
-        row_off[r] = base;
-        base += len;
-    }
-    if (tid == 0) row_off[nrows] = total;
-    __syncthreads();
-    // ---- phase 3: walk my slice of the flattened list
-    const int chunk = (total + kDescThreads - 1) / kDescThreads;
-    const int t0 = min(tid * chunk, total), t1 = min(t0 + chunk, total);
-
-    // Accumulation in integers. The three vertex magnitudes m_k = mag * bary_k are rounded
-    // to S fractional bits and the eight trilinear weights to 10, so that a contribution is
-    // one exact IMAD: P = M_k * W_c (|P| < 2^30), added as two 32-bit words (low 12 bits,
-    // signed rest) with the native ATOMS.ADD -- integer adds commute, so descriptors are
-    // reproducible run to run. S is the largest exponent for which neither |M| < 2^20 nor the
-    // high word can overflow under the analytic bound of the path: levels lie in [-1, 1]
-    // (im_scale), so |grad| <= sqrt(3)/u_min (x2 safety), and the weights one bin can
-    // receive sum to about one cell volume in voxels (x2 safety).
-    const float umin = fminf(uxf, fminf(uyf, uzf));
-    const float gbound = 2.0f * 1.7320508f / umin;
-    const float cellvox = fmaxf(hist_w * hist_w * hist_w / (uxf * uyf * uzf), 1.0f);
-    int fixS = min(ilogbf(1048576.0f / gbound), ilogbf(4294967296.0f / (gbound * cellvox)));
-    fixS = max(0, min(fixS, 22));
-    const float magic_m = ldexpf(1.5f, 23 - fixS);     // ulp(magic_m) = 2^-S
-    const int magic_m_bits = __float_as_int(magic_m);
-    const float m_lim = ldexpf(1048575.0f, -fixS);      // |M| < 2^20
-    const float magic_w = 12288.0f;                     // 1.5 * 2^13: ulp = 2^-10
-
-    if (t0 < t1) {
-        // row containing entry t0: the last r with row_off[r] <= t0 (its length is > 0)
-        int lo = 0, hi = nrows;  // invariant: row_off[lo] <= t0 < row_off[hi]
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (row_off[mid] <= t0) lo = mid; else hi = mid;
-        }
-        int r = lo;
-        int y = y0 + r % wy, z = z0 + r / wy;
-        int x = (int) row_xa[r] + (t0 - row_off[r]);
-        int xend = (int) row_xa[r] + (row_off[r + 1] - row_off[r]) - 1;
-        // per-row invariants
-        float dy, dz, dy2, dz2, bkx, bky, bkz, ckx, cky, ckz;
-        const float *__restrict__ row;
-#define S3D_ROW_SETUP()                                                                    \
-        {                                                                                  \
-            dy = __fmul_rn(__fsub_rn((float) y, cy), uyf);                                 \
-            dz = __fmul_rn(__fsub_rn((float) z, cz), uzf);                                 \
-            dy2 = __fmul_rn(dy, dy);                                                       \
-            dz2 = __fmul_rn(dz, dz);                                                       \
-            bkx = __fmul_rn(r10, dy); ckx = __fmul_rn(r20, dz);                            \
-            bky = __fmul_rn(r11, dy); cky = __fmul_rn(r21, dz);                            \
-            bkz = __fmul_rn(r12, dy); ckz = __fmul_rn(r22, dz);                            \
-            row = img + (size_t) z * zs + (size_t) y * ys;                                 \
-        }
-        S3D_ROW_SETUP();
-        for (int t = t0; t < t1; t++) {
-            do {  // one voxel; `break` = the reference's `continue`
-                const float dx = __fmul_rn(__fsub_rn((float) x, cx), uxf);
-                const float sq = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), dy2), dz2);
-                if (sq > rad2) break;
-                // vkp = Rt * vim (SIFT3D_MUL_MAT_RM_CVEC, immacros.h:326-342)
-                const float kx = __fadd_rn(__fadd_rn(__fmul_rn(r00, dx), bkx), ckx);
-                const float ky = __fadd_rn(__fadd_rn(__fmul_rn(r01, dx), bky), cky);
-                const float kz = __fadd_rn(__fadd_rn(__fmul_rn(r02, dx), bkz), ckz);
-                const float vbx = __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
-                const float vby = __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
-                const float vbz = __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
-                if (vbx < 0.0f || vby < 0.0f || vbz < 0.0f || vbx >= (float) kHistPerDim ||
-                    vby >= (float) kHistPerDim || vbz >= (float) kHistPerDim)
-                    break;
-
-                float gx = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + 1], row[x - 1])), ixu);
-                float gy = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys])), iyu);
-                float gz = __fmul_rn(__fmul_rn(0.5f, __fsub_rn(row[x + zs], row[(ptrdiff_t) x - (ptrdiff_t) zs])), izu);
-                const float w = expf(__fdiv_rn(__fmul_rn(-0.5f, sq), sig2));  // sift.c:1498
-                gx = __fmul_rn(gx, w);
-                gy = __fmul_rn(gy, w);
-                gz = __fmul_rn(gz, w);
-                const float rx = __fadd_rn(__fadd_rn(__fmul_rn(r00, gx), __fmul_rn(r10, gy)), __fmul_rn(r20, gz));
-                const float ry = __fadd_rn(__fadd_rn(__fmul_rn(r01, gx), __fmul_rn(r11, gy)), __fmul_rn(r21, gz));
-                const float rz = __fadd_rn(__fadd_rn(__fmul_rn(r02, gx), __fmul_rn(r12, gy)), __fmul_rn(r22, gz));
-
-                // icos_hist_bin (sift.c:1254-1291)
-                const float n2 = __fadd_rn(__fadd_rn(__fmul_rn(rx, rx), __fmul_rn(ry, ry)), __fmul_rn(rz, rz));
-                if ((double) n2 < kBaryEps) break;
-                // nearest face centre among the 4 candidates of this octant (selection only)
-                const float ax = fabsf(rx), ay = fabsf(ry), az = fabsf(rz);
-                const float kA = 2.6180339887f, kB = 1.6180339887f, kC = 4.2360679775f;  // 1+phi, phi, 2phi+1
-                const float d0 = kA * (ax + ay + az);
-                const float d1 = fmaf(kB, ax, kC * az);
-                const float d2 = fmaf(kC, ay, kB * az);
-                const float d3 = fmaf(kC, ax, kB * ay);
-                int which = 0;
-                float dbest = d0;
-                if (d1 > dbest) { dbest = d1; which = 1; }
-                if (d2 > dbest) { dbest = d2; which = 2; }
-                if (d3 > dbest) { dbest = d3; which = 3; }
-                const int oct = (rx < 0.0f ? 1 : 0) | (ry < 0.0f ? 2 : 0) | (rz < 0.0f ? 4 : 0);
-                const int best = slut[oct * 4 + which];
-                float bx, by, bz;
-                int face = -1;
-                if (face_hit_s(smesh + best * 16, rx, ry, rz, bx, by, bz) && bx > 1e-5f && by > 1e-5f &&
-                    bz > 1e-5f) {
-                    face = best;
-                } else {
-                    for (int f = 0; f < kFaces; f++) {
-                        if (face_hit_s(smesh + f * 16, rx, ry, rz, bx, by, bz)) { face = f; break; }
-                    }
-                }
-                if (face < 0) break;  // "unreachable" in the reference (sift.c:1288-1290)
-                const float mag = sqrtf(n2);
-
-                // SIFT3D_desc_acc_interp (sift.c:1318-1397)
-                const int bxi = (int) vbx, byi = (int) vby, bzi = (int) vbz;
-                const int hb = (bxi + byi * kPadDim + bzi * kPadDim * kPadDim) * kVerts;
-                const float fx = __fsub_rn(vbx, floorf(vbx));
-                const float fy = __fsub_rn(vby, floorf(vby));
-                const float fz = __fsub_rn(vbz, floorf(vbz));
-                int M[3], A[3];
-                {
-                    const float bary[3] = {bx, by, bz};
-#pragma unroll
-                    for (int k = 0; k < 3; k++) {
-                        const float m = fminf(fmaxf(__fmul_rn(mag, bary[k]), -m_lim), m_lim);
-                        M[k] = __float_as_int(__fadd_rn(m, magic_m)) - magic_m_bits;
-                        A[k] = hb + sidx[face * 3 + k];
-                    }
-                }
-                const float wx[2] = {__fsub_rn(1.0f, fx), fx};
-                const float wy2[2] = {__fsub_rn(1.0f, fy), fy};
-                const float wz2[2] = {__fsub_rn(1.0f, fz), fz};
-#pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    const int ddx = c >> 2, ddy = (c >> 1) & 1, ddz = c & 1;
-                    const float wgt = __fmul_rn(__fmul_rn(wx[ddx], wy2[ddy]), wz2[ddz]);
-                    const int W = __float_as_int(__fadd_rn(wgt, magic_w)) & 0x7ff;
-                    const int off = (ddx + ddy * kPadDim + ddz * kPadDim * kPadDim) * kVerts;
-#pragma unroll
-                    for (int k = 0; k < 3; k++) {
-                        const int P = M[k] * W;
-                        atomicAdd(hlo + A[k] + off, (unsigned) P & ((1u << kFix2LoBits) - 1u));
-                        atomicAdd(hhi + A[k] + off, P >> kFix2LoBits);
-                    }
-                }
-            } while (0);
-            // next entry of the flattened list
-            if (++x > xend && t + 1 < t1) {
-                do {
-                    r++;
-                    if (++y > y1) { y = y0; z++; }
-                } while (row_off[r + 1] == row_off[r]);
-                x = (int) row_xa[r];
-                xend = x + (row_off[r + 1] - row_off[r]) - 1;
-                S3D_ROW_SETUP();
-            }
-        }
-#undef S3D_ROW_SETUP
-    }
-    __syncthreads();
-    for (int i = tid; i < kDescNumel; i += kDescThreads) {
-        const int bin = i % kVerts, cell = i / kVerts;
-        const int hx = cell & 3, hy = (cell >> 2) & 3, hz = cell >> 4;
-        const int j = (hx + hy * kPadDim + hz * kPadDim * kPadDim) * kVerts + bin;
-        const long long q = (long long) hhi[j] * (1ll << kFix2LoBits) + (long long) hlo[j];
-        hist[i] = (float) ldexp((double) q, -(fixS + 10));
-    }
-    __syncthreads();
-
-    // normalise, clamp, normalise (sift.c:1513-1526)
-    const float trunc = __fdiv_rn(__fmul_rn(0.2f, 128.0f), (float) kDescNumel);  // sift.c:45
-    for (int pass = 0; pass < 2; pass++) {
-        double ssq = 0.0;
-        for (int i = tid; i < kDescNumel; i += kDescThreads) {
-            const float el = hist[i];
-            ssq += (double) el * (double) el;
-        }
-        for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
-        if (lane == 0) red[warp] = ssq;
-        __syncthreads();
-        if (tid == 0) {
-            double t = 0.0;
-            for (int wv = 0; wv < kDescThreads / 32; wv++) t += red[wv];
-            norm_sh = sqrt(t) + DBL_EPSILON;
-        }
-        __syncthreads();
-        const float norm_inv = (float) (1.0 / norm_sh);  // sift.c:1423
-        for (int i = tid; i < kDescNumel; i += kDescThreads) {
-            float el = __fmul_rn(hist[i], norm_inv);
-            if (pass == 0) el = fminf(el, trunc);
-            hist[i] = el;
-        }
-        __syncthreads();
-    }
-    float *o = desc_out + (size_t) J.out_index * kDescNumel;
-    for (int i = tid; i < kDescNumel; i += kDescThreads) o[i] = hist[i];
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1138,7 +807,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
                 const float p1 = dot3<true>(m1.x, rx, m1.y, ry2, m1.z, rz2);
                 const float p2 = dot3<true>(m2.x, rx, m2.y, ry2, m2.z, rz2);
                 const float sum = p0 + p1 + p2;
-                const float inv = __frcp_rn(sum);
+                const float inv = __fdividef(1.0f, sum);  // MUFU.RCP: the barycentric weights are tolerance quantities
                 bx = p0 * inv; by = p1 * inv; bz = p2 * inv;
                 hit = sum > 0.0f && bx > 1e-5f && by > 1e-5f && bz > 1e-5f;
             } else {
@@ -1150,7 +819,8 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             v.valid = ok;
             v.slow = ok && !hit;  // near an edge: the literal first-hit scan decides
             v.rx = rx; v.ry = ry2; v.rz = rz2; v.n2 = n2;
-            v.mag = sqrtf(n2);  // here, not in accumulate(): off the LDS -> FMA -> STS chain
+            // (here, not in accumulate(): off the LDS -> FMA -> STS chain) MUFU.SQRT, 1 ulp
+            asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(v.mag) : "f"(n2));
             v.b0 = bx; v.b1 = by; v.b2 = bz;
             return v;
         };
@@ -1299,11 +969,9 @@ int desc_job_rows(const DescJob &J) {
 int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_rows, float *d_desc,
                        uint64_t *launches) {
     if (n <= 0) return 0;
-    // the flattened-list kernel keeps 6 bytes per window row in shared memory; windows too
-    // large for that (huge sigma / tiny units) take the row-walking kernel
+    // $SIFT3D_CUDA_DESC_ROWS: the literal reference-loop kernel (diagnostics)
     static const bool force_rows = getenv("SIFT3D_CUDA_DESC_ROWS") != nullptr;
-    static const bool force_v3 = getenv("SIFT3D_CUDA_DESC_V3") != nullptr;
-    if (!force_rows && !force_v3) {
+    if (!force_rows) {
         const size_t dyn4 = (size_t) (kDescThreads / 32) * kCellBins * 32 * sizeof(float);
         static PerDeviceOnce attr4;
         if (attr4.first()) {
@@ -1316,17 +984,8 @@ int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_ro
         S3D_CK(cudaGetLastError());
         return 0;
     }
-    const size_t dyn = ((size_t) max_rows + 1) * 4 + (size_t) max_rows * 2 + 16;
-    const size_t kMaxDyn = 96 * 1024;
-    if (!force_rows && max_rows >= 1 && dyn <= kMaxDyn) {
-        static PerDeviceOnce attr_flat;
-        if (attr_flat.first())
-            S3D_CK(cudaFuncSetAttribute(descriptor_flat_kernel,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kMaxDyn));
-        descriptor_flat_kernel<<<(unsigned) n, kDescThreads, dyn, st>>>(d_jobs, n, d_desc, max_rows);
-    } else {
-        descriptor_rows_kernel<<<(unsigned) n, kDescThreads, 0, st>>>(d_jobs, n, d_desc);
-    }
+    (void) max_rows;
+    descriptor_rows_kernel<<<(unsigned) n, kDescThreads, 0, st>>>(d_jobs, n, d_desc);
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
     return 0;
