@@ -296,20 +296,28 @@ def run_product_arm(args):
     # input host->device and its results device->host inside the timed region: K steps,
     # K uploads (the first step consumes the upload started by the last warm-up step, the
     # last step starts the one the next step would consume).
-    def step(i):  # noqa: F811 - same sequence, with the next input in flight
-        # The upload is started between detect and extract: it then rides under the single
-        # long descriptor kernel. Started before detect it would delay each of detect's ~40
-        # launches by ~30 us (command fetches share PCIe with the 64 MiB transfer).
+    def step(i):  # noqa: F811 - same sequence, with the next inputs in flight
+        # Uploads run two volumes ahead and are started between detect and extract: an upload
+        # first rides under the single long descriptor kernel and has a whole further step to
+        # finish, so it is never waited for even when 8 ranks share the host's memory and PCIe
+        # bandwidth (at N = 8 a 64 MiB upload takes longer than the descriptor kernel). Started
+        # right before detect it would slow detect's launches down (PCIe traffic in front of
+        # the command fetches: +0.2 .. 0.35 ms per step).
         det.detect(images[i % NUM_INPUTS], kp)
-        images[(i + 1) % NUM_INPUTS].prefetch(local)
+        images[(i + 2) % NUM_INPUTS].prefetch(local)
         if len(kp):
             det.extract(kp, ds)
 
     images[0].prefetch(local)
+    images[1].prefetch(local)
     for i in range(NUM_INPUTS):
         step(i)
-    e_ms, e_wall, _, _ = timed(args.steps, 2, 3, False,
-                               drain=lambda k: images[k % NUM_INPUTS].prefetch_wait())
+
+    def drain(k):
+        images[k % NUM_INPUTS].prefetch_wait()
+        images[(k + 1) % NUM_INPUTS].prefetch_wait()
+
+    e_ms, e_wall, _, _ = timed(args.steps, 2, 3, False, drain=drain)
 
     if rank != 0:
         if dist is not None:
@@ -344,9 +352,9 @@ def run_product_arm(args):
         "wall_ms_per_step": 1e3 * wall / args.steps,
         "stage_ms": stage,
         "e2e": {"value": e2e, "unit": "voxels/s", "ms_per_step": e_ms / args.steps,
-                "mode": "stream of volumes: upload of volume i+1 (sift3d_image_prefetch) overlaps "
-                        "the kernels of volume i; every step uploads its input and downloads "
-                        "its results inside the timed region",
+                "mode": "stream of volumes: the upload of volume i+2 (sift3d_image_prefetch) is started "
+                        "during step i; every step uploads one whole input and downloads its "
+                        "results inside the timed region (K steps, K uploads)",
                 "single_volume_latency_ms": l_ms / args.steps,
                 "h2d_bytes_per_step": NVOX * 4 + nkeys * 96,
                 "d2h_bytes_per_step": ncand * 88 + nkeys * 768 * 4 + 64 * 4,

@@ -62,12 +62,25 @@ struct sift3d_cuda_ctx {
     cudaEvent_t ev_done[SIFT3D_CUDA_MAX_OCTAVES] = {};
     bool serial = false;                // $SIFT3D_CUDA_SERIAL: everything on one stream
     bool exact = false;                 // 0-ULP blur arithmetic (sift3d_cuda_set_exact, $SIFT3D_CUDA_EXACT)
+    // The launches of one detect (everything behind the first blur, whose source is the caller's
+    // image) as a CUDA graph: captured the second time a detect runs with the same geometry,
+    // units, thresholds and arithmetic mode -- the reference's own "re-plan only if the
+    // dimensions changed" point (sift.c:651-656) -- and replayed from then on.
+    bool use_graph = true;              // $SIFT3D_CUDA_NO_GRAPH switches it off
+    cudaGraphExec_t graph_exec = nullptr;
+    double graph_key[12] = {};
+    int graph_key_runs = 0;             // eager runs seen with graph_key
+    uint64_t graph_launches = 0;        // kernel launches inside the graph
+    uint64_t plan_gen = 0;              // bumped whenever device buffers may have moved
     DevBuf orient_plan;                 // OrientPlan on the device
     DevBuf orient_tab, orient_ntab;     // orientation window tables (OrientEntry) and their sizes
     double orient_key[11] = {};         // geometry the tables were built for
     bool orient_tab_ok = false;
     const OrientEntry *orient_tab_ptr[SIFT3D_CUDA_MAX_OCTAVES][SIFT3D_CUDA_MAX_FILTERS] = {};
     OrientPlan *h_plan = nullptr;       // pinned staging copy
+    OrientPlan h_plan_dev;              // what the device copy holds (valid if plan_uploaded)
+    bool plan_uploaded = false;
+    uint64_t plan_uploaded_gen = 0;
     DevBuf work;                        // work counter of the persistent orientation kernel
     DevBuf taps;                        // (1 + filters) * SIFT3D_CUDA_MAX_TAPS floats
     int base_octave = 0;                // octave number of this context's octave 0
@@ -152,6 +165,7 @@ sift3d_cuda_ctx *sift3d_cuda_ctx_create(int device) {
     }
     for (int i = 0; i < EV_COUNT; i++) cudaEventCreate(&ctx->ev[i]);
     ctx->serial = getenv("SIFT3D_CUDA_SERIAL") != nullptr;
+    ctx->use_graph = getenv("SIFT3D_CUDA_NO_GRAPH") == nullptr;
     {
         const char *e = getenv("SIFT3D_CUDA_EXACT");
         ctx->exact = e != nullptr && atoi(e) != 0;
@@ -176,6 +190,8 @@ void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
+    ctx->graph_exec = nullptr;
     ctx->pyr.release();
     ctx->input.release();
     ctx->tmp_a.release();
@@ -237,6 +253,7 @@ static void detect_timings(sift3d_cuda_ctx *ctx);
 
 static int plan_candidates(sift3d_cuda_ctx *ctx) {
     const int noct = ctx->desc.num_octaves;
+    ctx->plan_gen++;  // buffers may move: a captured graph holds their addresses
     ctx->cand_base.assign(noct, 0);
     ctx->cand_cap.assign(noct, 0);
     size_t cand_total = 0;
@@ -547,7 +564,20 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
                 H.ntab = nullptr;
             }
         }
-        S3D_CK(cudaMemcpyAsync(ctx->orient_plan.p, &H, sizeof(H), cudaMemcpyHostToDevice, st));
+        // The plan changes only with the geometry, the units or the tables: it is uploaded
+        // when it differs from the device copy. (Every detect used to upload it; a host-to-device
+        // copy queues on the copy engine BEHIND an image upload in flight for the next volume --
+        // sift3d_cuda_upload_begin -- and held the whole detect back for the length of that
+        // upload, 1.2 ms for 64 MiB.)
+        if (!ctx->plan_uploaded || ctx->plan_uploaded_gen != ctx->plan_gen ||
+            memcmp(&H, &ctx->h_plan_dev, sizeof(H)) != 0) {
+            S3D_CK(cudaMemcpyAsync(ctx->orient_plan.p, &H, sizeof(H), cudaMemcpyHostToDevice, st));
+            // (H is the pinned staging copy: it must not change before the copy has run)
+            S3D_CK(cudaStreamSynchronize(st));
+            memcpy(&ctx->h_plan_dev, &H, sizeof(H));
+            ctx->plan_uploaded = true;
+            ctx->plan_uploaded_gen = ctx->plan_gen;
+        }
     }
     S3D_CK(cudaEventRecord(ctx->ev[EV_SCALE], st));
 
@@ -669,10 +699,40 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     // (level s needs G(s-1) .. G(s+2)): scanned while octave 0 waits for octave 1's seed
     // chain, instead of on the critical path after the last blur.
     const int early_levels = (!slab && noct > 1) ? (ds_level - 1 > 0 ? (ds_level - 1 < kp ? ds_level - 1 : kp) : 0) : 0;
+    // ---- CUDA graph of everything behind the first blur (see the context's graph fields)
+    static const int reserve_env = getenv("SIFT3D_CUDA_RESERVE") ? atoi(getenv("SIFT3D_CUDA_RESERVE")) : 14;
+    static const int reserve_first = getenv("SIFT3D_CUDA_RESERVE_FIRST") ? atoi(getenv("SIFT3D_CUDA_RESERVE_FIRST")) : 40;
+    const bool graph_eligible = ctx->use_graph && !slab && !from_seed && !serial && !ctx->profiling && attempt == 0;
+    bool replay = false, capturing = false;
+    if (graph_eligible) {
+        const double key[12] = {(double) ctx->plan_gen, units[0], units[1], units[2], peak_thresh, corner_thresh,
+                                ctx->exact ? 1.0 : 0.0, (double) ctx->base_octave, ctx->orient_tab_ok ? 1.0 : 0.0,
+                                (double) (uintptr_t) ctx->orient_tab.p, (double) reserve_env, (double) reserve_first};
+        if (memcmp(key, ctx->graph_key, sizeof(key)) != 0) {
+            if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
+            ctx->graph_exec = nullptr;
+            memcpy(ctx->graph_key, key, sizeof(key));
+            ctx->graph_key_runs = 0;
+        }
+        replay = ctx->graph_exec != nullptr;
+        // the first run with a key is eager (one-time kernel attribute set-up happens there)
+        capturing = !replay && ctx->graph_key_runs >= 1;
+        ctx->graph_key_runs++;
+    }
+    // timing marks: inside a capture they become event-record nodes of the graph
+    auto mark = [&](cudaEvent_t ev) -> int {
+        if (capturing) S3D_CK(cudaEventRecordWithFlags(ev, st, cudaEventRecordExternal));
+        else S3D_CK(cudaEventRecord(ev, st));
+        return 0;
+    };
+    // the first blur reads the caller's image: always launched directly
+    if (!from_seed && run_level(0, -1)) return -1;
+
+    auto body = [&]() -> int {
     // Phase A, the critical chain: every octave up to the level that seeds the next one.
     for (int o = 0; o < noct; o++) {
         if (o > 0 && !serial) S3D_CK(cudaStreamWaitEvent(stream_of(o), ctx->ev_seed[o - 1], 0));
-        for (int s = (o == 0 && !from_seed ? -1 : 0); s <= ds_level && s < nlev - 1; s++)
+        for (int s = 0; s <= ds_level && s < nlev - 1; s++)
             if (run_level(o, s)) return -1;
         if (o == 0 && early_levels > 0 && run_extrema(0, 0, early_levels)) return -1;
     }
@@ -689,8 +749,6 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     }
     // Octave 0's remaining levels share the device with the other octaves' streams: leave
     // them some SMs (see set_fused_sm_reserve).
-    static const int reserve_env = getenv("SIFT3D_CUDA_RESERVE") ? atoi(getenv("SIFT3D_CUDA_RESERVE")) : 14;
-    static const int reserve_first = getenv("SIFT3D_CUDA_RESERVE_FIRST") ? atoi(getenv("SIFT3D_CUDA_RESERVE_FIRST")) : 40;
     if (noct > 1 && !serial) set_fused_sm_reserve(reserve_env);
     // The bulk levels of octave o >= 1 are not on the seed chain; held back until the chain is
     // `bulk_wait` octaves further on they do not take the reserved SMs from it.
@@ -698,7 +756,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     const int last_seed_ev = (tiny_from >= 0 ? tiny_from : noct_plan) - 1 < noct - 2
                                  ? (tiny_from >= 0 ? tiny_from : noct_plan) - 1 : noct - 2;
     for (int o = 0; o < noct; o++) {
-        const int sfirst = (o == 0 && !from_seed) ? -1 : 0;
+        const int sfirst = 0;
         int rc = 0;
         if (o >= 1 && bulk_wait > 0 && !serial && !slab && !(tiny_from >= 0 && o >= tiny_from)) {
             const int we = o + bulk_wait < last_seed_ev ? o + bulk_wait : last_seed_ev;
@@ -713,7 +771,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         }
         if (o == 0) set_fused_sm_reserve(0);
         if (rc) return -1;
-        if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_PYR], st));
+        if (o == 0 && mark(ctx->ev[EV_PYR])) return -1;
     }
     if (slab) {  // DoG maxima are over whole levels
         if (host_sync()) return -1;
@@ -729,12 +787,12 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         // the device and results go to the octave's own region, so no octave waits for another.
         // (At 256^3 three quarters of the candidates are in octaves >= 1, which finish long
         // before octave 0 -- orienting everything after the last octave cost 0.2 ms.)
-        if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_EXTREMA], st));
+        if (o == 0 && mark(ctx->ev[EV_EXTREMA])) return -1;
         if (launch_order_all(so, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
                              ctx->cand_base.data(), ctx->cand_cap.data(), noct,
                              (const int *) ctx->counts.p, &ctx->launches, o, o + 1))
             return -1;
-        if (o == 0) S3D_CK(cudaEventRecord(ctx->ev[EV_ORDER], st));
+        if (o == 0 && mark(ctx->ev[EV_ORDER])) return -1;
         if (launch_orient_all(so, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
                               (const int *) ctx->counts.p, (int *) ctx->work.p + o, corner_thresh,
                               ctx->kps_dev(), &ctx->launches, o, o + 1,
@@ -746,8 +804,52 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         for (int o = 1; o < noct; o++) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_done[o], 0));
     S3D_CK(cudaMemcpyAsync(ctx->h_counts, ctx->counts.p, sizeof(int) * noct,
                            cudaMemcpyDeviceToHost, st));
-    S3D_CK(cudaEventRecord(ctx->ev[EV_ORIENT], st));
-    if (ctx->kps_host) S3D_CK(cudaEventRecord(ctx->ev[EV_D2H], st));  // results are already in host memory
+    if (mark(ctx->ev[EV_ORIENT])) return -1;
+    if (ctx->kps_host && mark(ctx->ev[EV_D2H])) return -1;  // results are already in host memory
+    return 0;
+    };  // body
+
+    if (replay) {
+        S3D_CK(cudaGraphLaunch(ctx->graph_exec, st));
+        ctx->launches += ctx->graph_launches;
+    } else if (capturing) {
+        const uint64_t l0 = ctx->launches;
+        S3D_CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed));
+        const int rc = body();
+        cudaGraph_t g = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(st, &g);
+        set_fused_sm_reserve(0);
+        if (rc != 0 || e != cudaSuccess || g == nullptr) {
+            S3D_ERR("sift3d_cuda_detect: graph capture failed (%s); running without a graph\n",
+                    cudaGetErrorString(e));
+            cudaGetLastError();
+            if (g) cudaGraphDestroy(g);
+            ctx->use_graph = false;
+            ctx->launches = l0;
+            capturing = false;
+            if (body()) return -1;
+        } else {
+            cudaGraphExec_t ge = nullptr;
+            // (the octave streams' priorities are part of the schedule: keep them per node)
+            const cudaError_t ei = cudaGraphInstantiateWithFlags(&ge, g, cudaGraphInstantiateFlagUseNodePriority);
+            cudaGraphDestroy(g);
+            if (ei != cudaSuccess || ge == nullptr) {
+                S3D_ERR("sift3d_cuda_detect: cudaGraphInstantiate failed (%s); running without a graph\n",
+                        cudaGetErrorString(ei));
+                cudaGetLastError();
+                ctx->use_graph = false;
+                ctx->launches = l0;
+                capturing = false;
+                if (body()) return -1;
+            } else {
+                ctx->graph_exec = ge;
+                ctx->graph_launches = ctx->launches - l0;
+                S3D_CK(cudaGraphLaunch(ge, st));
+            }
+        }
+    } else if (body()) {
+        return -1;
+    }
     S3D_CK(cudaStreamSynchronize(st));
     int total = 0;
     bool overflow = false;
