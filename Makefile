@@ -38,7 +38,7 @@ $(LIBDIR)/libsift3d_cuda.so: $(CU_OBJS)
 
 $(LIBDIR)/libsift3D.so: sift3d_b200/host/sift3d_host.c sift3d_b200/host/nifti1.c sift3d_b200/host/nifti1.h include/sift3d.h include/sift3d_cuda.h $(LIBDIR)/libsift3d_cuda.so
 	$(HOSTCC) -O2 -ffp-contract=off -fno-fast-math -fPIC -shared -fvisibility=hidden -Wall \
-	    -o $@ sift3d_b200/host/sift3d_host.c sift3d_b200/host/nifti1.c -L$(LIBDIR) -lsift3d_cuda -lz -lm \
+	    -o $@ sift3d_b200/host/sift3d_host.c sift3d_b200/host/nifti1.c -L$(LIBDIR) -lsift3d_cuda -lz -lm -lpthread \
 	    -Wl,-rpath,'$$ORIGIN'
 
 $(LIBDIR)/libsift3d_synth.so: sift3d_b200/synth.c

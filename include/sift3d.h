@@ -177,6 +177,30 @@ SIFT3D_EXPORT int sift3d_keypoint_store_get(const sift3d_keypoint_store *, int i
                                             int *s, double xyz[3], double *sd, float *strength,
                                             float R[9]);
 
+/* Batch: detect + describe `num` volumes over `num_det` detectors, each
+ * bound to a device of its own (sift3d_make_detector_on_device). Volume i is processed by
+ * detector i % num_det exactly as sift3d_detect_keypoints + sift3d_extract_descriptors
+ * (sift.h:92-111) would; every detector is driven by a host thread of its own and the upload of
+ * its next volume overlaps the kernels of the current one. descs may be NULL (detection only)
+ * and so may single entries of it; a volume without keypoints leaves its descriptor store
+ * empty. Image buffers must stay unchanged during the call. Returns SIFT3D_FAILURE if any
+ * volume failed. */
+SIFT3D_EXPORT int sift3d_detect_describe_batch(sift3d_detector *const *dets, int num_det,
+                                               sift3d_image *const *ims,
+                                               sift3d_keypoint_store *const *kps,
+                                               sift3d_descriptor_store *const *descs, int num);
+
+/* Upstream-cased aliases (bbrister/SIFT3D spells the path SIFT3D_detect_keypoints /
+ * SIFT3D_extract_descriptors on Image / Keypoint_store / SIFT3D_Descriptor_store; the fork
+ * mounted as the reference renamed them, sift.h:92-111). Same argument order and return
+ * codes; the types are the fork's opaque handles under the upstream names. */
+typedef sift3d_detector SIFT3D;
+typedef sift3d_image Image;
+typedef sift3d_keypoint_store Keypoint_store;
+typedef sift3d_descriptor_store SIFT3D_Descriptor_store;
+SIFT3D_EXPORT int SIFT3D_detect_keypoints(SIFT3D *, const Image *, Keypoint_store *);
+SIFT3D_EXPORT int SIFT3D_extract_descriptors(SIFT3D *, const Keypoint_store *, SIFT3D_Descriptor_store *);
+
 /* The inner CUDA context of a detector (include/sift3d_cuda.h), for timing and
  * pyramid inspection by tests and benchmarks. */
 SIFT3D_EXPORT void *sift3d_detector_cuda_ctx(sift3d_detector *);

@@ -16,6 +16,7 @@ from .api import (  # noqa: F401
     KeypointStore,
     Sift3DError,
     cuda_device_count,
+    detect_describe_batch,
     lib,
     lib_paths,
     libcuda,
@@ -24,5 +25,5 @@ from .synth import synth_volume, workload  # noqa: F401
 
 __all__ = [
     "CudaKeypoint", "CudaTimings", "DescriptorStore", "Detector", "Image", "KeypointStore",
-    "Sift3DError", "cuda_device_count", "lib", "libcuda", "lib_paths", "synth_volume", "workload",
+    "Sift3DError", "cuda_device_count", "detect_describe_batch", "lib", "libcuda", "lib_paths", "synth_volume", "workload",
 ]

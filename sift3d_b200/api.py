@@ -181,6 +181,10 @@ def lib():
     L.sift3d_detector_set_num_kp_levels.argtypes = [vp, C.c_uint]
     L.sift3d_detect_keypoints.argtypes = [vp, vp, vp]
     L.sift3d_extract_descriptors.argtypes = [vp, vp, vp]
+    L.SIFT3D_detect_keypoints.argtypes = [vp, vp, vp]
+    L.SIFT3D_extract_descriptors.argtypes = [vp, vp, vp]
+    L.sift3d_detect_describe_batch.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(vp), C.POINTER(vp),
+                                               C.POINTER(vp), C.c_int]
     L.sift3d_keypoint_store_to_mat_rm.argtypes = [vp, vp]
     L.sift3d_descriptor_store_to_mat_rm.argtypes = [vp, vp]
     L.sift3d_keypoint_store_save.argtypes = [C.c_char_p, vp]
@@ -506,3 +510,20 @@ class Detector:
             self.close()
         except Exception:
             pass
+
+
+def detect_describe_batch(detectors, images, describe=True):
+    """sift3d_detect_describe_batch: volume i on detector i % len(detectors), one host thread
+    per detector inside the C library. Returns (keypoint stores, descriptor stores)."""
+    L = lib()
+    n = len(images)
+    kps = [KeypointStore() for _ in range(n)]
+    dss = [DescriptorStore() for _ in range(n)] if describe else []
+    vp = C.c_void_p
+    a_det = (vp * len(detectors))(*[d.handle for d in detectors])
+    a_im = (vp * max(n, 1))(*[im.handle for im in images])
+    a_kp = (vp * max(n, 1))(*[k.handle for k in kps])
+    a_ds = (vp * max(n, 1))(*[d.handle for d in dss]) if describe else None
+    if L.sift3d_detect_describe_batch(a_det, len(detectors), a_im, a_kp, a_ds, n):
+        raise Sift3DError("sift3d_detect_describe_batch failed")
+    return kps, dss

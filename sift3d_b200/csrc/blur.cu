@@ -401,6 +401,8 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
 static EncodeTiledFn encode_tiled_fn() {
     static EncodeTiledFn fn = nullptr;
     static bool tried = false;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
     if (!tried) {
         tried = true;
         void *p = nullptr;
@@ -539,10 +541,12 @@ static int launch_fused_t(cudaStream_t st, const FusedParams &P) {
             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return 1;
     static PerDeviceOnce attr_once;
-    if (attr_once.first()) {
-        S3D_CK(cudaFuncSetAttribute(blur_zmarch_kernel<HW, R, NT, EXACT>,
+    if (attr_once.run([&]() -> int {
+            S3D_CK(cudaFuncSetAttribute(blur_zmarch_kernel<HW, R, NT, EXACT>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int) SMEM));
-    }
+            return 0;
+        }))
+        return -1;
     const int tiles = ((P.nx + kFTX - 1) / kFTX) * ((P.ny + TY - 1) / TY);
     const int nzr = P.z1 - P.z0;
     // one wave of CTAs, but no CTA with less than ~8 outputs of one tile
@@ -622,10 +626,12 @@ static int launch_half_t(cudaStream_t st, const FusedParams &P, int nzc) {
             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return 1;
     static PerDeviceOnce attr_once;
-    if (attr_once.first()) {
-        S3D_CK(cudaFuncSetAttribute(blur_fused_half_kernel<HW, TY>,
+    if (attr_once.run([&]() -> int {
+            S3D_CK(cudaFuncSetAttribute(blur_fused_half_kernel<HW, TY>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int) SMEM));
-    }
+            return 0;
+        }))
+        return -1;
     dim3 grid((unsigned) ((P.nx + kFTX - 1) / kFTX), (unsigned) ((P.ny + TY - 1) / TY), (unsigned) nzc);
     blur_fused_half_kernel<HW, TY><<<grid, 8 * TY, SMEM, st>>>(tmap, P);
     S3D_CK(cudaGetLastError());
@@ -932,10 +938,12 @@ tiny_octaves_kernel(const TinyChainParams P) {
 int launch_tiny_octaves(cudaStream_t st, const TinyChainParams &P, uint64_t *launches) {
     const size_t dyn = (size_t) (4 * kTinyMaxVox + kTinyMaxVox / 8 + 64) * sizeof(float);
     static PerDeviceOnce attr_once;
-    if (attr_once.first()) {
-        S3D_CK(cudaFuncSetAttribute(tiny_octaves_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if (attr_once.run([&]() -> int {
+            S3D_CK(cudaFuncSetAttribute(tiny_octaves_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int) dyn));
-    }
+            return 0;
+        }))
+        return -1;
     tiny_octaves_kernel<<<1, kTinyThreads, dyn, st>>>(P);
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());

@@ -5,6 +5,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <mutex>
+
 #include "../../include/sift3d_cuda.h"
 
 #define S3D_ERR(...) fprintf(stderr, __VA_ARGS__)
@@ -37,13 +39,20 @@ struct Level {
 // PER DEVICE (a process may hold detectors on several GPUs, sift3d_detector_set_device).
 constexpr int kMaxDevices = 64;
 struct PerDeviceOnce {
+    std::mutex mu;
     bool done[kMaxDevices] = {};
-    bool first() {  // true the first time it is called on the current device
+    // Runs f() (0 = success) the first time it is called on the current device; a second host
+    // thread driving the same device waits until the set-up has been made (it would otherwise
+    // launch before the kernel's shared-memory attribute is in place).
+    template <typename F>
+    int run(F f) {
         int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return true;
-        if (done[dev]) return false;
-        done[dev] = true;
-        return true;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return f();
+        std::lock_guard<std::mutex> lock(mu);
+        if (done[dev]) return 0;
+        const int rc = f();
+        if (rc == 0) done[dev] = true;
+        return rc;
     }
 };
 

@@ -487,7 +487,7 @@ __constant__ unsigned char c_cell_order[64];
 
 static int upload_cell_order() {
     static PerDeviceOnce once;
-    if (!once.first()) return 0;
+    return once.run([&]() -> int {
     unsigned char order[64];
     int key[64];
     for (int c = 0; c < 64; c++) {
@@ -505,6 +505,7 @@ static int upload_cell_order() {
             }
     S3D_CK(cudaMemcpyToSymbol(c_cell_order, order, sizeof(order)));
     return 0;
+    });
 }
 
 __global__ void __launch_bounds__(kDescThreads)
@@ -974,11 +975,13 @@ int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_ro
     if (!force_rows) {
         const size_t dyn4 = (size_t) (kDescThreads / 32) * kCellBins * 32 * sizeof(float);
         static PerDeviceOnce attr4;
-        if (attr4.first()) {
-            if (upload_cell_order()) return -1;
-            S3D_CK(cudaFuncSetAttribute(descriptor_cell_kernel,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int) dyn4));
-        }
+        if (attr4.run([&]() -> int {
+                if (upload_cell_order()) return -1;
+                S3D_CK(cudaFuncSetAttribute(descriptor_cell_kernel,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int) dyn4));
+                return 0;
+            }))
+            return -1;
         descriptor_cell_kernel<<<(unsigned) n, kDescThreads, dyn4, st>>>(d_jobs, n, d_desc);
         if (launches) *launches += 1;
         S3D_CK(cudaGetLastError());

@@ -1049,3 +1049,112 @@ int sift3d_extract_descriptors(sift3d_detector *const d, const sift3d_keypoint_s
     free(keys);
     return SIFT3D_SUCCESS;
 }
+
+/* ---- batch: many volumes over several detectors (devices) ------------------------------
+ * Extension; the per-volume work is exactly sift3d_detect_keypoints
+ * + sift3d_extract_descriptors (sift.h:92-111), so every result equals the one-volume calls.
+ * Volume i goes to detector i % num_det; every detector is driven by a host thread of its own
+ * (one detector = one device + one stream), and the upload of a detector's next volume
+ * (sift3d_image_prefetch) is started between detect and extract of the current one, where it
+ * hides under the descriptor kernel. A volume without keypoints gets an empty descriptor
+ * store (the one-volume extract call fails on an empty store, sift.c:1178-1182). */
+#include <pthread.h>
+
+typedef struct {
+    sift3d_detector *det;
+    sift3d_image *const *ims;
+    sift3d_keypoint_store *const *kps;
+    sift3d_descriptor_store *const *descs;
+    int first, stride, num;
+    int status;
+} batch_job;
+
+static void *batch_worker(void *arg) {
+    batch_job *const j = (batch_job *) arg;
+    const int dev = sift3d_cuda_ctx_device(j->det->ctx);
+    int i;
+    j->status = SIFT3D_SUCCESS;
+    if (j->first < j->num)
+        sift3d_image_prefetch(j->ims[j->first], dev);
+    for (i = j->first; i < j->num; i += j->stride) {
+        if (sift3d_detect_keypoints(j->det, j->ims[i], j->kps[i])) {
+            j->status = SIFT3D_FAILURE;
+            break;
+        }
+        if (i + j->stride < j->num)
+            sift3d_image_prefetch(j->ims[i + j->stride], dev);
+        if (j->descs == NULL || j->descs[i] == NULL)
+            continue;
+        if (j->kps[i]->num == 0) {
+            j->descs[i]->num = 0;
+            continue;
+        }
+        if (sift3d_extract_descriptors(j->det, j->kps[i], j->descs[i])) {
+            j->status = SIFT3D_FAILURE;
+            break;
+        }
+    }
+    return NULL;
+}
+
+int sift3d_detect_describe_batch(sift3d_detector *const *dets, int num_det,
+                                 sift3d_image *const *ims, sift3d_keypoint_store *const *kps,
+                                 sift3d_descriptor_store *const *descs, int num) {
+    pthread_t *th;
+    batch_job *jobs;
+    int d, ret = SIFT3D_SUCCESS;
+    if (dets == NULL || ims == NULL || kps == NULL || num_det < 1 || num < 0)
+        return SIFT3D_FAILURE;
+    for (d = 0; d < num_det; d++)
+        if (dets[d] == NULL || dets[d]->ctx == NULL)
+            return SIFT3D_FAILURE;
+    for (d = 0; d < num; d++)
+        if (ims[d] == NULL || kps[d] == NULL)
+            return SIFT3D_FAILURE;
+    if (num == 0)
+        return SIFT3D_SUCCESS;
+    if (num_det > num)
+        num_det = num;
+    th = (pthread_t *) calloc((size_t) num_det, sizeof(*th));
+    jobs = (batch_job *) calloc((size_t) num_det, sizeof(*jobs));
+    if (th == NULL || jobs == NULL) {
+        free(th);
+        free(jobs);
+        return SIFT3D_FAILURE;
+    }
+    for (d = 0; d < num_det; d++) {
+        jobs[d].det = dets[d];
+        jobs[d].ims = ims;
+        jobs[d].kps = kps;
+        jobs[d].descs = descs;
+        jobs[d].first = d;
+        jobs[d].stride = num_det;
+        jobs[d].num = num;
+        jobs[d].status = SIFT3D_FAILURE;
+    }
+    /* detector 0 runs on the calling thread */
+    for (d = 1; d < num_det; d++)
+        if (pthread_create(&th[d], NULL, batch_worker, &jobs[d])) {
+            jobs[d].stride = 0; /* not started */
+            ret = SIFT3D_FAILURE;
+        }
+    batch_worker(&jobs[0]);
+    for (d = 1; d < num_det; d++)
+        if (jobs[d].stride != 0)
+            pthread_join(th[d], NULL);
+    for (d = 0; d < num_det; d++)
+        if (jobs[d].status != SIFT3D_SUCCESS)
+            ret = SIFT3D_FAILURE;
+    free(th);
+    free(jobs);
+    return ret;
+}
+
+/* ---- upstream-cased aliases (see include/sift3d.h) -------------------------------------- */
+int SIFT3D_detect_keypoints(SIFT3D *d, const Image *im, Keypoint_store *kp) {
+    return sift3d_detect_keypoints(d, im, kp);
+}
+
+int SIFT3D_extract_descriptors(SIFT3D *d, const Keypoint_store *kp, SIFT3D_Descriptor_store *desc) {
+    return sift3d_extract_descriptors(d, kp, desc);
+}
