@@ -20,7 +20,7 @@ NVFLAGS_descriptor := --fmad=true
 LIBDIR  := sift3d_b200/lib
 CSRC    := sift3d_b200/csrc
 CU_SRCS := $(CSRC)/sift3d_cuda.cu $(CSRC)/blur.cu $(CSRC)/extrema.cu $(CSRC)/orient.cu \
-           $(CSRC)/descriptor.cu
+           $(CSRC)/descriptor.cu $(CSRC)/multi.cu
 CU_OBJS := $(patsubst $(CSRC)/%.cu,build/%.o,$(CU_SRCS))
 CU_HDRS := $(wildcard $(CSRC)/*.cuh) include/sift3d_cuda.h
 
@@ -34,7 +34,7 @@ build/%.o: $(CSRC)/%.cu $(CU_HDRS)
 
 $(LIBDIR)/libsift3d_cuda.so: $(CU_OBJS)
 	@mkdir -p $(LIBDIR)
-	$(NVCC) $(ARCH) -shared -ccbin $(HOSTCXX) -o $@ $(CU_OBJS)
+	$(NVCC) $(ARCH) -shared -ccbin $(HOSTCXX) -o $@ $(CU_OBJS) -lpthread
 
 $(LIBDIR)/libsift3D.so: sift3d_b200/host/sift3d_host.c sift3d_b200/host/nifti1.c sift3d_b200/host/nifti1.h include/sift3d.h include/sift3d_cuda.h $(LIBDIR)/libsift3d_cuda.so
 	$(HOSTCC) -O2 -ffp-contract=off -fno-fast-math -fPIC -shared -fvisibility=hidden -Wall \

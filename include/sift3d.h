@@ -190,6 +190,23 @@ SIFT3D_EXPORT int sift3d_detect_describe_batch(sift3d_detector *const *dets, int
                                                sift3d_keypoint_store *const *kps,
                                                sift3d_descriptor_store *const *descs, int num);
 
+/* One tall volume over several devices: z-slabs of the volume, one
+ * per device, with halo exchange over NVLink between the slabs -- the same result as
+ * sift3d_detect_keypoints + sift3d_extract_descriptors on one device (the octave loops of
+ * sift.c:662-871, 1109-1167, 1442-1536 decomposed over z). `sharded_octaves` octaves run on
+ * the slabs, the smaller ones on devices[0]. desc may be NULL (detection only). The detector
+ * only lends its parameters; its own pyramid is not touched. */
+SIFT3D_EXPORT int sift3d_detect_describe_sharded(sift3d_detector *, const sift3d_image *,
+                                                 const int *devices, int num_devices,
+                                                 int sharded_octaves, sift3d_keypoint_store *,
+                                                 sift3d_descriptor_store *);
+/* total, slabs, unsharded octaves, slowest detect, slowest describe (ms); halo MiB moved */
+SIFT3D_EXPORT int sift3d_sharded_timings(sift3d_detector *, float out[6]);
+/* The layout rule (host only): owned [g0, g1) / held [a0, a1) planes per device; returns the
+ * halo in planes of octave 0, or -1 if nz cannot be split into num slabs aligned to 2^K. */
+SIFT3D_EXPORT int sift3d_sharded_layout(int nz, int num, int K, int window_planes, int max_half_width,
+                                        double uz, int *g0, int *g1, int *a0, int *a1);
+
 /* Upstream-cased aliases (bbrister/SIFT3D spells the path SIFT3D_detect_keypoints /
  * SIFT3D_extract_descriptors on Image / Keypoint_store / SIFT3D_Descriptor_store; the fork
  * mounted as the reference renamed them, sift.h:92-111). Same argument order and return

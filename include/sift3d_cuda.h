@@ -144,6 +144,13 @@ typedef struct {
      * with the context's stream drained. */
     int (*exchange)(void *user, int o, int s, float *d_level, int nx, int ny, int nz,
                     int own0, int own1);
+    /* != 0: the callbacks only ENQUEUE work on the context's stream (sift3d_cuda_ctx_stream),
+     * e.g. peer copies behind event waits: detect does not drain the stream before calling
+     * them (sift3d_cuda_multi, below). 0: they are called with the stream drained. */
+    int in_stream;
+    /* in_stream only: planes of the input image around the owned range that the first blur
+     * reads; only those are uploaded from a host image (0: the whole slab array) */
+    int input_reach;
 } sift3d_cuda_slab_callbacks;
 
 /* As sift3d_cuda_detect for a z-slab. Candidates are those of the owned planes, with
@@ -154,6 +161,9 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_detect_slab(sift3d_cuda_ctx *ctx, const float
                                                const sift3d_cuda_slab_desc *slab,
                                                const sift3d_cuda_slab_callbacks *cb,
                                                int *num_candidates);
+
+/* The context's stream as a plain pointer (a cudaStream_t), for in-stream slab callbacks. */
+SIFT3D_CUDA_EXPORT void *sift3d_cuda_ctx_stream(sift3d_cuda_ctx *ctx);
 
 /* As sift3d_cuda_detect, but `seed` already is level -1 of this context's octave 0 (the
  * 2x decimation sift.c:699-705 made in a larger pyramid): no im_scale, no first blur. */
@@ -169,6 +179,49 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_set_base_octave(sift3d_cuda_ctx *ctx, int bas
 /* Device address of level (o, s), s = -1 .. num_kp_levels + 1 (for the exchange
  * callbacks and for feeding a seed to another context). NULL if out of range. */
 SIFT3D_CUDA_EXPORT float *sift3d_cuda_level_ptr(sift3d_cuda_ctx *ctx, int o, int s);
+
+/* ---- one volume over several GPUs of ONE process (multi.cu) ---------------------------
+ * The slab decomposition above with the exchange done by the library itself: one context and
+ * one host thread per device, halo planes moved by peer copies (NVLink) that are enqueued
+ * behind events -- no host round trip per level -- and only as many planes as the consumers of
+ * a level read. The host library (libsift3D.so: sift3d_detect_describe_sharded) computes the
+ * layout and the per-slab plans and merges the per-device results. */
+#define SIFT3D_CUDA_MULTI_MAX_DEVICES 16
+typedef struct sift3d_cuda_multi sift3d_cuda_multi;
+typedef struct {
+    int num_devices;
+    int devices[SIFT3D_CUDA_MULTI_MAX_DEVICES];
+    int nx, ny, nz;                 /* the whole volume */
+    double units[3];
+    int sharded_octaves;            /* K: octaves 0 .. K-1 run on the slabs */
+    /* planes of octave 0: device r owns [g0, g1) (multiples of 2^K) and holds [a0, a1) */
+    int g0[SIFT3D_CUDA_MULTI_MAX_DEVICES], g1[SIFT3D_CUDA_MULTI_MAX_DEVICES];
+    int a0[SIFT3D_CUDA_MULTI_MAX_DEVICES], a1[SIFT3D_CUDA_MULTI_MAX_DEVICES];
+    /* [o]: planes of octave o (each side) that the orientation / descriptor windows of the
+     * keypoint levels reach (sift.c:936, 1453-1461) */
+    int window_planes[SIFT3D_CUDA_MAX_OCTAVES];
+} sift3d_cuda_multi_desc;
+typedef struct {
+    float total_ms, slabs_ms, tail_ms;      /* host wall clock of the last run */
+    float max_detect_ms, max_describe_ms;   /* slowest slab */
+    float exchanged_mbytes;                 /* halo planes moved between devices */
+} sift3d_cuda_multi_timings;
+/* slab_plans[r]: plan of device r's array (nx, ny, a1-a0; K or K+1 octaves); tail_plan: the
+ * octaves >= K of the whole volume (NULL if there are none). */
+SIFT3D_CUDA_EXPORT sift3d_cuda_multi *sift3d_cuda_multi_create(const sift3d_cuda_multi_desc *desc,
+                                                               const sift3d_cuda_plan_desc *slab_plans,
+                                                               const sift3d_cuda_plan_desc *tail_plan);
+SIFT3D_CUDA_EXPORT void sift3d_cuda_multi_destroy(sift3d_cuda_multi *m);
+/* detect (+ describe) the whole volume `host_image` (nx*ny*nz floats, page-locked for speed) */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_multi_run(sift3d_cuda_multi *m, const float *host_image,
+                                             double peak_thresh, double corner_thresh, int describe);
+/* part = device index, or num_devices for the unsharded octaves: its candidates (volume
+ * coordinates, the part's scan order) and 768 floats per VALID candidate in that order.
+ * Returns the number of candidates; pointers valid until the next run. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_multi_results(sift3d_cuda_multi *m, int part,
+                                                 const sift3d_cuda_keypoint **cands,
+                                                 const float **descriptors);
+SIFT3D_CUDA_EXPORT int sift3d_cuda_multi_get_timings(sift3d_cuda_multi *m, sift3d_cuda_multi_timings *t);
 
 /* All candidates in the reference's scan order (o, s, z, y, x), each with its
  * orientation result (valid flag + R). out has room for max entries. */

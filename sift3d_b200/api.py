@@ -57,7 +57,8 @@ EXCHANGE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c
 
 
 class CudaSlabCallbacks(C.Structure):
-    _fields_ = [("user", C.c_void_p), ("reduce_max", REDUCE_MAX_FN), ("exchange", EXCHANGE_FN)]
+    _fields_ = [("user", C.c_void_p), ("reduce_max", REDUCE_MAX_FN), ("exchange", EXCHANGE_FN),
+                ("in_stream", C.c_int), ("input_reach", C.c_int)]
 
 
 class CudaKeypoint(C.Structure):
@@ -185,6 +186,9 @@ def lib():
     L.SIFT3D_extract_descriptors.argtypes = [vp, vp, vp]
     L.sift3d_detect_describe_batch.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(vp), C.POINTER(vp),
                                                C.POINTER(vp), C.c_int]
+    L.sift3d_detect_describe_sharded.argtypes = [vp, vp, C.POINTER(C.c_int), C.c_int, C.c_int, vp, vp]
+    L.sift3d_sharded_timings.argtypes = [vp, C.POINTER(C.c_float)]
+    L.sift3d_sharded_layout.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double] + [C.POINTER(C.c_int)] * 4
     L.sift3d_keypoint_store_to_mat_rm.argtypes = [vp, vp]
     L.sift3d_descriptor_store_to_mat_rm.argtypes = [vp, vp]
     L.sift3d_keypoint_store_save.argtypes = [C.c_char_p, vp]
@@ -463,6 +467,25 @@ class Detector:
         if self._C.sift3d_cuda_elapsed_ms(self.ctx, int(a), int(b), C.byref(ms)):
             raise Sift3DError("sift3d_cuda_elapsed_ms failed")
         return ms.value
+
+    def detect_describe_sharded(self, im, devices, sharded_octaves=2, describe=True):
+        """sift3d_detect_describe_sharded: z-slabs of one volume over `devices` (entries may
+        repeat: several slabs on one device). Returns (KeypointStore, DescriptorStore | None)."""
+        kp = KeypointStore()
+        ds = DescriptorStore() if describe else None
+        devs = (C.c_int * len(devices))(*[int(v) for v in devices])
+        if self._L.sift3d_detect_describe_sharded(self.handle, im.handle, devs, len(devices),
+                                                  int(sharded_octaves), kp.handle,
+                                                  ds.handle if ds is not None else None):
+            raise Sift3DError("sift3d_detect_describe_sharded failed")
+        return kp, ds
+
+    def sharded_timings(self) -> dict:
+        out = (C.c_float * 6)()
+        if self._L.sift3d_sharded_timings(self.handle, out):
+            raise Sift3DError("no sharded run on this detector")
+        return dict(zip(("total_ms", "slabs_ms", "tail_ms", "max_detect_ms", "max_describe_ms",
+                         "exchanged_mib"), [float(v) for v in out]))
 
     def set_exact(self, exact=True):
         """0-ULP blur arithmetic (True) or one FFMA per tap (False, the default unless

@@ -466,6 +466,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     auto zorg = [&](int o) { return slab ? slab->org[o] : 0; };
     // hand the stream to the caller's collective (host callbacks, so the stream is drained)
     auto host_sync = [&]() -> int {
+        if (cb != nullptr && cb->in_stream) return 0;  // the callbacks enqueue behind the stream
         S3D_CK(cudaStreamSynchronize(st));
         return 0;
     };
@@ -489,7 +490,17 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         S3D_CK(cudaMemcpyAsync(ctx->level(0, -1).d, image, n0 * sizeof(float),
                                image_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
     } else if (!image_on_device) {
-        S3D_CK(cudaMemcpyAsync(ctx->input.p, image, n0 * sizeof(float), cudaMemcpyHostToDevice, st));
+        size_t first = 0, count = n0;
+        if (slab && cb->in_stream && cb->input_reach > 0) {
+            // only the planes the first blur reads around the owned range
+            const size_t plane = (size_t) D.nx * D.ny;
+            const int p0 = slab->own0[0] - cb->input_reach > 0 ? slab->own0[0] - cb->input_reach : 0;
+            const int p1 = slab->own1[0] + cb->input_reach < D.nz ? slab->own1[0] + cb->input_reach : D.nz;
+            first = (size_t) p0 * plane;
+            count = (size_t) (p1 - p0) * plane;
+        }
+        S3D_CK(cudaMemcpyAsync((float *) ctx->input.p + first, image + first, count * sizeof(float),
+                               cudaMemcpyHostToDevice, st));
         d_in = (const float *) ctx->input.p;
     }
     S3D_CK(cudaEventRecord(ctx->ev[EV_H2D], st));
@@ -1302,6 +1313,8 @@ int sift3d_cuda_upload_wait(sift3d_cuda_ctx *ctx, sift3d_cuda_upload *up) {
 }
 
 int sift3d_cuda_ctx_device(sift3d_cuda_ctx *ctx) { return ctx ? ctx->device : -1; }
+
+void *sift3d_cuda_ctx_stream(sift3d_cuda_ctx *ctx) { return ctx ? (void *) ctx->stream : nullptr; }
 
 int sift3d_cuda_mark(sift3d_cuda_ctx *ctx, int slot) {
     if (!ctx || slot < 0 || slot >= 8) return -1;

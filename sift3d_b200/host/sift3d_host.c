@@ -92,6 +92,9 @@ struct _sift3d_detector {
     int have_gpyr;     /* a detect has completed (detector_has_gpyr, sift.c:1544-1549) */
     sift3d_cuda_keypoint *scratch;
     size_t scratch_cap;
+    /* one volume over several devices (sift3d_detect_describe_sharded): cached per geometry */
+    sift3d_cuda_multi *multi;
+    double multi_key[32];
 };
 
 /* ---- matrices (imutil.c:134-290, 1676-1710) ------------------------------------------ */
@@ -578,6 +581,7 @@ void sift3d_free_detector(sift3d_detector *d) {
     if (d == NULL)
         return;
     sift3d_cuda_host_free(d->scratch);
+    sift3d_cuda_multi_destroy(d->multi);
     sift3d_cuda_ctx_destroy(d->ctx);
     free(d);
 }
@@ -1157,4 +1161,237 @@ int SIFT3D_detect_keypoints(SIFT3D *d, const Image *im, Keypoint_store *kp) {
 
 int SIFT3D_extract_descriptors(SIFT3D *d, const Keypoint_store *kp, SIFT3D_Descriptor_store *desc) {
     return sift3d_extract_descriptors(d, kp, desc);
+}
+
+/* ---- one tall volume over several devices (z-slabs) --------------------------------------
+ * Extension: the same path as sift3d_detect_keypoints +
+ * sift3d_extract_descriptors (sift.h:92-111), decomposed over z by libsift3d_cuda.so's
+ * sift3d_cuda_multi (multi.cu). This side computes the layout, designs the per-slab plans with
+ * the detector's parameters and merges the per-device results in the reference's scan order
+ * (o, s, z, y, x) = (o, s, device, local order), compacting the survivors like
+ * assign_orientations (sift.c:1148-1166), strength quirk included. */
+#define DESC_SIG_FCTR 7.071067812 /* sift.c:43 */
+#define DESC_RAD_FCTR 2.0         /* sift.c:44 */
+
+/* Layout of `nz` planes over `num` devices: owned ranges on multiples of 2^K, each with `halo`
+ * planes on its cut faces. Returns the halo, or -1 if the volume cannot be split that way. */
+int sift3d_sharded_layout(int nz, int num, int K, int window_planes, int max_half_width, double uz,
+                          int *g0, int *g1, int *a0, int *a1) {
+    const int align = 1 << K;
+    const int nblk = nz / align;
+    int reach = (int) ceil((double) max_half_width / uz) + 2, halo, r;
+    if (reach < window_planes)
+        reach = window_planes;
+    halo = (reach << (K - 1)) + align - 1;
+    halo -= halo % align;
+    if (num < 1 || K < 1 || nblk < num)
+        return -1;
+    for (r = 0; r < num; r++) {
+        g0[r] = align * (int) (((long) r * nblk) / num);
+        g1[r] = r + 1 < num ? align * (int) (((long) (r + 1) * nblk) / num) : nz;
+        a0[r] = g0[r] - halo > 0 ? g0[r] - halo : 0;
+        a1[r] = g1[r] + halo < nz ? g1[r] + halo : nz;
+    }
+    return halo;
+}
+
+int sift3d_detect_describe_sharded(sift3d_detector *const d, const sift3d_image *const im,
+                                   const int *devices, int num_devices, int sharded_octaves,
+                                   sift3d_keypoint_store *const kp,
+                                   sift3d_descriptor_store *const desc) {
+    sift3d_cuda_multi_desc M;
+    double key[32];
+    int total, K, tail_octaves, window, hwmax, r, o, s, i, part;
+    size_t ncand = 0, num = 0, nvalid = 0;
+    int idx[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1];
+    const sift3d_cuda_keypoint *cands[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1];
+    const float *descs[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1];
+    int counts[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1], vidx[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1];
+    float *strengths = NULL;
+
+    if (d == NULL || im == NULL || devices == NULL || kp == NULL || num_devices < 1 ||
+        num_devices > SIFT3D_CUDA_MULTI_MAX_DEVICES)
+        return SIFT3D_FAILURE;
+    if (im->nc != 1 || im->data == NULL) {
+        ERR("sift3d_detect_describe_sharded: single-channel images only \n");
+        return SIFT3D_FAILURE;
+    }
+    {
+        int min_dim = im->nx < im->ny ? im->nx : im->ny;
+        min_dim = min_dim < im->nz ? min_dim : im->nz;
+        total = (int) log2((double) min_dim) - 3 + 1; /* sift.c:441-452 */
+    }
+    if (total < 1) {
+        ERR("resize_SIFT3D: input image is too small: must have at least 8 voxels in each "
+            "dimension \n");
+        return SIFT3D_FAILURE;
+    }
+    K = sharded_octaves < 1 ? 1 : (sharded_octaves > total ? total : sharded_octaves);
+    tail_octaves = total - K;
+
+    /* (re)build the multi-device object when anything it depends on changed */
+    memset(key, 0, sizeof(key));
+    key[0] = im->nx; key[1] = im->ny; key[2] = im->nz;
+    key[3] = im->ux; key[4] = im->uy; key[5] = im->uz;
+    key[6] = d->sigma_n; key[7] = d->sigma0; key[8] = d->num_kp_levels;
+    key[9] = K; key[10] = num_devices;
+    for (r = 0; r < num_devices; r++)
+        key[11 + r] = devices[r];
+    if (d->multi == NULL || memcmp(key, d->multi_key, sizeof(key)) != 0) {
+        sift3d_cuda_plan_desc *plans, *tail_plan = NULL;
+        const double units[3] = {im->ux, im->uy, im->uz};
+        int ok = 1;
+        sift3d_cuda_multi_destroy(d->multi);
+        d->multi = NULL;
+        plans = (sift3d_cuda_plan_desc *) calloc((size_t) num_devices + 1, sizeof(*plans));
+        if (plans == NULL)
+            return SIFT3D_FAILURE;
+        /* filters do not depend on the geometry: design once to learn the blur's reach */
+        if (fill_plan(d, im->nx, im->ny, im->nz, units, 0, 1, &plans[0])) {
+            free(plans);
+            return SIFT3D_FAILURE;
+        }
+        hwmax = plans[0].first.width / 2;
+        for (i = 0; i < d->num_kp_levels + 2; i++)
+            if (plans[0].octave[i].width / 2 > hwmax)
+                hwmax = plans[0].octave[i].width / 2;
+        /* widest window of the path in planes of ITS octave: the descriptor window radius
+         * desc_rad_fctr * desc_sig_fctr * sd / unit of the top keypoint level (sift.c:1453-1461;
+         * it dominates the orientation window, sift.c:936), + 1 for the central differences,
+         * + 2 for the ceil / floor of the window bounds */
+        window = (int) ceil(DESC_RAD_FCTR * DESC_SIG_FCTR * d->sigma0 *
+                            pow(2.0, (double) (d->num_kp_levels - 1) / d->num_kp_levels) / im->uz) + 3;
+        memset(&M, 0, sizeof(M));
+        M.num_devices = num_devices;
+        for (r = 0; r < num_devices; r++)
+            M.devices[r] = devices[r];
+        M.nx = im->nx; M.ny = im->ny; M.nz = im->nz;
+        memcpy(M.units, units, sizeof(units));
+        M.sharded_octaves = K;
+        for (o = 0; o < SIFT3D_CUDA_MAX_OCTAVES; o++)
+            M.window_planes[o] = window;
+        if (sift3d_sharded_layout(im->nz, num_devices, K, window, hwmax, im->uz, M.g0, M.g1, M.a0, M.a1) < 0) {
+            ERR("sift3d_detect_describe_sharded: %d planes cannot be split into %d slabs aligned to %d \n",
+                im->nz, num_devices, 1 << K);
+            free(plans);
+            return SIFT3D_FAILURE;
+        }
+        for (r = 0; r < num_devices && ok; r++)
+            ok = fill_plan(d, im->nx, im->ny, M.a1[r] - M.a0[r], units, 0, K + (tail_octaves ? 1 : 0),
+                           &plans[r]) == SIFT3D_SUCCESS;
+        if (ok && tail_octaves) {
+            const double tu[3] = {ldexp(units[0], K), ldexp(units[1], K), ldexp(units[2], K)};
+            tail_plan = &plans[num_devices];
+            ok = fill_plan(d, im->nx >> K, im->ny >> K, im->nz >> K, tu, K, tail_octaves, tail_plan) ==
+                 SIFT3D_SUCCESS;
+        }
+        if (ok)
+            d->multi = sift3d_cuda_multi_create(&M, plans, tail_plan);
+        free(plans);
+        if (d->multi == NULL)
+            return SIFT3D_FAILURE;
+        memcpy(d->multi_key, key, sizeof(key));
+    }
+
+    if (sift3d_cuda_multi_run(d->multi, im->data, d->peak_thresh, d->corner_thresh, desc != NULL))
+        return SIFT3D_FAILURE;
+
+    /* ---- merge: (o, s, device, local order); the unsharded octaves follow */
+    for (part = 0; part <= num_devices; part++) {
+        counts[part] = sift3d_cuda_multi_results(d->multi, part, &cands[part], &descs[part]);
+        if (counts[part] < 0)
+            return SIFT3D_FAILURE;
+        ncand += (size_t) counts[part];
+        idx[part] = vidx[part] = 0;
+    }
+    kp->nx = im->nx;
+    kp->ny = im->ny;
+    kp->nz = im->nz;
+    if (kp_reserve(kp, ncand))
+        return SIFT3D_FAILURE;
+    for (part = 0; part <= num_devices; part++)
+        for (i = 0; i < counts[part]; i++)
+            nvalid += cands[part][i].valid != 0;
+    strengths = (float *) malloc((ncand + 1) * sizeof(float));
+    if (strengths == NULL)
+        return SIFT3D_FAILURE;
+    if (desc != NULL) {
+        if (nvalid > desc->cap) {
+            sift3d_cuda_host_free(desc->desc);
+            desc->cap = nvalid + nvalid / 2 + 64;
+            desc->desc = (float *) sift3d_cuda_host_alloc(desc->cap * DESC_NUMEL * sizeof(float));
+            if (desc->desc == NULL)
+                desc->cap = 0;
+        }
+        if (nvalid > 0) {
+            double *xb = (double *) realloc(desc->xyzs, nvalid * 4 * sizeof(double));
+            if (xb != NULL)
+                desc->xyzs = xb;
+            if (xb == NULL || desc->desc == NULL) {
+                free(strengths);
+                desc->num = 0;
+                return SIFT3D_FAILURE;
+            }
+        }
+        desc->nx = im->nx;
+        desc->ny = im->ny;
+        desc->nz = im->nz;
+    }
+    {
+        size_t seen = 0;
+#define TAKE(PART)                                                                              \
+    do {                                                                                        \
+        const sift3d_cuda_keypoint *c = cands[PART] + idx[PART]++;                              \
+        strengths[seen++] = c->strength;                                                        \
+        if (c->valid) {                                                                         \
+            keypoint_rec *dst = kp->buf + num;                                                  \
+            dst->xd = c->x; dst->yd = c->y; dst->zd = c->z; dst->sd = c->sd;                    \
+            dst->o = c->o; dst->s = c->s;                                                       \
+            memcpy(dst->R, c->R, sizeof(dst->R));                                               \
+            if (desc != NULL) {                                                                 \
+                const double f = ldexp(1.0, c->o); /* sift.c:1528-1533 */                       \
+                memcpy(desc->desc + num * DESC_NUMEL, descs[PART] + (size_t) vidx[PART] * DESC_NUMEL, \
+                       DESC_NUMEL * sizeof(float));                                             \
+                desc->xyzs[4 * num + 0] = c->x * f; desc->xyzs[4 * num + 1] = c->y * f;         \
+                desc->xyzs[4 * num + 2] = c->z * f; desc->xyzs[4 * num + 3] = c->sd;            \
+            }                                                                                   \
+            vidx[PART]++;                                                                       \
+            num++;                                                                              \
+        }                                                                                       \
+    } while (0)
+        for (o = 0; o < K; o++)
+            for (s = 0; s < d->num_kp_levels; s++)
+                for (part = 0; part < num_devices; part++)
+                    while (idx[part] < counts[part] && cands[part][idx[part]].o == o &&
+                           cands[part][idx[part]].s == s)
+                        TAKE(part);
+        while (idx[num_devices] < counts[num_devices])
+            TAKE(num_devices);
+#undef TAKE
+        if (seen != ncand) {
+            ERR("sift3d_detect_describe_sharded: per-device candidate lists are not in scan order \n");
+            free(strengths);
+            return SIFT3D_FAILURE;
+        }
+    }
+    /* copy_Keypoint does not copy `strength` (sift.c:372-384): survivor j carries candidate j's */
+    for (i = 0; (size_t) i < num; i++)
+        kp->buf[i].strength = strengths[i];
+    free(strengths);
+    kp->num = num;
+    if (desc != NULL)
+        desc->num = num;
+    d->have_gpyr = 0; /* the pyramid lives on the slabs: no later extract on this detector */
+    return SIFT3D_SUCCESS;
+}
+
+/* Wall-clock split of the last sharded run (milliseconds): total, slabs, unsharded octaves,
+ * slowest slab's detect and describe, and the MiB of halo planes moved between devices. */
+int sift3d_sharded_timings(sift3d_detector *d, float out[6]) {
+    sift3d_cuda_multi_timings t;
+    if (d == NULL || d->multi == NULL || out == NULL || sift3d_cuda_multi_get_timings(d->multi, &t))
+        return SIFT3D_FAILURE;
+    out[0] = t.total_ms; out[1] = t.slabs_ms; out[2] = t.tail_ms;
+    out[3] = t.max_detect_ms; out[4] = t.max_describe_ms; out[5] = t.exchanged_mbytes;
+    return SIFT3D_SUCCESS;
 }

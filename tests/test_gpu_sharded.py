@@ -1,0 +1,88 @@
+"""sift3d_detect_describe_sharded (C host + libsift3d_cuda multi.cu: z-slabs of one volume, one
+host thread per slab, halo exchange by in-stream peer copies) must give the one-device result
+bit for bit: keypoints (incl. the strength-slot quirk) and descriptors. On a one-GPU box all
+slabs share device 0 (the peer copies degenerate to device-local ones); with more GPUs every
+slab gets a device of its own. Blur arithmetic: exact (the slab kernels see other tile and
+chunk shapes than the whole-volume ones; only the 0-ULP mode is shape independent)."""
+import numpy as np
+import pytest
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
+
+
+def _single(vol, units, params):
+    import sift3d_b200 as s3
+    det = s3.Detector(0)
+    det.set_exact(True)
+    for k, v in (params or {}).items():
+        assert getattr(det, f"set_{k}")(v) == 0
+    kp = det.detect(s3.Image.from_array(vol, units))
+    keys = kp.records()
+    desc = det.extract(kp).to_matrix() if len(kp) else np.zeros((0, 771), np.float32)
+    det.close()
+    return keys, desc
+
+
+def _sharded(vol, units, params, world, octaves):
+    import sift3d_b200 as s3
+    ndev = s3.cuda_device_count()
+    det = s3.Detector(0)
+    for k, v in (params or {}).items():
+        assert getattr(det, f"set_{k}")(v) == 0
+    devices = [r % ndev for r in range(world)]
+    im = s3.Image.from_array(vol, units)
+    out = None
+    for _ in range(2):  # second run: the cached multi-device object is reused
+        kp, ds = det.detect_describe_sharded(im, devices, octaves)
+        cur = (kp.records(), ds.to_matrix() if len(kp) else np.zeros((0, 771), np.float32))
+        if out is not None:
+            assert np.array_equal(out[1].view(np.uint32), cur[1].view(np.uint32))
+        out = cur
+    tm = det.sharded_timings()
+    det.close()
+    return out[0], out[1], tm
+
+
+@pytest.fixture(autouse=True)
+def _exact_mode(monkeypatch):
+    monkeypatch.setenv("SIFT3D_CUDA_EXACT", "1")  # contexts made by the library read it at creation
+
+
+@pytest.mark.parametrize("world,dims,octaves,units,params", [
+    (2, (96, 96, 320), 2, (1.0, 1.0, 1.0), None),      # two sharded octaves + unsharded tail
+    (2, (128, 64, 250), 1, (1.0, 1.0, 1.0), None),     # nz not a multiple of the alignment
+    (3, (64, 64, 480), 2, (1.0, 1.0, 1.0), None),      # an interior slab with two cut faces
+    (4, (64, 64, 640), 2, (1.0, 1.0, 1.0), None),
+    (2, (64, 64, 384), 2, (2.0, 2.0, 2.0), {"peak_thresh": 0.05, "corner_thresh": 0.3, "num_kp_levels": 4}),
+    (2, (64, 64, 320), 1, (0.9, 0.9, 1.4), None),      # non-dyadic tap spacing
+])
+def test_sharded_equals_single_device(world, dims, octaves, units, params):
+    from sift3d_b200.synth import synth_volume
+    nx, ny, nz = dims
+    vol = synth_volume(nx, ny, nz, num_blobs=nx * ny * nz // 4096, seed=77 + nz, flags=3)
+    keys, desc = _single(vol, units, params)
+    got_keys, got_desc, tm = _sharded(vol, units, params, world, octaves)
+    assert len(keys) > 10
+    assert len(got_keys) == len(keys)
+    for f in keys.dtype.names:
+        assert np.array_equal(got_keys[f], keys[f]), f
+    assert np.array_equal(got_desc.view(np.uint32), desc.view(np.uint32))
+    assert tm["exchanged_mib"] > 0
+
+
+def test_sharded_layout_rule():
+    """host only, but lives here with its users: owned ranges tile the volume on multiples of
+    2^K and every cut face carries the halo"""
+    import ctypes as C
+    import sift3d_b200 as s3
+    L = s3.lib()
+    for nz, num, K in ((1024, 8, 3), (250, 2, 1), (480, 3, 2)):
+        arr = [(C.c_int * num)() for _ in range(4)]
+        halo = L.sift3d_sharded_layout(nz, num, K, 40, 8, 1.0, *arr)
+        g0, g1, a0, a1 = [list(a) for a in arr]
+        assert halo > 0 and halo % (1 << K) == 0 and halo >= 40 << (K - 1)
+        assert g0[0] == 0 and g1[-1] == nz and all(g1[r] == g0[r + 1] for r in range(num - 1))
+        assert all(g % (1 << K) == 0 for g in g0)
+        assert all(a0[r] == max(0, g0[r] - halo) and a1[r] == min(nz, g1[r] + halo) for r in range(num))
+    arr = [(C.c_int * 4)() for _ in range(4)]
+    assert L.sift3d_sharded_layout(24, 4, 3, 40, 8, 1.0, *arr) == -1
