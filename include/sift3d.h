@@ -200,8 +200,9 @@ SIFT3D_EXPORT int sift3d_detect_describe_sharded(sift3d_detector *, const sift3d
                                                  const int *devices, int num_devices,
                                                  int sharded_octaves, sift3d_keypoint_store *,
                                                  sift3d_descriptor_store *);
-/* total, slabs, unsharded octaves, slowest detect, slowest describe (ms); halo MiB moved */
-SIFT3D_EXPORT int sift3d_sharded_timings(sift3d_detector *, float out[6]);
+/* total, slab detects, unsharded octaves' detect, describe phase, slowest slab detect, slowest
+ * part's describe (ms of host wall clock); MiB of halo planes moved between devices */
+SIFT3D_EXPORT int sift3d_sharded_timings(sift3d_detector *, float out[7]);
 /* The layout rule (host only): owned [g0, g1) / held [a0, a1) planes per device; returns the
  * halo in planes of octave 0, or -1 if nz cannot be split into num slabs aligned to 2^K. */
 SIFT3D_EXPORT int sift3d_sharded_layout(int nz, int num, int K, int window_planes, int max_half_width,

@@ -153,6 +153,9 @@ typedef struct {
     int input_reach;
 } sift3d_cuda_slab_callbacks;
 
+/* Returned by sift3d_cuda_detect_slab with in-stream callbacks when a candidate region was too
+ * small: the regions have been resized, run the detect again on EVERY slab. */
+#define SIFT3D_CUDA_SLAB_RETRY 2
 /* As sift3d_cuda_detect for a z-slab. Candidates are those of the owned planes, with
  * slab-array coordinates; the caller offsets z and merges ranks in (o, s, rank) order. */
 SIFT3D_CUDA_EXPORT int sift3d_cuda_detect_slab(sift3d_cuda_ctx *ctx, const float *image,
@@ -202,8 +205,9 @@ typedef struct {
     int window_planes[SIFT3D_CUDA_MAX_OCTAVES];
 } sift3d_cuda_multi_desc;
 typedef struct {
-    float total_ms, slabs_ms, tail_ms;      /* host wall clock of the last run */
-    float max_detect_ms, max_describe_ms;   /* slowest slab */
+    float total_ms, slabs_ms, tail_ms;      /* host wall clock of the last run: detect phase */
+    float describe_ms;                      /* ... and describe phase (total_ms includes it) */
+    float max_detect_ms, max_describe_ms;   /* slowest part */
     float exchanged_mbytes;                 /* halo planes moved between devices */
 } sift3d_cuda_multi_timings;
 /* slab_plans[r]: plan of device r's array (nx, ny, a1-a0; K or K+1 octaves); tail_plan: the
@@ -212,15 +216,18 @@ SIFT3D_CUDA_EXPORT sift3d_cuda_multi *sift3d_cuda_multi_create(const sift3d_cuda
                                                                const sift3d_cuda_plan_desc *slab_plans,
                                                                const sift3d_cuda_plan_desc *tail_plan);
 SIFT3D_CUDA_EXPORT void sift3d_cuda_multi_destroy(sift3d_cuda_multi *m);
-/* detect (+ describe) the whole volume `host_image` (nx*ny*nz floats, page-locked for speed) */
-SIFT3D_CUDA_EXPORT int sift3d_cuda_multi_run(sift3d_cuda_multi *m, const float *host_image,
-                                             double peak_thresh, double corner_thresh, int describe);
-/* part = device index, or num_devices for the unsharded octaves: its candidates (volume
- * coordinates, the part's scan order) and 768 floats per VALID candidate in that order.
- * Returns the number of candidates; pointers valid until the next run. */
+/* Phase 1: detect on the whole volume `host_image` (nx*ny*nz floats, page-locked for speed). */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_multi_detect(sift3d_cuda_multi *m, const float *host_image,
+                                                double peak_thresh, double corner_thresh);
+/* part = device index, or num_devices for the unsharded octaves: its candidates in volume
+ * coordinates, the part's scan order. Returns their number; valid until the next detect. */
 SIFT3D_CUDA_EXPORT int sift3d_cuda_multi_results(sift3d_cuda_multi *m, int part,
-                                                 const sift3d_cuda_keypoint **cands,
-                                                 const float **descriptors);
+                                                 const sift3d_cuda_keypoint **cands);
+/* Phase 2: every part describes its VALID candidates (in the part's order) on its own device,
+ * all parts at once; the j-th valid candidate of part p goes to row rows[p][j] of `desc`
+ * (page-locked host memory or device memory reachable from every device). */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_multi_describe(sift3d_cuda_multi *m, float *desc,
+                                                  const int *const *rows);
 SIFT3D_CUDA_EXPORT int sift3d_cuda_multi_get_timings(sift3d_cuda_multi *m, sift3d_cuda_multi_timings *t);
 
 /* All candidates in the reference's scan order (o, s, z, y, x), each with its
@@ -249,6 +256,13 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_candidates_flags(sift3d_cuda_ctx *ctx, int oc
 SIFT3D_CUDA_EXPORT int sift3d_cuda_describe(sift3d_cuda_ctx *ctx,
                                             const sift3d_cuda_keypoint *keys, int num,
                                             float *desc, int desc_on_device);
+
+/* As sift3d_cuda_describe, but the descriptor of keys[i] goes to row rows[i] of `desc` (which
+ * must be device-accessible: device memory or page-locked host memory). Lets several
+ * contexts fill disjoint rows of one result buffer (sift3d_cuda_multi). */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_describe_rows(sift3d_cuda_ctx *ctx,
+                                                 const sift3d_cuda_keypoint *keys, int num,
+                                                 float *desc, int desc_on_device, const int *rows);
 
 /* Test / inspection hooks. */
 SIFT3D_CUDA_EXPORT int sift3d_cuda_level_info(sift3d_cuda_ctx *ctx, int o, int s, int dims[3],

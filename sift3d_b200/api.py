@@ -468,11 +468,12 @@ class Detector:
             raise Sift3DError("sift3d_cuda_elapsed_ms failed")
         return ms.value
 
-    def detect_describe_sharded(self, im, devices, sharded_octaves=2, describe=True):
+    def detect_describe_sharded(self, im, devices, sharded_octaves=2, describe=True, kp=None, ds=None):
         """sift3d_detect_describe_sharded: z-slabs of one volume over `devices` (entries may
-        repeat: several slabs on one device). Returns (KeypointStore, DescriptorStore | None)."""
-        kp = KeypointStore()
-        ds = DescriptorStore() if describe else None
+        repeat: several slabs on one device). Returns (KeypointStore, DescriptorStore | None);
+        stores passed in are reused (their page-locked buffers with them)."""
+        kp = KeypointStore() if kp is None else kp
+        ds = (DescriptorStore() if ds is None else ds) if describe else None
         devs = (C.c_int * len(devices))(*[int(v) for v in devices])
         if self._L.sift3d_detect_describe_sharded(self.handle, im.handle, devs, len(devices),
                                                   int(sharded_octaves), kp.handle,
@@ -481,11 +482,11 @@ class Detector:
         return kp, ds
 
     def sharded_timings(self) -> dict:
-        out = (C.c_float * 6)()
+        out = (C.c_float * 7)()
         if self._L.sift3d_sharded_timings(self.handle, out):
             raise Sift3DError("no sharded run on this detector")
-        return dict(zip(("total_ms", "slabs_ms", "tail_ms", "max_detect_ms", "max_describe_ms",
-                         "exchanged_mib"), [float(v) for v in out]))
+        return dict(zip(("total_ms", "slabs_ms", "tail_ms", "describe_ms", "max_detect_ms",
+                         "max_describe_ms", "exchanged_mib"), [float(v) for v in out]))
 
     def set_exact(self, exact=True):
         """0-ULP blur arithmetic (True) or one FFMA per tap (False, the default unless

@@ -19,6 +19,7 @@
 //   * every device describes its own keypoints; the host library merges the per-device lists in
 //     the reference's scan order (o, s, z, y, x) = (o, s, device, local order).
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -69,7 +70,6 @@ struct sift3d_cuda_multi {
     float *seed = nullptr;             // level (K, -1) of the whole volume, on device of rank 0
     // results, per rank (+ one slot for the tail octaves)
     std::vector<sift3d_cuda_keypoint> cand[kMaxRanks + 1];
-    std::vector<float> desc[kMaxRanks + 1];  // 768 floats per VALID candidate, in candidate order
     sift3d_cuda_multi_timings tm;
     size_t exchanged_bytes[kMaxRanks] = {};
 };
@@ -289,73 +289,73 @@ sift3d_cuda_multi *sift3d_cuda_multi_create(const sift3d_cuda_multi_desc *d,
 
 namespace {
 
-// candidates of a context + descriptors of the valid ones
-int fetch_and_describe(sift3d_cuda_ctx *ctx, int n, std::vector<sift3d_cuda_keypoint> &cand,
-                       std::vector<float> &desc, bool describe) {
-    cand.resize((size_t) n);
-    desc.clear();
-    if (n == 0) return 0;
-    if (sift3d_cuda_fetch_candidates(ctx, cand.data(), n) != n) return -1;
-    if (!describe) return 0;
-    std::vector<sift3d_cuda_keypoint> keys;
-    keys.reserve((size_t) n / 3 + 16);
-    for (const sift3d_cuda_keypoint &c : cand)
-        if (c.valid) keys.push_back(c);
-    if (keys.empty()) return 0;
-    desc.resize(keys.size() * SIFT3D_CUDA_DESC_NUMEL);
-    return sift3d_cuda_describe(ctx, keys.data(), (int) keys.size(), desc.data(), 0);
-}
-
 double now_ms() {
     timespec ts;
     clock_gettime(CLOCK_MONOTONIC, &ts);
     return 1e3 * (double) ts.tv_sec + 1e-6 * (double) ts.tv_nsec;
 }
 
+int fetch(sift3d_cuda_ctx *ctx, int n, std::vector<sift3d_cuda_keypoint> &cand) {
+    cand.resize((size_t) n);
+    if (n == 0) return 0;
+    return sift3d_cuda_fetch_candidates(ctx, cand.data(), n) == n ? 0 : -1;
+}
+
 }  // namespace
 
 extern "C" {
 
-int sift3d_cuda_multi_run(sift3d_cuda_multi *m, const float *host_image, double peak_thresh,
-                          double corner_thresh, int describe) {
+int sift3d_cuda_multi_detect(sift3d_cuda_multi *m, const float *host_image, double peak_thresh,
+                             double corner_thresh) {
     if (!m || !host_image || m->failed.load()) {
-        S3D_ERR("sift3d_cuda_multi_run: unusable object or NULL image\n");
+        S3D_ERR("sift3d_cuda_multi_detect: unusable object or NULL image\n");
         return -1;
     }
     const int P = m->P, K = m->K;
     const size_t plane0 = (size_t) m->D.nx * m->D.ny;
     int status[kMaxRanks] = {};
-    double t_detect[kMaxRanks] = {}, t_describe[kMaxRanks] = {};
+    double t_detect[kMaxRanks] = {};
     const double t0 = now_ms();
     auto work = [&](int r) {
         int n = 0;
         const double ta = now_ms();
         int rc = sift3d_cuda_detect_slab(m->ctx[r], host_image + (size_t) m->D.a0[r] * plane0, 0, m->D.units,
                                          peak_thresh, corner_thresh, &m->slab[r], &m->cb[r], &n);
-        const double tb = now_ms();
-        if (rc == 0) rc = fetch_and_describe(m->ctx[r], n, m->cand[r], m->desc[r], describe != 0);
+        t_detect[r] = now_ms() - ta;
+        if (rc == 0) rc = fetch(m->ctx[r], n, m->cand[r]) ? -1 : 0;
         if (rc == 0)
             for (sift3d_cuda_keypoint &c : m->cand[r])  // slab-array z -> volume z (octave coordinates)
                 c.z += (double) (m->D.a0[r] >> c.o);
-        t_detect[r] = tb - ta;
-        t_describe[r] = now_ms() - tb;
-        if (rc) m->failed.store(1);
+        if (rc != 0 && rc != SIFT3D_CUDA_SLAB_RETRY) m->failed.store(1);
         status[r] = rc;
     };
-    {
-        std::vector<std::thread> th;
-        for (int r = 1; r < P; r++) th.emplace_back(work, r);
-        work(0);
-        for (std::thread &t : th) t.join();
-    }
-    for (int r = 0; r < P; r++)
-        if (status[r]) {
-            S3D_ERR("sift3d_cuda_multi_run: slab %d failed\n", r);
+    for (int attempt = 0;; attempt++) {
+        {
+            std::vector<std::thread> th;
+            for (int r = 1; r < P; r++) th.emplace_back(work, r);
+            work(0);
+            for (std::thread &t : th) t.join();
+        }
+        bool retry = false;
+        for (int r = 0; r < P; r++) {
+            if (status[r] == SIFT3D_CUDA_SLAB_RETRY) {
+                retry = true;
+            } else if (status[r]) {
+                S3D_ERR("sift3d_cuda_multi_detect: slab %d failed\n", r);
+                return -1;
+            }
+        }
+        if (!retry) break;
+        // a busy image overflowed a candidate region (resized by now): every slab runs again
+        if (attempt >= 2) {
+            S3D_ERR("sift3d_cuda_multi_detect: candidate regions still too small\n");
+            m->failed.store(1);
             return -1;
         }
+        m->failed.store(0);
+    }
     const double t1 = now_ms();
     m->cand[P].clear();
-    m->desc[P].clear();
     if (m->has_tail) {
         // level (K, -1) of the whole volume from the owners' planes, then the small octaves
         const int dev0 = m->D.devices[0];
@@ -375,7 +375,7 @@ int sift3d_cuda_multi_run(sift3d_cuda_multi *m, const float *host_image, double 
         double tu[3] = {ldexp(m->D.units[0], K), ldexp(m->D.units[1], K), ldexp(m->D.units[2], K)};
         int n = 0;
         if (sift3d_cuda_detect_from_seed(m->tail, m->seed, 1, tu, peak_thresh, corner_thresh, &n) ||
-            fetch_and_describe(m->tail, n, m->cand[P], m->desc[P], describe != 0)) {
+            fetch(m->tail, n, m->cand[P])) {
             m->failed.store(1);
             return -1;
         }
@@ -384,11 +384,9 @@ int sift3d_cuda_multi_run(sift3d_cuda_multi *m, const float *host_image, double 
     m->tm.slabs_ms = (float) (t1 - t0);
     m->tm.tail_ms = (float) (t2 - t1);
     m->tm.total_ms = (float) (t2 - t0);
-    m->tm.max_detect_ms = m->tm.max_describe_ms = 0.0f;
-    for (int r = 0; r < P; r++) {
+    m->tm.max_detect_ms = m->tm.max_describe_ms = m->tm.describe_ms = 0.0f;
+    for (int r = 0; r < P; r++)
         if (t_detect[r] > m->tm.max_detect_ms) m->tm.max_detect_ms = (float) t_detect[r];
-        if (t_describe[r] > m->tm.max_describe_ms) m->tm.max_describe_ms = (float) t_describe[r];
-    }
     size_t ex = 0;
     for (int r = 0; r < P; r++) {
         ex += m->exchanged_bytes[r];
@@ -398,12 +396,54 @@ int sift3d_cuda_multi_run(sift3d_cuda_multi *m, const float *host_image, double 
     return 0;
 }
 
-int sift3d_cuda_multi_results(sift3d_cuda_multi *m, int part, const sift3d_cuda_keypoint **cands,
-                              const float **descriptors) {
+int sift3d_cuda_multi_results(sift3d_cuda_multi *m, int part, const sift3d_cuda_keypoint **cands) {
     if (!m || part < 0 || part > m->P) return -1;
     if (cands) *cands = m->cand[part].empty() ? nullptr : m->cand[part].data();
-    if (descriptors) *descriptors = m->desc[part].empty() ? nullptr : m->desc[part].data();
     return (int) m->cand[part].size();
+}
+
+int sift3d_cuda_multi_describe(sift3d_cuda_multi *m, float *desc, const int *const *rows) {
+    if (!m || !desc || !rows || m->failed.load()) return -1;
+    const int P = m->P;
+    int status[kMaxRanks + 1] = {};
+    double t_desc[kMaxRanks + 1] = {};
+    const double t0 = now_ms();
+    auto work = [&](int part) {
+        const double ta = now_ms();
+        sift3d_cuda_ctx *ctx = part < P ? m->ctx[part] : m->tail;
+        std::vector<sift3d_cuda_keypoint> keys;
+        keys.reserve(m->cand[part].size() / 3 + 16);
+        for (const sift3d_cuda_keypoint &c : m->cand[part])
+            if (c.valid) {
+                keys.push_back(c);
+                if (part < P) keys.back().z -= (double) (m->D.a0[part] >> c.o);  // back to slab-array z
+            }
+        int rc = 0;
+        if (!keys.empty()) {
+            if (rows[part] == nullptr) rc = -1;
+            else rc = sift3d_cuda_describe_rows(ctx, keys.data(), (int) keys.size(), desc, 0, rows[part]);
+        }
+        status[part] = rc;
+        t_desc[part] = now_ms() - ta;
+    };
+    {
+        // the unsharded octaves live on device 0 next to slab 0: a thread of their own
+        std::vector<std::thread> th;
+        const int nparts = P + (m->has_tail ? 1 : 0);
+        for (int part = 1; part < nparts; part++) th.emplace_back(work, part);
+        work(0);
+        for (std::thread &t : th) t.join();
+    }
+    for (int part = 0; part <= P; part++)
+        if (status[part]) {
+            S3D_ERR("sift3d_cuda_multi_describe: part %d failed\n", part);
+            return -1;
+        }
+    m->tm.describe_ms = (float) (now_ms() - t0);
+    for (int part = 0; part <= P; part++)
+        if (t_desc[part] > m->tm.max_describe_ms) m->tm.max_describe_ms = (float) t_desc[part];
+    m->tm.total_ms += m->tm.describe_ms;
+    return 0;
 }
 
 int sift3d_cuda_multi_get_timings(sift3d_cuda_multi *m, sift3d_cuda_multi_timings *t) {

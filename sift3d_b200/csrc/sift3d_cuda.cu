@@ -874,7 +874,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         // counted and run the detection again (a slab cannot: its peers would not follow).
         for (int o = 0; o < noct; o++)
             if (ctx->h_counts[o] > ctx->cand_cap[o]) {
-                if (slab != nullptr || attempt >= 2) {
+                if ((slab != nullptr && !cb->in_stream) || attempt >= 2) {
                     S3D_ERR("sift3d_cuda_detect: octave %d produced %d extrema, capacity %d\n", o,
                             ctx->h_counts[o], ctx->cand_cap[o]);
                     return -1;
@@ -882,6 +882,9 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
                 ctx->cand_min[o] = ctx->h_counts[o] + ctx->h_counts[o] / 4 + 1024;
             }
         if (plan_candidates(ctx)) return -1;
+        // a slab cannot run again on its own (its peers would not follow): the regions are
+        // resized and the caller (sift3d_cuda_multi_detect) repeats the detect on every slab
+        if (slab != nullptr) return SIFT3D_CUDA_SLAB_RETRY;
         return detect_impl(ctx, image, image_on_device, units, peak_thresh, corner_thresh,
                            num_candidates, from_seed, slab, cb, attempt + 1);
     }
@@ -999,8 +1002,25 @@ int sift3d_cuda_candidates_flags(sift3d_cuda_ctx *ctx, int octave_index,
     return ctx->h_counts[octave_index];
 }
 
+static int describe_impl(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys, int num,
+                         float *desc, int desc_on_device, const int *rows);
+
 int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys, int num,
                          float *desc, int desc_on_device) {
+    return describe_impl(ctx, keys, num, desc, desc_on_device, nullptr);
+}
+
+int sift3d_cuda_describe_rows(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys, int num,
+                              float *desc, int desc_on_device, const int *rows) {
+    if (!rows) {
+        S3D_ERR("sift3d_cuda_describe_rows: NULL row table\n");
+        return -1;
+    }
+    return describe_impl(ctx, keys, num, desc, desc_on_device, rows);
+}
+
+static int describe_impl(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys, int num,
+                         float *desc, int desc_on_device, const int *rows) {
     if (!ctx || !ctx->have_pyramid) {
         S3D_ERR("sift3d_cuda_describe: no Gaussian pyramid is available; run detect first\n");
         return -1;
@@ -1092,7 +1112,7 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
         J.cx = (float) k.x; J.cy = (float) k.y; J.cz = (float) k.z;  // sift.c:1474-1476
         J.sigma = (float) (k.sd * 7.071067812);                        // sift.c:43,1453
         for (int j = 0; j < 9; j++) J.R[j] = k.R[j];
-        J.out_index = i;
+        J.out_index = rows ? rows[i] : i;
         J.max_rows = ord[(size_t) r].first;
     }
     const int max_rows = jobs[0].max_rows;
@@ -1111,6 +1131,11 @@ int sift3d_cuda_describe(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
             direct = true;
         } else {
             cudaGetLastError();
+            if (rows) {
+                S3D_ERR("sift3d_cuda_describe_rows: the descriptor buffer must be device-accessible "
+                        "(device memory or page-locked host memory)\n");
+                return -1;
+            }
             if (ctx->desc_out.ensure(sizeof(float) * SIFT3D_CUDA_DESC_NUMEL * (size_t) num)) return -1;
             d_out = (float *) ctx->desc_out.p;
         }

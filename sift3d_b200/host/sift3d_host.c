@@ -1202,12 +1202,13 @@ int sift3d_detect_describe_sharded(sift3d_detector *const d, const sift3d_image 
     sift3d_cuda_multi_desc M;
     double key[32];
     int total, K, tail_octaves, window, hwmax, r, o, s, i, part;
-    size_t ncand = 0, num = 0, nvalid = 0;
+    size_t ncand = 0, num = 0;
     int idx[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1];
     const sift3d_cuda_keypoint *cands[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1];
-    const float *descs[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1];
+    int *rows[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1];
     int counts[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1], vidx[SIFT3D_CUDA_MULTI_MAX_DEVICES + 1];
     float *strengths = NULL;
+    int ok;
 
     if (d == NULL || im == NULL || devices == NULL || kp == NULL || num_devices < 1 ||
         num_devices > SIFT3D_CUDA_MULTI_MAX_DEVICES)
@@ -1293,51 +1294,31 @@ int sift3d_detect_describe_sharded(sift3d_detector *const d, const sift3d_image 
         memcpy(d->multi_key, key, sizeof(key));
     }
 
-    if (sift3d_cuda_multi_run(d->multi, im->data, d->peak_thresh, d->corner_thresh, desc != NULL))
+    if (sift3d_cuda_multi_detect(d->multi, im->data, d->peak_thresh, d->corner_thresh))
         return SIFT3D_FAILURE;
 
     /* ---- merge: (o, s, device, local order); the unsharded octaves follow */
     for (part = 0; part <= num_devices; part++) {
-        counts[part] = sift3d_cuda_multi_results(d->multi, part, &cands[part], &descs[part]);
+        counts[part] = sift3d_cuda_multi_results(d->multi, part, &cands[part]);
         if (counts[part] < 0)
             return SIFT3D_FAILURE;
         ncand += (size_t) counts[part];
         idx[part] = vidx[part] = 0;
+        rows[part] = NULL;
     }
     kp->nx = im->nx;
     kp->ny = im->ny;
     kp->nz = im->nz;
     if (kp_reserve(kp, ncand))
         return SIFT3D_FAILURE;
-    for (part = 0; part <= num_devices; part++)
-        for (i = 0; i < counts[part]; i++)
-            nvalid += cands[part][i].valid != 0;
     strengths = (float *) malloc((ncand + 1) * sizeof(float));
-    if (strengths == NULL)
-        return SIFT3D_FAILURE;
-    if (desc != NULL) {
-        if (nvalid > desc->cap) {
-            sift3d_cuda_host_free(desc->desc);
-            desc->cap = nvalid + nvalid / 2 + 64;
-            desc->desc = (float *) sift3d_cuda_host_alloc(desc->cap * DESC_NUMEL * sizeof(float));
-            if (desc->desc == NULL)
-                desc->cap = 0;
-        }
-        if (nvalid > 0) {
-            double *xb = (double *) realloc(desc->xyzs, nvalid * 4 * sizeof(double));
-            if (xb != NULL)
-                desc->xyzs = xb;
-            if (xb == NULL || desc->desc == NULL) {
-                free(strengths);
-                desc->num = 0;
-                return SIFT3D_FAILURE;
-            }
-        }
-        desc->nx = im->nx;
-        desc->ny = im->ny;
-        desc->nz = im->nz;
+    ok = strengths != NULL;
+    for (part = 0; part <= num_devices && ok; part++) {
+        /* row of the j-th valid candidate of the part in the merged survivor list */
+        rows[part] = (int *) malloc(((size_t) counts[part] + 1) * sizeof(int));
+        ok = rows[part] != NULL;
     }
-    {
+    if (ok) {
         size_t seen = 0;
 #define TAKE(PART)                                                                              \
     do {                                                                                        \
@@ -1348,14 +1329,7 @@ int sift3d_detect_describe_sharded(sift3d_detector *const d, const sift3d_image 
             dst->xd = c->x; dst->yd = c->y; dst->zd = c->z; dst->sd = c->sd;                    \
             dst->o = c->o; dst->s = c->s;                                                       \
             memcpy(dst->R, c->R, sizeof(dst->R));                                               \
-            if (desc != NULL) {                                                                 \
-                const double f = ldexp(1.0, c->o); /* sift.c:1528-1533 */                       \
-                memcpy(desc->desc + num * DESC_NUMEL, descs[PART] + (size_t) vidx[PART] * DESC_NUMEL, \
-                       DESC_NUMEL * sizeof(float));                                             \
-                desc->xyzs[4 * num + 0] = c->x * f; desc->xyzs[4 * num + 1] = c->y * f;         \
-                desc->xyzs[4 * num + 2] = c->z * f; desc->xyzs[4 * num + 3] = c->sd;            \
-            }                                                                                   \
-            vidx[PART]++;                                                                       \
+            rows[PART][vidx[PART]++] = (int) num;                                               \
             num++;                                                                              \
         }                                                                                       \
     } while (0)
@@ -1370,28 +1344,62 @@ int sift3d_detect_describe_sharded(sift3d_detector *const d, const sift3d_image 
 #undef TAKE
         if (seen != ncand) {
             ERR("sift3d_detect_describe_sharded: per-device candidate lists are not in scan order \n");
-            free(strengths);
-            return SIFT3D_FAILURE;
+            ok = 0;
         }
     }
-    /* copy_Keypoint does not copy `strength` (sift.c:372-384): survivor j carries candidate j's */
-    for (i = 0; (size_t) i < num; i++)
-        kp->buf[i].strength = strengths[i];
+    if (ok) {
+        /* copy_Keypoint does not copy `strength` (sift.c:372-384): survivor j carries candidate j's */
+        for (i = 0; (size_t) i < num; i++)
+            kp->buf[i].strength = strengths[i];
+        kp->num = num;
+    }
+    if (ok && desc != NULL) {
+        desc->num = 0;
+        desc->nx = im->nx;
+        desc->ny = im->ny;
+        desc->nz = im->nz;
+        if (num > desc->cap) {
+            /* page-locked: every device writes its rows straight into it */
+            sift3d_cuda_host_free(desc->desc);
+            desc->cap = num + num / 2 + 64;
+            desc->desc = (float *) sift3d_cuda_host_alloc(desc->cap * DESC_NUMEL * sizeof(float));
+            if (desc->desc == NULL)
+                desc->cap = 0;
+        }
+        if (num > 0) {
+            double *xb = (double *) realloc(desc->xyzs, num * 4 * sizeof(double));
+            if (xb != NULL)
+                desc->xyzs = xb;
+            ok = xb != NULL && desc->desc != NULL &&
+                 sift3d_cuda_multi_describe(d->multi, desc->desc, (const int *const *) rows) == 0;
+            for (i = 0; ok && (size_t) i < num; i++) {
+                /* descriptor location in base-octave coordinates (sift.c:1528-1533) */
+                const keypoint_rec *key = kp->buf + i;
+                const double f = ldexp(1.0, key->o);
+                desc->xyzs[4 * (size_t) i + 0] = key->xd * f;
+                desc->xyzs[4 * (size_t) i + 1] = key->yd * f;
+                desc->xyzs[4 * (size_t) i + 2] = key->zd * f;
+                desc->xyzs[4 * (size_t) i + 3] = key->sd;
+            }
+        }
+        if (ok)
+            desc->num = num;
+    }
+    for (part = 0; part <= num_devices; part++)
+        free(rows[part]);
     free(strengths);
-    kp->num = num;
-    if (desc != NULL)
-        desc->num = num;
     d->have_gpyr = 0; /* the pyramid lives on the slabs: no later extract on this detector */
-    return SIFT3D_SUCCESS;
+    return ok ? SIFT3D_SUCCESS : SIFT3D_FAILURE;
 }
 
-/* Wall-clock split of the last sharded run (milliseconds): total, slabs, unsharded octaves,
- * slowest slab's detect and describe, and the MiB of halo planes moved between devices. */
-int sift3d_sharded_timings(sift3d_detector *d, float out[6]) {
+/* Wall-clock split of the last sharded run (milliseconds): total, slab detects, unsharded
+ * octaves' detect, describe phase, slowest slab detect, slowest part's describe, and the MiB of
+ * halo planes moved between devices. */
+int sift3d_sharded_timings(sift3d_detector *d, float out[7]) {
     sift3d_cuda_multi_timings t;
     if (d == NULL || d->multi == NULL || out == NULL || sift3d_cuda_multi_get_timings(d->multi, &t))
         return SIFT3D_FAILURE;
-    out[0] = t.total_ms; out[1] = t.slabs_ms; out[2] = t.tail_ms;
-    out[3] = t.max_detect_ms; out[4] = t.max_describe_ms; out[5] = t.exchanged_mbytes;
+    out[0] = t.total_ms; out[1] = t.slabs_ms; out[2] = t.tail_ms; out[3] = t.describe_ms;
+    out[4] = t.max_detect_ms; out[5] = t.max_describe_ms; out[6] = t.exchanged_mbytes;
     return SIFT3D_SUCCESS;
 }
