@@ -201,6 +201,8 @@ def run_product_arm(args):
     import sift3d_b200 as s3
 
     rank, world, local = dist_env()
+    if rank == 0:
+        use_all_host_threads()  # the workload generator (OpenMP) and the CPU leg run on rank 0
     dist = None
     if world > 1:
         import torch
@@ -319,6 +321,26 @@ def run_product_arm(args):
 
     e_ms, e_wall, _, _ = timed(args.steps, 2, 3, False, drain=drain)
 
+    # ---- config 5 at N > 1: ONE 1024^3 volume z-slab sharded over the N GPUs of this box by
+    # rank 0's process (sift3d_detect_describe_sharded: one host thread per device, halo
+    # exchange over NVLink peer copies); the other ranks wait at the barrier
+    c5 = None
+    if dist is not None:
+        for im in images:
+            im.make_resident(-1)
+        # the other ranks wait on the HOST (gloo): an NCCL barrier would keep a spinning kernel
+        # on their GPUs, which rank 0's slabs would then have to time-slice with
+        import torch
+        host_group = dist.new_group(backend="gloo")
+        torch.cuda.synchronize()
+        dist.barrier(group=host_group)
+        if rank == 0 and not os.environ.get("SIFT3D_BENCH_NO_C5"):
+            try:
+                c5 = run_c5_sharded(world)
+            except Exception as e:  # noqa: BLE001 - reported in the line, the headline stands
+                c5 = {"error": repr(e)}
+        dist.barrier(group=host_group)
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -372,9 +394,49 @@ def run_product_arm(args):
         # (rank 0 at N=1 only: at N>1 the reference arm carries the CPU number)
         "cpu_baseline": None if (os.environ.get("SIFT3D_BENCH_NO_CPU") or world > 1) else measure_cpu_baseline(),
     }
+    if c5 is not None:
+        line["c5_slab"] = c5
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def run_c5_sharded(ngpus, dim=1024, reps=3):
+    """BASELINE.json configs[4]: one dim^3 volume over `ngpus` GPUs (z-slabs) against the same
+    volume on one GPU, through the public C API with the HOST image (uploads inside the time)."""
+    import sift3d_b200 as s3
+    from sift3d_b200 import synth_volume
+
+    nvox = dim ** 3
+    im = s3.Image(dim, dim, dim)
+    synth_volume(dim, dim, dim, num_blobs=nvox // 4096, seed=SEED, flags=0, out=im.array)
+    octaves = 4
+    det = s3.Detector(0)
+    kp, ds = s3.KeypointStore(), s3.DescriptorStore()
+    best1 = None
+    for _ in range(2):
+        t0 = time.perf_counter()
+        det.detect(im, kp)
+        det.extract(kp, ds)
+        dt = time.perf_counter() - t0
+        best1 = dt if best1 is None else min(best1, dt)
+    n1 = len(kp)
+    det.close()
+    det = s3.Detector(0)
+    best, tm = None, None
+    for i in range(reps + 1):  # the first run builds the per-device contexts
+        t0 = time.perf_counter()
+        det.detect_describe_sharded(im, list(range(ngpus)), octaves, kp=kp, ds=ds)
+        dt = time.perf_counter() - t0
+        if i > 0 and (best is None or dt < best):
+            best, tm = dt, det.sharded_timings()
+    out = {"workload": f"C5: one {dim}^3 float32 blob volume, units (1,1,1), z-slabs over {ngpus} GPUs "
+                       f"of one process, {octaves} sharded octaves, host image (upload inside the time)",
+           "n_gpus": ngpus, "e2e_ms": 1e3 * best, "value": nvox / best, "unit": "voxels/s",
+           "single_gpu_e2e_ms": 1e3 * best1, "speedup_vs_single_gpu": best1 / best,
+           "keypoints": len(kp), "keypoints_single_gpu": n1, "timings_ms": tm}
+    det.close()
+    return out
 
 
 def measure_cpu_baseline():
