@@ -133,6 +133,10 @@ typedef struct {
                                         /* slab array's plane 0 is: interpolation         */
                                         /* coordinates are formed in volume coordinates   */
                                         /* so that they round as on a single device       */
+    int vol_nz[SIFT3D_CUDA_MAX_OCTAVES];/* planes of the whole volume's octave o (0: unknown; */
+                                        /* a face of the array that is a face of the volume   */
+                                        /* may then not lie inside a filter's reach of the    */
+                                        /* owned range)                                       */
 } sift3d_cuda_slab_desc;
 
 typedef struct {

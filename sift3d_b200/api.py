@@ -48,7 +48,8 @@ class CudaPlanDesc(C.Structure):
 
 class CudaSlabDesc(C.Structure):
     _fields_ = [("num_sharded_octaves", C.c_int), ("own0", C.c_int * MAX_OCTAVES),
-                ("own1", C.c_int * MAX_OCTAVES), ("org", C.c_int * MAX_OCTAVES)]
+                ("own1", C.c_int * MAX_OCTAVES), ("org", C.c_int * MAX_OCTAVES),
+                ("vol_nz", C.c_int * MAX_OCTAVES)]
 
 
 REDUCE_MAX_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_int)

@@ -672,24 +672,32 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
                 int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
                 const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
                 const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches,
-                int z0, int z1, int zorg, bool exact) {
+                int z0, int z1, int zorg, bool exact, int vol_nz) {
     const int hw = f.width / 2;
     if (z1 < 0) {  // whole volume
         z0 = 0;
         z1 = nz;
     }
-    // A cut face (z-slab mode) must keep the filter footprint inside the array: the planes
-    // beyond it are halo filled by the neighbouring rank, not a volume boundary.
-    if ((z0 > 0 && z0 < 2 * hw + 2) || (z1 < nz && nz - z1 < 2 * hw + 2) || z0 < 0 || z1 > nz || z0 >= z1) {
+    const AxisSpec ax = axis_spec(nx, units[0], hw);
+    const AxisSpec ay = axis_spec(ny, units[1], hw);
+    const AxisSpec az = axis_spec(nz + zorg, units[2], hw);
+    // z-slab mode: a CUT face must keep the filter footprint inside the array (the planes beyond
+    // the owned range are halo filled by the neighbouring device); a face of the array that is a
+    // face of the volume (zorg == 0 below, zorg + nz == vol_nz above) takes the boundary rules.
+    const bool bottom_is_volume = zorg == 0;
+    const bool top_is_volume = vol_nz <= 0 ? false : zorg + nz == vol_nz;
+    const int need = az.uhw + 2;
+    bool fused_ok = true;  // the fused kernels apply the top boundary rule in the chunk that ends at nz only
+    if (z0 < 0 || z1 > nz || z0 >= z1 || (z0 > 0 && !bottom_is_volume && z0 < need) ||
+        (z1 < nz && nz - z1 < need && !top_is_volume) ||
+        (vol_nz <= 0 && ((z0 > 0 && z0 < 2 * hw + 2) || (z1 < nz && nz - z1 < 2 * hw + 2)))) {
         S3D_ERR("sift3d_cuda: z range [%d, %d) of %d planes leaves no room for a %d-tap halo\n", z0, z1,
                 nz, f.width);
         return -1;
     }
+    if (z1 < nz && nz - z1 < need) fused_ok = false;
     const size_t total = (size_t) nx * ny * nz;
     const unsigned blocks = (unsigned) ((total + 255) / 256);
-    const AxisSpec ax = axis_spec(nx, units[0], hw);
-    const AxisSpec ay = axis_spec(ny, units[1], hw);
-    const AxisSpec az = axis_spec(nz + zorg, units[2], hw);
 
     // Fused single-launch path: unit tap spacing on every axis, TMA-compatible rows, taps
     // symmetric bit for bit (the kernel shares the products of twin taps).
@@ -699,7 +707,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
     const int ty_half = (ty_env == 32 || ny < 64) ? 32 : 64;
     bool symmetric = true;
     for (int i = 0; i < hw; i++) symmetric = symmetric && f.taps[i] == f.taps[f.width - 1 - i];
-    if (!force_generic && symmetric && ax.uf == 1.0f && ay.uf == 1.0f && az.uf == 1.0f && hw >= 1 &&
+    if (!force_generic && fused_ok && symmetric && ax.uf == 1.0f && ay.uf == 1.0f && az.uf == 1.0f && hw >= 1 &&
         hw <= 8 && f.width <= kMaxParamTaps && nx % 4 == 0 && nx >= kFTX && ny >= 32 &&
         ny >= 2 * hw + 2 && nz >= 2 * hw + 2 && (((uintptr_t) src | (uintptr_t) dst | (uintptr_t) ds_dst) & 15) == 0 &&
         (d_dogmax_slot == nullptr || dog_prev == src) &&
@@ -739,7 +747,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
     }
 
     // Fused single-launch path for tap spacing 1/2 on every axis (octave 1).
-    if (!force_generic && symmetric && ax.uf == 0.5f && ay.uf == 0.5f && az.uf == 0.5f && hw >= 1 &&
+    if (!force_generic && fused_ok && symmetric && ax.uf == 0.5f && ay.uf == 0.5f && az.uf == 0.5f && hw >= 1 &&
         hw <= 8 && d_divisor == nullptr && nx % 4 == 0 && nx >= kFTX && ny >= ty_half && nx < (1 << 20) &&
         ny < (1 << 20) && nz < (1 << 20) && ny >= hw + 3 && nz >= hw + 3 &&
         ((uintptr_t) src & 15) == 0 && (d_dogmax_slot == nullptr || dog_prev == src)) {

@@ -255,6 +255,7 @@ sift3d_cuda_multi *sift3d_cuda_multi_create(const sift3d_cuda_multi_desc *d,
             S.own0[o] = (d->g0[r] >> o) - (d->a0[r] >> o);
             S.own1[o] = (d->g1[r] >> o) - (d->a0[r] >> o);
             S.org[o] = d->a0[r] >> o;
+            S.vol_nz[o] = d->nz >> o;
         }
         m->self[r].m = m;
         m->self[r].r = r;

@@ -668,7 +668,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             const double u[3] = {L.ux, L.uy, L.uz};
             rc = launch_blur(so, d_in, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.first, ctx->d_taps(-1),
                              ctx->d_scalar(0), nullptr, nullptr, ds_dst, false, &ctx->launches,
-                             zr0(o), zr1(o), zorg(o), ctx->exact);
+                             zr0(o), zr1(o), zorg(o), ctx->exact, slab ? slab->vol_nz[o] : 0);
         } else {
             Level &P = ctx->level(o, s - 1);
             const double u[3] = {P.ux, P.uy, P.uz};
@@ -677,7 +677,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             if (s - 1 >= 0 && s - 1 < kp) slot = ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (s - 1));
             rc = launch_blur(so, P.d, L.d, ta, tb, L.nx, L.ny, L.nz, u, D.octave[s], ctx->d_taps(s),
                              nullptr, slot, P.d, ds_dst, false, &ctx->launches, zr0(o), zr1(o),
-                             zorg(o), ctx->exact);
+                             zorg(o), ctx->exact, slab ? slab->vol_nz[o] : 0);
         }
         if (rc) return -1;
         if (ctx->profiling) S3D_CK(cudaEventRecord(ctx->blur_ev[2 * li + 1], so));

@@ -53,6 +53,8 @@ def _exact_mode(monkeypatch):
     (2, (128, 64, 250), 1, (1.0, 1.0, 1.0), None),     # nz not a multiple of the alignment
     (3, (64, 64, 480), 2, (1.0, 1.0, 1.0), None),      # an interior slab with two cut faces
     (4, (64, 64, 640), 2, (1.0, 1.0, 1.0), None),
+    (8, (64, 64, 512), 3, (1.0, 1.0, 1.0), None),      # halos that reach the volume's faces
+    (8, (96, 64, 512), 4, (1.0, 1.0, 1.0), None),      # every octave sharded (no unsharded tail)
     (2, (64, 64, 384), 2, (2.0, 2.0, 2.0), {"peak_thresh": 0.05, "corner_thresh": 0.3, "num_kp_levels": 4}),
     (2, (64, 64, 320), 1, (0.9, 0.9, 1.4), None),      # non-dyadic tap spacing
 ])
