@@ -70,21 +70,3 @@ def test_sharded_equals_single_device(world, dims, octaves, units, params):
         assert np.array_equal(got_keys[f], keys[f]), f
     assert np.array_equal(got_desc.view(np.uint32), desc.view(np.uint32))
     assert tm["exchanged_mib"] > 0
-
-
-def test_sharded_layout_rule():
-    """host only, but lives here with its users: owned ranges tile the volume on multiples of
-    2^K and every cut face carries the halo"""
-    import ctypes as C
-    import sift3d_b200 as s3
-    L = s3.lib()
-    for nz, num, K in ((1024, 8, 3), (250, 2, 1), (480, 3, 2)):
-        arr = [(C.c_int * num)() for _ in range(4)]
-        halo = L.sift3d_sharded_layout(nz, num, K, 40, 8, 1.0, *arr)
-        g0, g1, a0, a1 = [list(a) for a in arr]
-        assert halo > 0 and halo % (1 << K) == 0 and halo >= 40 << (K - 1)
-        assert g0[0] == 0 and g1[-1] == nz and all(g1[r] == g0[r + 1] for r in range(num - 1))
-        assert all(g % (1 << K) == 0 for g in g0)
-        assert all(a0[r] == max(0, g0[r] - halo) and a1[r] == min(nz, g1[r] + halo) for r in range(num))
-    arr = [(C.c_int * 4)() for _ in range(4)]
-    assert L.sift3d_sharded_layout(24, 4, 3, 40, 8, 1.0, *arr) == -1
