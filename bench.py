@@ -341,6 +341,13 @@ def run_product_arm(args):
                 c5 = {"error": repr(e)}
         dist.barrier(group=host_group)
 
+    # ---- the other single-GPU configurations of BASELINE.json, timed once each on rank 0
+    # (N = 1 only): C1 = the CLI's call sequence on 128^3 (detect, keep the 100 "strongest",
+    # describe; cli/kpSift3D.c:116-135), C3 = 512 x 512 x 300 with anisotropic units
+    extras = None
+    if rank == 0 and world == 1 and not os.environ.get("SIFT3D_BENCH_NO_EXTRAS"):
+        extras = run_other_configs(local)
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -396,9 +403,44 @@ def run_product_arm(args):
     }
     if c5 is not None:
         line["c5_slab"] = c5
+    if extras is not None:
+        line["other_configs"] = extras
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def run_other_configs(device, reps=5):
+    """Best-of-`reps` host wall clock of the public call sequence, host image (upload inside)."""
+    import sift3d_b200 as s3
+    from sift3d_b200.synth import WORKLOADS, workload
+
+    out = {}
+    for name, limit in (("C1_blobs_128", 100), ("C3_ct_512x512x300", None)):
+        (nx, ny, nz), units, _, _ = WORKLOADS[name]
+        im = s3.Image(nx, ny, nz)
+        workload(name, out=im.array)
+        im.set_units(*units)
+        det = s3.Detector(device)
+        kp, ds = s3.KeypointStore(), s3.DescriptorStore()
+        best, stage = None, None
+        for i in range(reps + 1):
+            t0 = time.perf_counter()
+            det.detect(im, kp)
+            nall = len(kp)
+            if limit is not None:
+                kp.sort_by_strength(limit)
+            if len(kp):
+                det.extract(kp, ds)
+            dt = time.perf_counter() - t0
+            if i > 0 and (best is None or dt < best):
+                best, stage = dt, det.timings()
+        out[name] = {"dims": [nx, ny, nz], "units": list(units), "e2e_ms": 1e3 * best,
+                     "voxels_per_s": nx * ny * nz / best, "keypoints_detected": nall,
+                     "keypoints_described": len(kp),
+                     "stage_ms": {k: round(v, 4) for k, v in stage.items() if v}}
+        det.close()
+    return out
 
 
 def run_c5_sharded(ngpus, dim=1024, reps=3):

@@ -122,9 +122,16 @@ int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, in
                    int *d_count, uint64_t *launches, int z0 = 0, int z1 = -1,
                    int s_begin = 0, int s_end = -1)  /* keypoint levels [s_begin, s_end) */;  // planes [z0, z1)
 // all octaves in one launch; counts stay on the device
+struct OrderScratch {   // for the bucket path of busy regions (extrema.cu)
+    Cand *grouped;      // as large as the candidate regions
+    int *ints;          // 3 * nbkt[o] ints per octave at off[o]
+    int nz[SIFT3D_CUDA_MAX_OCTAVES], nbkt[SIFT3D_CUDA_MAX_OCTAVES];
+    size_t off[SIFT3D_CUDA_MAX_OCTAVES];
+};
 int launch_order_all(cudaStream_t st, const Cand *d_raw, Cand *d_sorted, const int *base,
                      const int *cap, int noct, const int *d_counts, uint64_t *launches,
-                     int o_begin = 0, int o_end = -1);  // octaves [o_begin, o_end) only
+                     int o_begin = 0, int o_end = -1,   // octaves [o_begin, o_end) only
+                     const OrderScratch *scratch = nullptr);
 
 // orient.cu
 struct OctaveInfo {  // what the per-candidate kernels need to know about one octave

@@ -202,12 +202,21 @@ struct OrderParams {
     int cap[SIFT3D_CUDA_MAX_OCTAVES];
 };
 
+// Regions with at most kOrderSmall candidates are rank-sorted directly (O(n^2 / 256) per CTA:
+// a few microseconds for the few thousand candidates of a 256^3 octave). Busier regions (1024^3:
+// 300k candidates in octave 0, 130k in a 128^3 octave of noise-free blobs -- 10 ms quadratic) are
+// first grouped by their (level, plane) bucket and rank-sorted inside each bucket. Both sets
+// of kernels are always enqueued and choose on the device by the counted number, so the
+// schedule needs no host round trip.
+constexpr int kOrderSmall = 6144;
+
 __global__ void __launch_bounds__(256)
 order_all_kernel(const Cand *__restrict__ raw, Cand *__restrict__ sorted, const OrderParams P,
                  const int *__restrict__ counts, int o_begin) {
     __shared__ unsigned long long tile[256];
     const int o = blockIdx.y + o_begin;
     const int n = min(counts[o], P.cap[o]);
+    if (n > kOrderSmall) return;  // the bucket kernels take it
     const Cand *__restrict__ in = raw + P.base[o];
     Cand *__restrict__ out = sorted + P.base[o];
     for (int first = blockIdx.x * 256; first < n; first += gridDim.x * 256) {
@@ -228,6 +237,116 @@ order_all_kernel(const Cand *__restrict__ raw, Cand *__restrict__ sorted, const 
             for (int k = 0; k < lim; k++) rank += tile[k] < mine.key ? 1 : 0;
         }
         if (i < n) out[rank] = mine;
+    }
+}
+
+// ---- bucket path: bucket = level * nz + plane (the two leading fields of the key)
+struct BucketParams {
+    int base, cap;     // candidate region of the octave
+    int nz, nbkt;      // planes of the octave, buckets = keypoint levels * nz
+    int *bcount;       // [nbkt] members per bucket (zeroed before the launch)
+    int *bstart;       // [nbkt] first slot of the bucket in the grouped / sorted region
+    int *cursor;       // [nbkt] scatter cursors
+};
+__device__ __forceinline__ int bucket_of(unsigned long long key, int nz) {
+    return (int) (key >> 60) * nz + (int) ((key >> 40) & 0xfffffull);
+}
+
+__global__ void __launch_bounds__(256)
+bucket_count_kernel(const Cand *__restrict__ raw, const BucketParams B, const int *__restrict__ count) {
+    const int n = min(*count, B.cap);
+    if (n <= kOrderSmall) return;
+    const Cand *__restrict__ in = raw + B.base;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256)
+        atomicAdd(&B.bcount[bucket_of(in[i].key, B.nz)], 1);
+}
+
+__global__ void __launch_bounds__(1024)
+bucket_scan_kernel(const BucketParams B, const int *__restrict__ count) {
+    __shared__ int wsum[32];
+    __shared__ int carry;
+    const int n = min(*count, B.cap);
+    if (n <= kOrderSmall) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int first = 0; first < B.nbkt; first += 1024) {
+        const int b = first + tid;
+        const int v = b < B.nbkt ? B.bcount[b] : 0;
+        int incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) wsum[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int w = wsum[lane], wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, wi, o);
+                if (lane >= o) wi += t;
+            }
+            wsum[lane] = wi - w;  // exclusive over the warps
+        }
+        __syncthreads();
+        const int excl = carry + wsum[warp] + incl - v;
+        if (b < B.nbkt) {
+            B.bstart[b] = excl;
+            B.cursor[b] = 0;
+        }
+        __syncthreads();
+        if (tid == 1023) carry = excl + v;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256)
+bucket_scatter_kernel(const Cand *__restrict__ raw, Cand *__restrict__ grouped, const BucketParams B,
+                      const int *__restrict__ count) {
+    const int n = min(*count, B.cap);
+    if (n <= kOrderSmall) return;
+    const Cand *__restrict__ in = raw + B.base;
+    Cand *__restrict__ out = grouped + B.base;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
+        const Cand c = in[i];
+        const int b = bucket_of(c.key, B.nz);
+        out[B.bstart[b] + atomicAdd(&B.cursor[b], 1)] = c;
+    }
+}
+
+// one CTA per bucket (grid-stride over the buckets): rank sort of its members by the whole key
+__global__ void __launch_bounds__(128)
+bucket_rank_kernel(const Cand *__restrict__ grouped, Cand *__restrict__ sorted, const BucketParams B,
+                   const int *__restrict__ count) {
+    __shared__ unsigned long long tile[128];
+    const int n = min(*count, B.cap);
+    if (n <= kOrderSmall) return;
+    for (int b = blockIdx.x; b < B.nbkt; b += gridDim.x) {
+        const int m = B.bcount[b];
+        if (m == 0) continue;
+        const Cand *__restrict__ in = grouped + B.base + B.bstart[b];
+        Cand *__restrict__ out = sorted + B.base + B.bstart[b];
+        for (int first = 0; first < m; first += 128) {
+            const int i = first + threadIdx.x;
+            Cand mine;
+            mine.key = ~0ull;
+            mine.strength = 0.f;
+            mine.pad = 0;
+            if (i < m) mine = in[i];
+            int rank = 0;
+            for (int base = 0; base < m; base += 128) {
+                const int j = base + threadIdx.x;
+                __syncthreads();
+                tile[threadIdx.x] = j < m ? in[j].key : ~0ull;
+                __syncthreads();
+                const int lim = min(128, m - base);
+                for (int k = 0; k < lim; k++) rank += tile[k] < mine.key ? 1 : 0;
+            }
+            if (i < m) out[rank] = mine;
+        }
+        __syncthreads();
     }
 }
 
@@ -279,7 +398,7 @@ int launch_extrema(cudaStream_t st, const float *const *g, int num_kp_levels, in
 
 int launch_order_all(cudaStream_t st, const Cand *d_raw, Cand *d_sorted, const int *base,
                      const int *cap, int noct, const int *d_counts, uint64_t *launches,
-                     int o_begin, int o_end) {
+                     int o_begin, int o_end, const OrderScratch *scratch) {
     OrderParams P;
     for (int o = 0; o < SIFT3D_CUDA_MAX_OCTAVES; o++) {
         P.base[o] = o < noct ? base[o] : 0;
@@ -287,15 +406,29 @@ int launch_order_all(cudaStream_t st, const Cand *d_raw, Cand *d_sorted, const i
     }
     if (o_end < 0) o_end = noct;
     if (o_end <= o_begin) return 0;
-    // 32 CTAs per octave are plenty for the few thousand candidates of a 256^3 volume; the rank
-    // sort is O(n^2), so the regions of a big volume (1024^3: 300k candidates in octave 0, 13 ms on
-    // 32 SMs) get a grid that fills the device. CTAs beyond the counted candidates exit at once.
-    int big = 0;
-    for (int o = o_begin; o < o_end && o < noct; o++) big = cap[o] > big ? cap[o] : big;
-    const unsigned gx = big > (1 << 21) ? (unsigned) kNumSMs * 8 : 32u;
-    order_all_kernel<<<dim3(gx, (unsigned) (o_end - o_begin)), 256, 0, st>>>(d_raw, d_sorted, P, d_counts,
-                                                                            o_begin);
+    order_all_kernel<<<dim3(32u, (unsigned) (o_end - o_begin)), 256, 0, st>>>(d_raw, d_sorted, P, d_counts,
+                                                                             o_begin);
     if (launches) *launches += 1;
+    // regions that can hold more than the direct sort takes also get the bucket kernels
+    for (int o = o_begin; o < o_end && o < noct && scratch != nullptr; o++) {
+        if (cap[o] <= kOrderSmall || scratch->grouped == nullptr) continue;
+        BucketParams B;
+        B.base = base[o];
+        B.cap = cap[o];
+        B.nz = scratch->nz[o];
+        B.nbkt = scratch->nbkt[o];
+        B.bcount = scratch->ints + scratch->off[o];
+        B.bstart = B.bcount + B.nbkt;
+        B.cursor = B.bstart + B.nbkt;
+        S3D_CK(cudaMemsetAsync(B.bcount, 0, sizeof(int) * (size_t) B.nbkt, st));
+        const unsigned g = (unsigned) kNumSMs * 4;
+        bucket_count_kernel<<<g, 256, 0, st>>>(d_raw, B, d_counts + o);
+        bucket_scan_kernel<<<1, 1024, 0, st>>>(B, d_counts + o);
+        bucket_scatter_kernel<<<g, 256, 0, st>>>(d_raw, scratch->grouped, B, d_counts + o);
+        bucket_rank_kernel<<<(unsigned) (B.nbkt < kNumSMs * 16 ? B.nbkt : kNumSMs * 16), 128, 0, st>>>(
+            scratch->grouped, d_sorted, B, d_counts + o);
+        if (launches) *launches += 4;
+    }
     S3D_CK(cudaGetLastError());
     return 0;
 }

@@ -86,6 +86,8 @@ struct sift3d_cuda_ctx {
     int base_octave = 0;                // octave number of this context's octave 0
     DevBuf scalars;                     // [0] image max-abs; [1 + o*MAX_FILTERS + s] DoG max
     DevBuf cand_raw, cand_sorted;       // Cand regions, one per octave
+    DevBuf cand_grouped, order_ints;    // scratch of the bucket ordering of busy regions
+    OrderScratch order_scratch;
     DevBuf counts;                      // int per octave
     DevBuf kps;                         // sift3d_cuda_keypoint regions, one per octave (device)
     // ... or, when they fit kKpsHostMax, in page-locked host memory that the orientation
@@ -215,6 +217,8 @@ void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx) {
     ctx->scalars.release();
     ctx->cand_raw.release();
     ctx->cand_sorted.release();
+    ctx->cand_grouped.release();
+    ctx->order_ints.release();
     ctx->counts.release();
     ctx->kps.release();
     if (ctx->kps_host) cudaFreeHost(ctx->kps_host);
@@ -267,6 +271,22 @@ static int plan_candidates(sift3d_cuda_ctx *ctx) {
         ctx->cand_base[o] = (int) cand_total;
         ctx->cand_cap[o] = (int) cap;
         cand_total += cap;
+    }
+    {
+        // bucket ordering (extrema.cu): one bucket per (keypoint level, plane) of an octave
+        OrderScratch &S = ctx->order_scratch;
+        memset(&S, 0, sizeof(S));
+        size_t ints = 0;
+        for (int o = 0; o < noct; o++) {
+            S.nz[o] = ctx->level(o, 0).nz;
+            S.nbkt[o] = ctx->desc.num_kp_levels * S.nz[o];
+            S.off[o] = ints;
+            ints += 3 * (size_t) S.nbkt[o];
+        }
+        if (ctx->cand_grouped.ensure(cand_total * sizeof(Cand)) || ctx->order_ints.ensure((ints + 1) * sizeof(int)))
+            return -1;
+        S.grouped = (Cand *) ctx->cand_grouped.p;
+        S.ints = (int *) ctx->order_ints.p;
     }
     if (ctx->cand_raw.ensure(cand_total * sizeof(Cand)) ||
         ctx->cand_sorted.ensure(cand_total * sizeof(Cand)) ||
@@ -801,7 +821,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         if (o == 0 && mark(ctx->ev[EV_EXTREMA])) return -1;
         if (launch_order_all(so, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
                              ctx->cand_base.data(), ctx->cand_cap.data(), noct,
-                             (const int *) ctx->counts.p, &ctx->launches, o, o + 1))
+                             (const int *) ctx->counts.p, &ctx->launches, o, o + 1, &ctx->order_scratch))
             return -1;
         if (o == 0 && mark(ctx->ev[EV_ORDER])) return -1;
         if (launch_orient_all(so, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
