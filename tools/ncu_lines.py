@@ -1,14 +1,14 @@
 #!/usr/bin/env python3
 """Executed warp-instructions and stall samples of one kernel of an .ncu-rep, per CUDA source
 line (needs -lineinfo and --import-source on).
-    python tools/ncu_lines.py rep.ncu-rep [kernel-id-regex] [top]"""
+    python tools/ncu_lines.py rep.ncu-rep [kernel-name-regex] [top]"""
 import csv, io, subprocess, sys
 rep = sys.argv[1]
 kid = sys.argv[2] if len(sys.argv) > 2 and sys.argv[2] else None
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
 cmd = ["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"]
 if kid:
-    cmd += ["--kernel-id", "::" + kid]
+    cmd += ["--kernel-name", "regex:" + kid]
 out = subprocess.run(cmd, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hdr, fpath, lines = None, "", []
