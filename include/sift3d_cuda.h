@@ -306,6 +306,17 @@ SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_static(int device, const float *d_src, f
  * + warm-up planes) of the most expensive range, or -1 on invalid arguments. */
 SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_chunk_table(int ncta, int tiles, int nzr, int hw,
                                                     int top_is_volume_top, int *bounds);
+/* Host-only: the banded weights of one pass of the fast-mode blur for a general tap spacing (no
+ * device needed; blur_band.cuh). A line of `n_line` samples of which the array holds
+ * [org, n_line) (org > 0: the lower cut face of a z-slab), tap spacing `unit_factor` (1 / units
+ * of the axis, as a float, like imutil.c:760), filter `f`. Position p of the array gets
+ * out[p] = sum_j w[j * n + p] * in[base[p] + j], j < *band, n = n_line - org: the same samples the
+ * reference's coordinate rule reads (imutil.c:742-861), products of one sample folded together.
+ * `w` holds w_capacity floats, `base` n ints. Returns 0, 1 if the band does not fit w_capacity or
+ * the line is not representable, -1 on invalid arguments. */
+SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_band_table(int n_line, int org, float unit_factor,
+                                                   const sift3d_cuda_filter *f, float *w,
+                                                   size_t w_capacity, int *base, int *band);
 SIFT3D_CUDA_EXPORT int sift3d_cuda_get_timings(sift3d_cuda_ctx *ctx, sift3d_cuda_timings *t);
 /* Number of kernel launches issued by this context since creation. */
 SIFT3D_CUDA_EXPORT uint64_t sift3d_cuda_launch_count(sift3d_cuda_ctx *ctx);

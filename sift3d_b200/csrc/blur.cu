@@ -375,6 +375,7 @@ absdiffmax_kernel(const float *__restrict__ a, const float *__restrict__ b, size
 
 #include "blur_zmarch.cuh"
 #include "blur_fused_half.cuh"
+#include "blur_band.cuh"
 
 namespace s3d {
 
@@ -516,6 +517,30 @@ extern "C" SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_chunk_table(int ncta, int til
         if (cost > worst) worst = cost;
     }
     return worst;
+}
+extern "C" SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_band_table(int n_line, int org, float unit_factor,
+                                                             const sift3d_cuda_filter *f, float *w,
+                                                             size_t w_capacity, int *base, int *band) {
+    using namespace s3d;
+    if (!f || !w || !base || !band || f->width < 1 || f->width > SIFT3D_CUDA_MAX_TAPS || !(f->width & 1) ||
+        org < 0 || n_line - org < 2 || !(unit_factor > 0.0f))
+        return -1;
+    BandKey K;
+    memset(&K, 0, sizeof(K));
+    K.n_line = n_line;
+    K.org = org;
+    K.hw = f->width / 2;
+    K.uf = unit_factor;
+    for (int i = 0; i < f->width; i++) K.taps[i] = f->taps[i];
+    std::vector<float> wT;
+    std::vector<int> b;
+    int B = 0;
+    if (build_band(K, wT, b, B)) return 1;
+    *band = B;
+    if (wT.size() > w_capacity) return 1;
+    memcpy(w, wT.data(), wT.size() * sizeof(float));
+    memcpy(base, b.data(), b.size() * sizeof(int));
+    return 0;
 }
 namespace s3d {
 
@@ -672,7 +697,7 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
                 int nx, int ny, int nz, const double units[3], const sift3d_cuda_filter &f,
                 const float *d_taps, const float *d_divisor, float *d_dogmax_slot,
                 const float *dog_prev, float *ds_dst, bool force_generic, uint64_t *launches,
-                int z0, int z1, int zorg, bool exact, int vol_nz) {
+                int z0, int z1, int zorg, bool exact, int vol_nz, bool no_alloc) {
     const int hw = f.width / 2;
     if (z1 < 0) {  // whole volume
         z0 = 0;
@@ -773,6 +798,46 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
 
     const bool want_max = d_dogmax_slot != nullptr && dog_prev != nullptr;
     if (want_max) S3D_CK(cudaMemsetAsync(d_dogmax_slot, 0, sizeof(float), st));
+
+    // Fast mode, any tap spacing: the three passes as banded multiply-adds (blur_band.cuh).
+    static const bool no_band = getenv("SIFT3D_CUDA_NO_BAND") != nullptr;
+    if (!exact && !force_generic && !no_band && !no_alloc && nx % 4 == 0 && ny % 4 == 0 && nx >= 16 &&
+        (((uintptr_t) src | (uintptr_t) tmp_a | (uintptr_t) tmp_b | (uintptr_t) dst | (uintptr_t) dog_prev) & 15) == 0 &&
+        tmp_a != nullptr && tmp_b != nullptr) {
+        BandAxis bx_, by_, bz_;
+        int r = get_band(nx, 0, ax.uf, f, bx_);
+        if (r == 0) r = get_band(ny, 0, ay.uf, f, by_);
+        if (r == 0) r = get_band(nz + zorg, zorg, az.uf, f, bz_);
+        if (r < 0) return -1;
+        if (r == 0) {
+            // x and y passes cover the z range plus the z band of the last pass
+            const int reach = bz_.B;
+            const int zlo = z0 - reach > 0 ? z0 - reach : 0;
+            const int zhi = z1 + reach < nz ? z1 + reach : nz;
+            int bxx = 32;
+            while (bxx < nx && bxx < 256) bxx <<= 1;
+            unsigned byy = 256 / bxx;
+            if (byy > (unsigned) (ny / 4)) byy = (unsigned) (ny / 4);
+            if (byy < 1) byy = 1;
+            const dim3 rblock((unsigned) bxx, byy, 1);
+            const dim3 rgrid((unsigned) ((nx + bxx - 1) / bxx), (unsigned) ((ny / 4 + byy - 1) / byy),
+                             (unsigned) (zhi - zlo));
+            band_x_rows4_kernel<<<rgrid, rblock, 0, st>>>(src, tmp_a, nx, ny, bx_, d_divisor, zlo);
+            int bx4 = 8;
+            while (bx4 < nx / 4 && bx4 < 64) bx4 <<= 1;
+            const dim3 vblock((unsigned) bx4, (unsigned) (256 / bx4), 1);
+            const dim3 vgrid_xy((unsigned) ((nx / 4 + bx4 - 1) / bx4), (unsigned) ((ny + vblock.y - 1) / vblock.y),
+                                (unsigned) (zhi - zlo));
+            const dim3 vgrid_z(vgrid_xy.x, vgrid_xy.y, (unsigned) (z1 - z0));
+            band4_kernel<1, false><<<vgrid_xy, vblock, 0, st>>>(tmp_a, tmp_b, nx, ny, nz, by_, nullptr, nullptr,
+                                                              nullptr, zlo);
+            band4_kernel<2, true><<<vgrid_z, vblock, 0, st>>>(tmp_b, dst, nx, ny, nz, bz_, dog_prev,
+                                                            want_max ? d_dogmax_slot : nullptr, ds_dst, z0);
+            if (launches) *launches += 3;
+            S3D_CK(cudaGetLastError());
+            return 0;
+        }
+    }
     int bx = 32;
     while (bx < nx && bx < 256) bx <<= 1;
     const dim3 gblock((unsigned) bx, (unsigned) (256 / bx), 1);
@@ -1077,7 +1142,8 @@ extern "C" SIFT3D_CUDA_EXPORT int sift3d_cuda_blur_static(int device, const floa
     static_blur_taps_kernel<<<1, SIFT3D_CUDA_MAX_TAPS, 0, st>>>(*f, d_taps);
     S3D_CK(cudaGetLastError());
     if (launch_blur(st, d_src, d_dst, tmp_a, tmp_b, nx, ny, nz, units, *f, d_taps, nullptr, nullptr,
-                    nullptr, nullptr, false, nullptr, 0, -1, 0, exact != 0))
+                    nullptr, nullptr, false, nullptr, 0, -1, 0, exact != 0, 0, /* no_alloc: the band tables are
+                    allocated at first use, so the literal kernels take the general spacings */ true))
         return -1;
     if (sync) S3D_CK(cudaStreamSynchronize(st));
     return 0;

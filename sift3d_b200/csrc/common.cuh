@@ -90,7 +90,8 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
                 int z0 = 0, int z1 = -1,   // output planes [z0, z1); z1 < 0: the whole volume
                 int zorg = 0,              // z-slab: volume plane of array plane 0
                 bool exact = true,         // 0-ULP arithmetic (else one FFMA per tap, see blur_zmarch.cuh)
-                int vol_nz = 0);           // z-slab: planes of the whole volume at this octave (0: unknown)
+                int vol_nz = 0,            // z-slab: planes of the whole volume at this octave (0: unknown)
+                bool no_alloc = false);    // never allocate (no band tables: literal kernels for general spacings)
 // Chain of tiny octaves in one launch (blur.cu: tiny_octaves_kernel)
 constexpr int kTinyThreads = 1024;
 constexpr int kTinyMaxVox = 4096;   // voxels of the largest octave the chain kernel takes

@@ -70,9 +70,15 @@ def test_blur_static_matches_blur_two_calls_in_a_row(exact):
             want = det.blur(vol, units, taps)
             rc, got = _blur_static(L, dev, vol, units, taps, exact)
             assert rc == 0
-            # same kernels, same arithmetic mode: the tolerance of the exact-mode tests, 0 bits
+            # exact mode and the fused kernel: the same kernels, 0 differing bits (the tolerance of
+            # the exact-mode tests). Fast mode with a general spacing: the existing entry point
+            # runs the banded kernels (their tables are allocated at first use), this one the
+            # literal kernels -- the fast-mode tolerance of tests/test_gpu_parity.py
             rel, nbits = parity.level_error(got, want)
-            assert nbits == 0, f"{shape} {units}: {nbits} voxels differ (max rel err {rel:.3g})"
+            if exact or units == (1.0, 1.0, 1.0):
+                assert nbits == 0, f"{shape} {units}: {nbits} voxels differ (max rel err {rel:.3g})"
+            else:
+                assert rel <= 2e-6, f"{shape} {units}: max rel err {rel:.3g}"
     finally:
         det.close()
 
