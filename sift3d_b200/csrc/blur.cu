@@ -805,34 +805,40 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         (((uintptr_t) src | (uintptr_t) tmp_a | (uintptr_t) tmp_b | (uintptr_t) dst | (uintptr_t) dog_prev) & 15) == 0 &&
         tmp_a != nullptr && tmp_b != nullptr) {
         BandAxis bx_, by_, bz_;
-        int r = get_band(nx, 0, ax.uf, f, bx_);
-        if (r == 0) r = get_band(ny, 0, ay.uf, f, by_);
-        if (r == 0) r = get_band(nz + zorg, zorg, az.uf, f, bz_);
+        int r = get_band(nx, 0, ax.uf, f, 4, bx_);
+        if (r == 0) r = get_band(ny, 0, ay.uf, f, 1, by_);
+        if (r == 0) r = get_band(nz + zorg, zorg, az.uf, f, 1, bz_);
         if (r < 0) return -1;
         if (r == 0) {
-            // x and y passes cover the z range plus the z band of the last pass
-            const int reach = bz_.B;
+            // x and y passes cover the planes the z blocks of [z0, z1) read
+            const int kz0 = z0 >> 2, kz1 = (z1 + 3) >> 2;
+            const int reach = bz_.BB + 4;
             const int zlo = z0 - reach > 0 ? z0 - reach : 0;
             const int zhi = z1 + reach < nz ? z1 + reach : nz;
-            int bxx = 32;
-            while (bxx < nx && bxx < 256) bxx <<= 1;
-            unsigned byy = 256 / bxx;
-            if (byy > (unsigned) (ny / 4)) byy = (unsigned) (ny / 4);
-            if (byy < 1) byy = 1;
-            const dim3 rblock((unsigned) bxx, byy, 1);
-            const dim3 rgrid((unsigned) ((nx + bxx - 1) / bxx), (unsigned) ((ny / 4 + byy - 1) / byy),
-                             (unsigned) (zhi - zlo));
-            band_x_rows4_kernel<<<rgrid, rblock, 0, st>>>(src, tmp_a, nx, ny, bx_, d_divisor, zlo);
-            int bx4 = 8;
-            while (bx4 < nx / 4 && bx4 < 64) bx4 <<= 1;
-            const dim3 vblock((unsigned) bx4, (unsigned) (256 / bx4), 1);
-            const dim3 vgrid_xy((unsigned) ((nx / 4 + bx4 - 1) / bx4), (unsigned) ((ny + vblock.y - 1) / vblock.y),
+            const int nbx = nx / 4;  // blocks of four x (x pass), float4 columns (y, z passes)
+            int tx = 8;
+            while (tx < nbx && tx < 32) tx <<= 1;
+            {
+                const int rows = ny % 8 == 0 ? 8 : 4;
+                unsigned ty = 128 / tx;
+                if (ty > (unsigned) (ny / rows)) ty = (unsigned) (ny / rows);
+                const dim3 block((unsigned) tx, ty, 1);
+                const dim3 grid((unsigned) ((nbx + tx - 1) / tx), (unsigned) ((ny / rows + ty - 1) / ty),
                                 (unsigned) (zhi - zlo));
-            const dim3 vgrid_z(vgrid_xy.x, vgrid_xy.y, (unsigned) (z1 - z0));
-            band4_kernel<1, false><<<vgrid_xy, vblock, 0, st>>>(tmp_a, tmp_b, nx, ny, nz, by_, nullptr, nullptr,
-                                                              nullptr, zlo);
-            band4_kernel<2, true><<<vgrid_z, vblock, 0, st>>>(tmp_b, dst, nx, ny, nz, bz_, dog_prev,
-                                                            want_max ? d_dogmax_slot : nullptr, ds_dst, z0);
+                if (rows == 8) band_x_kernel<8><<<grid, block, 0, st>>>(src, tmp_a, nx, ny, bx_, d_divisor, zlo);
+                else band_x_kernel<4><<<grid, block, 0, st>>>(src, tmp_a, nx, ny, bx_, d_divisor, zlo);
+            }
+            int vx = 8;
+            while (vx < nbx && vx < 64) vx <<= 1;
+            const dim3 vblock((unsigned) vx, (unsigned) (256 / vx), 1);
+            const dim3 grid_y((unsigned) ((nbx + vx - 1) / vx), (unsigned) ((by_.nblk + vblock.y - 1) / vblock.y),
+                              (unsigned) (zhi - zlo));
+            const dim3 grid_z(grid_y.x, (unsigned) ((ny + vblock.y - 1) / vblock.y), (unsigned) (kz1 - kz0));
+            band_blk_kernel<1, false><<<grid_y, vblock, 0, st>>>(tmp_a, tmp_b, nx, ny, nz, by_, nullptr, nullptr,
+                                                                nullptr, zlo, 0, ny);
+            band_blk_kernel<2, true><<<grid_z, vblock, 0, st>>>(tmp_b, dst, nx, ny, nz, bz_, dog_prev,
+                                                               want_max ? d_dogmax_slot : nullptr, ds_dst, kz0,
+                                                               z0, z1);
             if (launches) *launches += 3;
             S3D_CK(cudaGetLastError());
             return 0;

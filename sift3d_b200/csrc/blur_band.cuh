@@ -6,7 +6,7 @@
 // 2 * uhw + 3 samples. The host walks the literal rule once per line position (same float
 // operations as conv_point_generic, so every weight lands on the sample the reference reads)
 // and folds the 2 * (2 hw + 1) products of a position into its band; the kernels are then
-// plain multiply-adds over the band: 15 - 27 FFMA per voxel and axis instead of 17 taps x
+// plain multiply-adds over the band: ~12 - 32 FFMA per voxel and axis instead of 17 taps x
 // (two loads, a float -> int -> float round trip, five unfused operations), at a reordering of
 // the sum (~1e-7 of the level's max-abs; the contract is 1e-5). The exact mode keeps the literal
 // kernels of blur.cu.
@@ -21,10 +21,15 @@
 
 namespace s3d {
 
+// Device form of an axis: positions in blocks of four, block k holding positions 4k .. 4k + 3,
+//     out[4k + i] = sum_r w4[r * nblk + k].i * in[bb[k] + r],   r < BB,
+// the union of the four bands (zero weights where a position does not reach): a thread computes
+// the four positions of a block from ONE pass over the BB samples -- 16 multiply-adds per 16-byte
+// load for the y and z passes -- instead of re-reading the band per position.
 struct BandAxis {
-    const float *wT;  // [B][n]: weight j of position p at wT[j * n + p]
-    const int *base;  // [n]: first sample of position p's band (array coordinates)
-    int B, n;
+    const float4 *w4;  // [BB][nblk]
+    const int *bb;     // [nblk]: first sample of block k (array coordinates; a multiple of 4 for the x axis)
+    int BB, nblk, n;
 };
 
 // ---- host: the band of one axis -----------------------------------------------------------
@@ -35,9 +40,10 @@ struct BandKey {
 };
 struct BandEntry {
     BandKey key;
-    float *d_w = nullptr;
-    int *d_base = nullptr;
-    int B = 0, n = 0;
+    float4 *d_w = nullptr;
+    int *d_bb = nullptr;
+    int BB = 0, nblk = 0, n = 0;
+    int align = 1;
 };
 
 // Literal coordinate rule of one (position, tap): array sample lo (clamped like samp()) and fraction.
@@ -62,7 +68,8 @@ static inline void band_rule(int p, int d, float uf, int n_line, int org, int uh
     lo = (lo < org ? org : lo) - org;
 }
 
-static int build_band(const BandKey &K, std::vector<float> &wT, std::vector<int> &base, int &B) {
+static int build_band(const BandKey &K, std::vector<float> &wT, std::vector<int> &base, int &B,
+                      std::vector<int> *lo_min_out = nullptr, std::vector<int> *lo_max_out = nullptr) {
     const int n = K.n_line - K.org;  // samples held by the array
     const int uhw = (int) ceilf((float) K.hw * K.uf);
     if (n < 2) return -1;
@@ -103,12 +110,54 @@ static int build_band(const BandKey &K, std::vector<float> &wT, std::vector<int>
         base[(size_t) pa] = b;
         for (const auto &e : rows[(size_t) pa]) wT[(size_t) (e.first - b) * n + pa] += e.second;
     }
+    if (lo_min_out) *lo_min_out = lo_min;
+    if (lo_max_out) *lo_max_out = lo_max;
+    return 0;
+}
+
+// Blocks of four positions (the device form above). `align`: bb[] and BB are multiples of it.
+static int pack_band_blocks(int n, int B, const std::vector<float> &wT, const std::vector<int> &base,
+                            const std::vector<int> &lo_min, const std::vector<int> &lo_max, int align,
+                            std::vector<float> &w4, std::vector<int> &bb, int &BB) {
+    const int nblk = (n + 3) / 4;
+    bb.assign((size_t) nblk, 0);
+    int need = 1;
+    for (int k = 0; k < nblk; k++) {
+        int mn = n, mx = -1;
+        for (int p = 4 * k; p < 4 * k + 4 && p < n; p++) {
+            mn = lo_min[(size_t) p] < mn ? lo_min[(size_t) p] : mn;
+            mx = lo_max[(size_t) p] > mx ? lo_max[(size_t) p] : mx;
+        }
+        mn = mn / align * align;
+        bb[(size_t) k] = mn;
+        need = mx - mn + 1 > need ? mx - mn + 1 : need;
+    }
+    BB = (need + align - 1) / align * align;
+    if (BB > n) {
+        if (n % align) return -1;
+        BB = n;
+    }
+    for (int k = 0; k < nblk; k++) {
+        if (bb[(size_t) k] + BB > n) bb[(size_t) k] = (n - BB) / align * align;
+        if (bb[(size_t) k] < 0 || bb[(size_t) k] + BB > n) return -1;
+    }
+    w4.assign((size_t) BB * nblk * 4, 0.0f);
+    for (int p = 0; p < n; p++) {
+        const int k = p >> 2, i = p & 3;
+        for (int j = 0; j < B; j++) {
+            const float w = wT[(size_t) j * n + p];
+            if (w == 0.0f) continue;
+            const int r = base[(size_t) p] + j - bb[(size_t) k];
+            if (r < 0 || r >= BB) return -1;
+            w4[((size_t) r * nblk + k) * 4 + i] = w;
+        }
+    }
     return 0;
 }
 
 // Device copy of an axis band, built at first use and cached for the life of the process (a few
 // tens of KB per (axis length, spacing, filter)); the upload is synchronous, once.
-static int get_band(int n_line, int org, float uf, const sift3d_cuda_filter &f, BandAxis &out) {
+static int get_band(int n_line, int org, float uf, const sift3d_cuda_filter &f, int align, BandAxis &out) {
     static std::mutex mu;
     static std::vector<BandEntry> cache;
     BandKey K;
@@ -121,105 +170,135 @@ static int get_band(int n_line, int org, float uf, const sift3d_cuda_filter &f, 
     for (int i = 0; i < f.width; i++) K.taps[i] = f.taps[i];
     std::lock_guard<std::mutex> lock(mu);
     for (const BandEntry &e : cache)
-        if (memcmp(&e.key, &K, sizeof(K)) == 0) {
-            out.wT = e.d_w; out.base = e.d_base; out.B = e.B; out.n = e.n;
+        if (e.align == align && memcmp(&e.key, &K, sizeof(K)) == 0) {
+            out.w4 = e.d_w; out.bb = e.d_bb; out.BB = e.BB; out.nblk = e.nblk; out.n = e.n;
             return 0;
         }
     if (cache.size() >= 4096) {
         S3D_ERR("sift3d_cuda: band table cache full\n");
         return -1;
     }
-    std::vector<float> wT;
-    std::vector<int> base;
+    std::vector<float> wT, w4;
+    std::vector<int> base, bb, lo_min, lo_max;
     BandEntry e;
     e.key = K;
+    e.align = align;
     e.n = n_line - org;
-    if (build_band(K, wT, base, e.B)) return 1;  // not representable: the literal kernels take it
-    S3D_CK(cudaMalloc((void **) &e.d_w, wT.size() * sizeof(float)));
-    S3D_CK(cudaMalloc((void **) &e.d_base, base.size() * sizeof(int)));
-    S3D_CK(cudaMemcpy(e.d_w, wT.data(), wT.size() * sizeof(float), cudaMemcpyHostToDevice));
-    S3D_CK(cudaMemcpy(e.d_base, base.data(), base.size() * sizeof(int), cudaMemcpyHostToDevice));
+    e.nblk = (e.n + 3) / 4;
+    int B = 0;
+    // not representable: the literal kernels take it
+    if (build_band(K, wT, base, B, &lo_min, &lo_max)) return 1;
+    if (pack_band_blocks(e.n, B, wT, base, lo_min, lo_max, align, w4, bb, e.BB)) return 1;
+    S3D_CK(cudaMalloc((void **) &e.d_w, w4.size() * sizeof(float)));
+    S3D_CK(cudaMalloc((void **) &e.d_bb, bb.size() * sizeof(int)));
+    S3D_CK(cudaMemcpy(e.d_w, w4.data(), w4.size() * sizeof(float), cudaMemcpyHostToDevice));
+    S3D_CK(cudaMemcpy(e.d_bb, bb.data(), bb.size() * sizeof(int), cudaMemcpyHostToDevice));
     cache.push_back(e);
-    out.wT = e.d_w; out.base = e.d_base; out.B = e.B; out.n = e.n;
+    out.w4 = e.d_w; out.bb = e.d_bb; out.BB = e.BB; out.nblk = e.nblk; out.n = e.n;
     return 0;
 }
 
 // ---- kernels ---------------------------------------------------------------------------------
-// x pass: thread = one column x of four rows (the band of a position depends on x only; lanes are
-// adjacent x, so weights and samples are read coalesced). `oscale`: im_scale folded in (first blur).
-__global__ void __launch_bounds__(256)
-band_x_rows4_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny, const BandAxis A,
-                    const float *__restrict__ divisor, int zoff) {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    const int y = 4 * (blockIdx.y * blockDim.y + threadIdx.y);
+// x pass: thread = one block of four x positions on ROWS rows. Lanes are adjacent blocks: the
+// 16-byte sample loads (bb[] is a multiple of 4) and the 16-byte weight loads are coalesced; the
+// weights of a block are shared by its ROWS rows. im_scale (first blur) is folded into the store.
+template <int ROWS>
+__global__ void __launch_bounds__(128)
+band_x_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny, const BandAxis A,
+              const float *__restrict__ divisor, int zoff) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = ROWS * (blockIdx.y * blockDim.y + threadIdx.y);
     const int z = blockIdx.z + zoff;
-    if (x >= nx || y >= ny) return;
+    if (k >= A.nblk || y >= ny) return;
     const size_t row = ((size_t) z * ny + (size_t) y) * nx;
-    const float *__restrict__ q = src + row + A.base[x];
-    const float *__restrict__ w = A.wT + x;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    for (int j = 0; j < A.B; j++) {
-        const float wj = __ldg(w + (size_t) j * nx);
-        a0 = fmaf(wj, q[j], a0);
-        a1 = fmaf(wj, q[j + (size_t) nx], a1);
-        a2 = fmaf(wj, q[j + 2 * (size_t) nx], a2);
-        a3 = fmaf(wj, q[j + 3 * (size_t) nx], a3);
+    const float *__restrict__ q = src + row + A.bb[k];
+    const float4 *__restrict__ w = A.w4 + k;
+    float4 acc[ROWS];
+#pragma unroll
+    for (int i = 0; i < ROWS; i++) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < A.BB; r += 4) {
+        const float4 w0 = __ldg(w + (size_t) r * A.nblk);
+        const float4 w1 = __ldg(w + (size_t) (r + 1) * A.nblk);
+        const float4 w2 = __ldg(w + (size_t) (r + 2) * A.nblk);
+        const float4 w3 = __ldg(w + (size_t) (r + 3) * A.nblk);
+#pragma unroll
+        for (int i = 0; i < ROWS; i++) {
+            const float4 v = *reinterpret_cast<const float4 *>(q + (size_t) i * nx + r);
+            acc[i].x = fmaf(w3.x, v.w, fmaf(w2.x, v.z, fmaf(w1.x, v.y, fmaf(w0.x, v.x, acc[i].x))));
+            acc[i].y = fmaf(w3.y, v.w, fmaf(w2.y, v.z, fmaf(w1.y, v.y, fmaf(w0.y, v.x, acc[i].y))));
+            acc[i].z = fmaf(w3.z, v.w, fmaf(w2.z, v.z, fmaf(w1.z, v.y, fmaf(w0.z, v.x, acc[i].z))));
+            acc[i].w = fmaf(w3.w, v.w, fmaf(w2.w, v.z, fmaf(w1.w, v.y, fmaf(w0.w, v.x, acc[i].w))));
+        }
     }
+    float s = 1.0f;
     if (divisor != nullptr) {
         const float dv = *divisor;
-        if (dv != 0.0f) {  // an all-zero image is left alone (imutil.c:706)
-            const float s = __fdiv_rn(1.0f, dv);
-            a0 *= s; a1 *= s; a2 *= s; a3 *= s;
-        }
+        if (dv != 0.0f) s = __fdiv_rn(1.0f, dv);  // an all-zero image is left alone (imutil.c:706)
     }
-    float *o = dst + row + x;
-    o[0] = a0;
-    o[(size_t) nx] = a1;
-    o[2 * (size_t) nx] = a2;
-    o[3 * (size_t) nx] = a3;
+    float *o = dst + row + 4 * (size_t) k;
+#pragma unroll
+    for (int i = 0; i < ROWS; i++) {
+        if (divisor != nullptr) { acc[i].x *= s; acc[i].y *= s; acc[i].z *= s; acc[i].w *= s; }
+        *reinterpret_cast<float4 *>(o + (size_t) i * nx) = acc[i];
+    }
 }
 
-// y or z pass: thread = four x-adjacent voxels (16-byte accesses); the band depends on (y | z) only.
-// The z pass (EPI) carries the epilogue of a level: max|prev - out| and the 2x decimation.
+// y or z pass: thread = four x-adjacent voxels (16-byte accesses) on the four positions of one
+// block of the axis; the weights are uniform across the warp. The z pass (EPI) carries the
+// epilogue of a level: max|prev - out| and the 2x decimation. Positions [p0, p1) are stored.
 template <int AXIS, bool EPI>
 __global__ void __launch_bounds__(256)
-band4_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny, int nz, const BandAxis A,
-             const float *__restrict__ dog_prev, float *__restrict__ dogmax, float *__restrict__ ds_dst,
-             int zoff) {
+band_blk_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny, int nz, const BandAxis A,
+                const float *__restrict__ dog_prev, float *__restrict__ dogmax, float *__restrict__ ds_dst,
+                int zoff, int p0, int p1) {
     static_assert(AXIS == 1 || AXIS == 2, "the x pass has a kernel of its own");
     const int x = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
-    const int y = blockIdx.y * blockDim.y + threadIdx.y;
-    const int z = blockIdx.z + zoff;
+    const int u = blockIdx.y * blockDim.y + threadIdx.y;  // AXIS 1: block of y; AXIS 2: y
+    const int v_ = blockIdx.z + zoff;                     // AXIS 1: z; AXIS 2: block of z
+    const int k = AXIS == 1 ? u : v_;
     float vmax = 0.0f;
-    if (x < nx && y < ny) {
-        const size_t idx = ((size_t) z * ny + (size_t) y) * nx + (size_t) x;
-        const int p = AXIS == 1 ? y : z;
+    if (x < nx && k < A.nblk && (AXIS == 1 || u < ny)) {
         const size_t stride = AXIS == 1 ? (size_t) nx : (size_t) nx * ny;
-        const float *__restrict__ q = src + (idx - (size_t) p * stride) + (size_t) A.base[p] * stride;
-        const float *__restrict__ w = A.wT + p;
-        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int j = 0; j < A.B; j++) {
-            const float wj = __ldg(w + (size_t) j * A.n);
-            const float4 v = *reinterpret_cast<const float4 *>(q + (size_t) j * stride);
-            a.x = fmaf(wj, v.x, a.x);
-            a.y = fmaf(wj, v.y, a.y);
-            a.z = fmaf(wj, v.z, a.z);
-            a.w = fmaf(wj, v.w, a.w);
+        const size_t line = AXIS == 1 ? (size_t) v_ * ny * nx + (size_t) x : (size_t) u * nx + (size_t) x;
+        const float *__restrict__ q = src + line + (size_t) A.bb[k] * stride;
+        const float4 *__restrict__ w = A.w4 + k;
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, a2 = a0, a3 = a0;
+#pragma unroll 4
+        for (int r = 0; r < A.BB; r++) {
+            const float4 wr = __ldg(w + (size_t) r * A.nblk);
+            const float4 v = *reinterpret_cast<const float4 *>(q + (size_t) r * stride);
+            a0.x = fmaf(wr.x, v.x, a0.x); a0.y = fmaf(wr.x, v.y, a0.y);
+            a0.z = fmaf(wr.x, v.z, a0.z); a0.w = fmaf(wr.x, v.w, a0.w);
+            a1.x = fmaf(wr.y, v.x, a1.x); a1.y = fmaf(wr.y, v.y, a1.y);
+            a1.z = fmaf(wr.y, v.z, a1.z); a1.w = fmaf(wr.y, v.w, a1.w);
+            a2.x = fmaf(wr.z, v.x, a2.x); a2.y = fmaf(wr.z, v.y, a2.y);
+            a2.z = fmaf(wr.z, v.z, a2.z); a2.w = fmaf(wr.z, v.w, a2.w);
+            a3.x = fmaf(wr.w, v.x, a3.x); a3.y = fmaf(wr.w, v.y, a3.y);
+            a3.z = fmaf(wr.w, v.z, a3.z); a3.w = fmaf(wr.w, v.w, a3.w);
         }
-        *reinterpret_cast<float4 *>(dst + idx) = a;
-        if (EPI) {
-            if (dogmax != nullptr) {
-                const float4 pq = *reinterpret_cast<const float4 *>(dog_prev + idx);
-                vmax = fmaxf(fmaxf(fabsf(__fsub_rn(pq.x, a.x)), fabsf(__fsub_rn(pq.y, a.y))),
-                             fmaxf(fabsf(__fsub_rn(pq.z, a.z)), fabsf(__fsub_rn(pq.w, a.w))));
-            }
-            if (ds_dst != nullptr && !((y | z) & 1)) {
-                const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
-                const int qx = x >> 1, qy = y >> 1, qz = z >> 1;
-                if (qy < dny && qz < dnz) {
-                    float *o = ds_dst + ((size_t) qz * dny + qy) * dnx + qx;
-                    if (qx < dnx) o[0] = a.x;
-                    if (qx + 1 < dnx) o[1] = a.z;
+        const float4 out[4] = {a0, a1, a2, a3};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int p = 4 * k + i;
+            if (p < p0 || p >= p1) continue;
+            const size_t idx = line + (size_t) p * stride;
+            const float4 a = out[i];
+            *reinterpret_cast<float4 *>(dst + idx) = a;
+            if (EPI) {
+                const int y = u, z = p;
+                if (dogmax != nullptr) {
+                    const float4 pq = *reinterpret_cast<const float4 *>(dog_prev + idx);
+                    vmax = fmaxf(vmax, fmaxf(fmaxf(fabsf(__fsub_rn(pq.x, a.x)), fabsf(__fsub_rn(pq.y, a.y))),
+                                             fmaxf(fabsf(__fsub_rn(pq.z, a.z)), fabsf(__fsub_rn(pq.w, a.w)))));
+                }
+                if (ds_dst != nullptr && !((y | z) & 1)) {
+                    const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
+                    const int qx = x >> 1, qy = y >> 1, qz = z >> 1;
+                    if (qy < dny && qz < dnz) {
+                        float *o = ds_dst + ((size_t) qz * dny + qy) * dnx + qx;
+                        if (qx < dnx) o[0] = a.x;
+                        if (qx + 1 < dnx) o[1] = a.z;
+                    }
                 }
             }
         }
