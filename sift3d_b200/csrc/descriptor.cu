@@ -620,7 +620,8 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         if (wyc <= 0 || wzc <= 0 || x1 < x0) continue;
         const int nrows = wyc * wzc;
 #pragma unroll 8
-        for (int i = 0; i < kCellBins; i++) wacc[i * 32 + lane] = 0.0f;
+        for (int i = 0; i < kCellBins / 4; i++)
+            *reinterpret_cast<float4 *>(wacc + i * 128 + lane * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
         bool any = false;
 
         // Rows are taken 32 at a time (one per lane): x interval of row /\ sphere /\ cell, then
@@ -843,31 +844,37 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         auto accumulate = [&](const Vox &v) {
             const float mag = v.mag;
             const float m3[3] = {__fmul_rn(mag, v.b0), __fmul_rn(mag, v.b1), __fmul_rn(mag, v.b2)};
-            float *a3[3];
+            // a lane's copy of the cell's bins: [vertex][ddx][lane][ddy ddz] -- the four (ddy, ddz)
+            // corners of a (vertex, ddx) are one 16-byte word, so a voxel is 6 LDS.128 + 6 STS.128
+            // (each four conflict-free wavefronts) instead of 24 + 24 32-bit accesses
+            float4 *a4[3];
 #pragma unroll
-            for (int k = 0; k < 3; k++) a3[k] = wacc + (k == 0 ? v.i0 : (k == 1 ? v.i1 : v.i2)) + lane;
-            const float wx[2] = {__fsub_rn(1.0f, v.fx), v.fx};
-            const float wy2[2] = {__fsub_rn(1.0f, v.fy), v.fy};
-            const float wz2[2] = {__fsub_rn(1.0f, v.fz), v.fz};
-            // all 24 loads first, then the FMAs, then the stores: written bin by bin the
-            // compiler must assume the three vertex columns alias and serialises
-            // LDS -> FFMA -> STS 24 times (~35 cycles each)
-            float acc[8][3];
+            for (int k = 0; k < 3; k++)
+                a4[k] = reinterpret_cast<float4 *>(wacc + (k == 0 ? v.i0 : (k == 1 ? v.i1 : v.i2)) * 8 + lane * 4);
+            const float wx0 = __fsub_rn(1.0f, v.fx), wy0 = __fsub_rn(1.0f, v.fy), wz0 = __fsub_rn(1.0f, v.fz);
+            const float4 yz = make_float4(__fmul_rn(wy0, wz0), __fmul_rn(wy0, v.fz), __fmul_rn(v.fy, wz0),
+                                          __fmul_rn(v.fy, v.fz));
+            // all loads first, then the FMAs, then the stores: written bin by bin the compiler
+            // must assume the three vertex columns alias and serialises LDS -> FFMA -> STS
+            float4 acc[3][2];
 #pragma unroll
-            for (int c = 0; c < 8; c++)
-#pragma unroll
-                for (int k = 0; k < 3; k++) acc[c][k] = a3[k][c * (kVerts * 32)];
-#pragma unroll
-            for (int c = 0; c < 8; c++) {
-                const int ddx = c >> 2, ddy = (c >> 1) & 1, ddz = c & 1;
-                const float wgt = __fmul_rn(__fmul_rn(wx[ddx], wy2[ddy]), wz2[ddz]);
-#pragma unroll
-                for (int k = 0; k < 3; k++) acc[c][k] = fmaf(m3[k], wgt, acc[c][k]);
+            for (int k = 0; k < 3; k++) {
+                acc[k][0] = a4[k][0];
+                acc[k][1] = a4[k][32];
             }
 #pragma unroll
-            for (int c = 0; c < 8; c++)
+            for (int k = 0; k < 3; k++) {
+                const float m0 = __fmul_rn(m3[k], wx0), m1 = __fmul_rn(m3[k], v.fx);
+                acc[k][0].x = fmaf(m0, yz.x, acc[k][0].x); acc[k][0].y = fmaf(m0, yz.y, acc[k][0].y);
+                acc[k][0].z = fmaf(m0, yz.z, acc[k][0].z); acc[k][0].w = fmaf(m0, yz.w, acc[k][0].w);
+                acc[k][1].x = fmaf(m1, yz.x, acc[k][1].x); acc[k][1].y = fmaf(m1, yz.y, acc[k][1].y);
+                acc[k][1].z = fmaf(m1, yz.z, acc[k][1].z); acc[k][1].w = fmaf(m1, yz.w, acc[k][1].w);
+            }
 #pragma unroll
-                for (int k = 0; k < 3; k++) a3[k][c * (kVerts * 32)] = acc[c][k];
+            for (int k = 0; k < 3; k++) {
+                a4[k][0] = acc[k][0];
+                a4[k][32] = acc[k][1];
+            }
         };
 
         for (;;) {
@@ -889,11 +896,14 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             const int hb = (b0 + b1 * kPadDim + b2 * kPadDim * kPadDim) * kVerts;
 #pragma unroll
             for (int q = 0; q < kCellBins / 32; q++) {
-                const int bin = q * 32 + lane;
+                const int t = q * 32 + lane;
+                const int g = t >> 2, j = t & 3;  // g = vertex * 2 + ddx, j = ddy * 2 + ddz
                 float sum = 0.0f;
+                // lanes of one j start 8 banks apart ((lane >> 2) * 4 + j): conflict-free
 #pragma unroll 8
-                for (int i = 0; i < 32; i++) sum = __fadd_rn(sum, wacc[bin * 32 + ((lane + i) & 31)]);
-                const int c = bin / kVerts, v = bin - c * kVerts;
+                for (int i = 0; i < 32; i++)
+                    sum = __fadd_rn(sum, wacc[g * 128 + (((lane >> 2) + i) & 31) * 4 + j]);
+                const int v = g >> 1, c = ((g & 1) << 2) | j;
                 const int off = ((c >> 2) + ((c >> 1) & 1) * kPadDim + (c & 1) * kPadDim * kPadDim) * kVerts;
                 if (sum != 0.0f) fix_add2(hlo, hhi, hb + off + v, sum);
             }
