@@ -522,6 +522,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     __shared__ double red[kDescThreads / 32];
     __shared__ double norm_sh;
     __shared__ int next_cell;
+    __shared__ unsigned char rowlane_all[kDescThreads];  // per warp: lane of the k-th non-empty row
     const int ki = blockIdx.x;
     if (ki >= n) return;
     const DescJob J = jobs[ki];
@@ -529,6 +530,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     const int lane = tid & 31, warp = tid >> 5;
     const unsigned full = 0xffffffffu;
     float *__restrict__ wacc = wacc_all + warp * (kCellBins * 32);
+    unsigned char *rowlane = rowlane_all + warp * 32;
     for (int i = tid; i < kPadNumel; i += kDescThreads) {
         hlo[i] = 0u;
         hhi[i] = 0;
@@ -567,6 +569,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     const float rad2 = __fmul_rn(rad, rad);
     const float sig2 = __fmul_rn(sigma, sigma);
     const float nhs = -0.5f / sig2;
+    const float nhs2 = nhs * 1.4426950408889634f;  // exp(x) = 2^(x log2 e)
     const float ixu = __fdiv_rn(1.0f, uxf), iyu = __fdiv_rn(1.0f, uyf), izu = __fdiv_rn(1.0f, uzf);
     const float hixu = 0.5f * ixu, hiyu = 0.5f * iyu, hizu = 0.5f * izu;
     const float hw_bf = half_w * bin_fctr;  // == 2: (k + half_w) * bin_fctr as one FMA
@@ -600,6 +603,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         if (ci >= 64) break;
         const int cell = c_cell_order[ci];
         const int b0 = cell & 3, b1 = (cell >> 2) & 3, b2 = cell >> 4;
+        const float fb0 = (float) b0, fb1 = (float) b1, fb2 = (float) b2;
         // rotated-frame slab of the cell along each axis, and its centre
         const float lo0 = (float) b0 * hist_w - half_w, lo1 = (float) b1 * hist_w - half_w,
                     lo2 = (float) b2 * hist_w - half_w;
@@ -628,10 +632,10 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         // an exclusive scan -> a set of up to 32 segments holding `T` flattened entries. Steps
         // consume 32 entries; when the current set runs short the step is topped up from the
         // next set, so only the last step of a cell can be partial.
-        auto load_set = [&](int batch, int &pre, int &xa, int &ry, int &rz, int &T) {
+        auto load_set = [&](int batch, int &pre, int &xa, int &ry, int &T) {
             const int rr = batch * 32 + lane;
-            int len = 0;
-            xa = x0; ry = ya; rz = za;
+            int len = 0, rz = za;
+            xa = x0; ry = ya;
             if (rr < nrows) {
                 rz = za + rr / wyc;
                 ry = ya + (rr - (rz - za) * wyc);
@@ -668,33 +672,38 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
                 if (lane >= o) incl += v;
             }
             T = __shfl_sync(full, incl, 31);
-            pre = incl - len;
-        };
-        // segment of entry t in a set: the last lane j with pre_j <= t
-        auto find_row = [&](int pre, int t) {
-            int j = 0;
-#pragma unroll
-            for (int st = 16; st >= 1; st >>= 1) {
-                const int pv = __shfl_sync(full, pre, (j + st) & 31);
-                if (j + st < 32 && pv <= t) j += st;
-            }
-            return j;
+            // compact the non-empty rows to lanes 0 .. K-1 (in order): their starts are then
+            // strictly increasing and the row of an entry is a population count (next_entries)
+            const unsigned nb = __ballot_sync(full, len > 0);
+            if (len > 0) rowlane[__popc(nb & ((1u << lane) - 1u))] = (unsigned char) lane;
+            __syncwarp();
+            const int src = rowlane[lane];
+            __syncwarp();
+            const int ex = incl - len;
+            const int p = __shfl_sync(full, ex, src);
+            const int xm = __shfl_sync(full, xa - ex, src);
+            const int pk = __shfl_sync(full, ((rz - za) << 16) | (ry - ya), src);
+            const bool held = lane < __popc(nb);
+            pre = held ? p : 0x7fffffff;
+            xa = xm;   // x of entry t of this row: xa + t
+            ry = pk;   // (z - za) << 16 | (y - ya)
         };
         const int nbatch = (nrows + 31) >> 5;
         int bi = 0;
-        int c_pre, c_xa, c_y, c_z, c_T, c_off = 0;
-        int n_pre = 0, n_xa = 0, n_y = 0, n_z = 0, n_T = 0;
+        int c_pre, c_xm, c_yz, c_T, c_off = 0;
+        int n_pre = 0x7fffffff, n_xm = 0, n_yz = 0, n_T = 0;
         bool have_next = false;
-        load_set(bi++, c_pre, c_xa, c_y, c_z, c_T);
+        load_set(bi++, c_pre, c_xm, c_yz, c_T);
+        const unsigned le_mask = 0xffffffffu >> (31 - lane);  // bits 0 .. lane
         // the next 32 flattened entries: one voxel per lane (warp-uniform control flow)
         auto next_entries = [&](int &x, int &y, int &z, bool &active) -> bool {
             for (;;) {
                 if (c_T - c_off > 0) break;
                 if (have_next) {
-                    c_pre = n_pre; c_xa = n_xa; c_y = n_y; c_z = n_z; c_T = n_T; c_off = 0;
+                    c_pre = n_pre; c_xm = n_xm; c_yz = n_yz; c_T = n_T; c_off = 0;
                     have_next = false;
                 } else if (bi < nbatch) {
-                    load_set(bi++, c_pre, c_xa, c_y, c_z, c_T);
+                    load_set(bi++, c_pre, c_xm, c_yz, c_T);
                     c_off = 0;
                 } else {
                     x = x0; y = ya; z = za; active = false;
@@ -706,7 +715,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             bool mixed = false;
             if (avail < 32 && (have_next || bi < nbatch)) {
                 if (!have_next) {
-                    load_set(bi++, n_pre, n_xa, n_y, n_z, n_T);
+                    load_set(bi++, n_pre, n_xm, n_yz, n_T);
                     have_next = true;
                 }
                 mixed = true;
@@ -714,21 +723,29 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             const int take_b = mixed ? min(32 - fill_a, n_T) : 0;
             const bool from_a = lane < fill_a;
             const bool from_b = !from_a && lane - fill_a < take_b;
-            const int t = from_a ? c_off + lane : lane - fill_a;
-            const int j = find_row(c_pre, from_a ? t : 0);
-            x = __shfl_sync(full, c_xa, j) + (t - __shfl_sync(full, c_pre, j));
-            y = __shfl_sync(full, c_y, j);
-            z = __shfl_sync(full, c_z, j);
-            if (take_b > 0) {  // warp-uniform
-                const int jb = find_row(n_pre, from_b ? t : 0);
-                const int xb = __shfl_sync(full, n_xa, jb) + (t - __shfl_sync(full, n_pre, jb));
-                const int yb2 = __shfl_sync(full, n_y, jb);
-                const int zb2 = __shfl_sync(full, n_z, jb);
-                if (from_b) { x = xb; y = yb2; z = zb2; }
+            // Row of entry c_off + lane: the rows that start at or before c_off (a ballot) plus the
+            // starts inside the step up to this lane (one bit per start, OR-reduced: REDUX) -- the
+            // held rows are non-empty, so the starts are distinct.
+            const int sa = c_pre - c_off;
+            const unsigned bits_a = __reduce_or_sync(full, (unsigned) (sa - 1) < 31u ? 1u << sa : 0u);
+            const int ja = __popc(__ballot_sync(full, sa <= 0)) - 1 + __popc(bits_a & le_mask);
+            int xm = __shfl_sync(full, c_xm, ja);
+            int yz = __shfl_sync(full, c_yz, ja);
+            int t = c_off + lane;
+            if (take_b > 0) {  // warp-uniform: the step is topped up from the next set
+                const int sb = n_pre < 32 ? n_pre + fill_a : 32;
+                const unsigned bits_b = __reduce_or_sync(full, sb < 32 ? 1u << sb : 0u);
+                const int jb = __popc(bits_b & le_mask) - 1;
+                const int xmb = __shfl_sync(full, n_xm, jb);
+                const int yzb = __shfl_sync(full, n_yz, jb);
+                if (from_b) { xm = xmb; yz = yzb; t = lane - fill_a; }
             }
+            x = xm + t;
+            y = ya + (yz & 0xffff);
+            z = za + (yz >> 16);
             c_off += fill_a;
             if (mixed && c_off >= c_T) {  // the current set is used up: the next one takes over
-                c_pre = n_pre; c_xa = n_xa; c_y = n_y; c_z = n_z; c_T = n_T; c_off = take_b;
+                c_pre = n_pre; c_xm = n_xm; c_yz = n_yz; c_T = n_T; c_off = take_b;
                 have_next = false;
             }
             active = from_a || from_b;
@@ -760,20 +777,22 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             const float vbx = kDescFma ? fmaf(kx, bin_fctr, hw_bf) : __fmul_rn(__fadd_rn(kx, half_w), bin_fctr);
             const float vby = kDescFma ? fmaf(ky, bin_fctr, hw_bf) : __fmul_rn(__fadd_rn(ky, half_w), bin_fctr);
             const float vbz = kDescFma ? fmaf(kz, bin_fctr, hw_bf) : __fmul_rn(__fadd_rn(kz, half_w), bin_fctr);
-            ok = ok && !(vbx < 0.0f || vby < 0.0f || vbz < 0.0f || vbx >= (float) kHistPerDim ||
-                         vby >= (float) kHistPerDim || vbz >= (float) kHistPerDim);
-            // the voxel belongs to the cell its own indices name (the interval margins overlap)
-            ok = ok && (int) vbx == b0 && (int) vby == b1 && (int) vbz == b2;
-            v.fx = __fsub_rn(vbx, floorf(vbx));
-            v.fy = __fsub_rn(vby, floorf(vby));
-            v.fz = __fsub_rn(vbz, floorf(vbz));
+            // sift.c:1481-1486 rejects vb outside [0, 4) and bins by (int) vb; the voxel belongs to the
+            // cell its own indices name (the interval margins overlap). For vb >= 0 the cast is the
+            // floor, for vb < 0 the floor is <= -1 and matches no cell: one compare per axis.
+            const float flx = floorf(vbx), fly = floorf(vby), flz = floorf(vbz);
+            ok = ok && flx == fb0 && fly == fb1 && flz == fb2;
+            v.fx = __fsub_rn(vbx, flx);
+            v.fy = __fsub_rn(vby, fly);
+            v.fz = __fsub_rn(vbz, flz);
 
             const float *__restrict__ row = img + (size_t) z * zs + (size_t) y * ys;
             // 0.5 * (a - b) / u: the halving is exact, so (a - b) * (0.5 / u) has the same bits
             float gx = __fmul_rn(__fsub_rn(row[x + 1], row[x - 1]), hixu);
             float gy = __fmul_rn(__fsub_rn(row[x + ys], row[(ptrdiff_t) x - (ptrdiff_t) ys]), hiyu);
             float gz = __fmul_rn(__fsub_rn(row[x + zs], row[(ptrdiff_t) x - (ptrdiff_t) zs]), hizu);
-            const float w = __expf(sq * nhs);  // exp(-0.5 * sq / sigma^2), sift.c:1498
+            float w;  // exp(-0.5 * sq / sigma^2), sift.c:1498: one multiply and MUFU.EX2
+            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(w) : "f"(sq * nhs2));
             gx = __fmul_rn(gx, w);
             gy = __fmul_rn(gy, w);
             gz = __fmul_rn(gz, w);
