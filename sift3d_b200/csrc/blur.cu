@@ -805,14 +805,14 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         (((uintptr_t) src | (uintptr_t) tmp_a | (uintptr_t) tmp_b | (uintptr_t) dst | (uintptr_t) dog_prev) & 15) == 0 &&
         tmp_a != nullptr && tmp_b != nullptr) {
         BandAxis bx_, by_, bz_;
-        int r = get_band(nx, 0, ax.uf, f, 4, bx_);
-        if (r == 0) r = get_band(ny, 0, ay.uf, f, 1, by_);
-        if (r == 0) r = get_band(nz + zorg, zorg, az.uf, f, 1, bz_);
+        int r = get_band(nx, 0, ax.uf, f, 4, 4, bx_);
+        if (r == 0) r = get_band(ny, 0, ay.uf, f, 1, kBandR, by_);
+        if (r == 0) r = get_band(nz + zorg, zorg, az.uf, f, 1, kBandR, bz_);
         if (r < 0) return -1;
         if (r == 0) {
             // x and y passes cover the planes the z blocks of [z0, z1) read
-            const int kz0 = z0 >> 2, kz1 = (z1 + 3) >> 2;
-            const int reach = bz_.BB + 4;
+            const int kz0 = z0 / kBandR, kz1 = (z1 + kBandR - 1) / kBandR;
+            const int reach = bz_.BB + kBandR;
             const int zlo = z0 - reach > 0 ? z0 - reach : 0;
             const int zhi = z1 + reach < nz ? z1 + reach : nz;
             const int nbx = nx / 4;  // blocks of four x (x pass), float4 columns (y, z passes)

@@ -21,13 +21,14 @@
 
 namespace s3d {
 
-// Device form of an axis: positions in blocks of four, block k holding positions 4k .. 4k + 3,
-//     out[4k + i] = sum_r w4[r * nblk + k].i * in[bb[k] + r],   r < BB,
-// the union of the four bands (zero weights where a position does not reach): a thread computes
-// the four positions of a block from ONE pass over the BB samples -- 16 multiply-adds per 16-byte
+// Device form of an axis: positions in blocks of R (4 along x, 8 along y and z), block k holding
+// positions R k .. R k + R - 1,
+//     out[R k + i] = sum_r w[(r * nblk + k) * R + i] * in[bb[k] + r],   r < BB,
+// the union of the R bands (zero weights where a position does not reach): a thread computes
+// the R positions of a block from ONE pass over the BB samples -- 32 multiply-adds per 16-byte
 // load for the y and z passes -- instead of re-reading the band per position.
 struct BandAxis {
-    const float4 *w4;  // [BB][nblk]
+    const float4 *w4;  // [BB][nblk][R / 4]
     const int *bb;     // [nblk]: first sample of block k (array coordinates; a multiple of 4 for the x axis)
     int BB, nblk, n;
 };
@@ -43,7 +44,7 @@ struct BandEntry {
     float4 *d_w = nullptr;
     int *d_bb = nullptr;
     int BB = 0, nblk = 0, n = 0;
-    int align = 1;
+    int align = 1, R = 4;
 };
 
 // Literal coordinate rule of one (position, tap): array sample lo (clamped like samp()) and fraction.
@@ -115,16 +116,16 @@ static int build_band(const BandKey &K, std::vector<float> &wT, std::vector<int>
     return 0;
 }
 
-// Blocks of four positions (the device form above). `align`: bb[] and BB are multiples of it.
+// Blocks of R positions (the device form above). `align`: bb[] and BB are multiples of it.
 static int pack_band_blocks(int n, int B, const std::vector<float> &wT, const std::vector<int> &base,
-                            const std::vector<int> &lo_min, const std::vector<int> &lo_max, int align,
+                            const std::vector<int> &lo_min, const std::vector<int> &lo_max, int align, int R,
                             std::vector<float> &w4, std::vector<int> &bb, int &BB) {
-    const int nblk = (n + 3) / 4;
+    const int nblk = (n + R - 1) / R;
     bb.assign((size_t) nblk, 0);
     int need = 1;
     for (int k = 0; k < nblk; k++) {
         int mn = n, mx = -1;
-        for (int p = 4 * k; p < 4 * k + 4 && p < n; p++) {
+        for (int p = R * k; p < R * k + R && p < n; p++) {
             mn = lo_min[(size_t) p] < mn ? lo_min[(size_t) p] : mn;
             mx = lo_max[(size_t) p] > mx ? lo_max[(size_t) p] : mx;
         }
@@ -141,15 +142,15 @@ static int pack_band_blocks(int n, int B, const std::vector<float> &wT, const st
         if (bb[(size_t) k] + BB > n) bb[(size_t) k] = (n - BB) / align * align;
         if (bb[(size_t) k] < 0 || bb[(size_t) k] + BB > n) return -1;
     }
-    w4.assign((size_t) BB * nblk * 4, 0.0f);
+    w4.assign((size_t) BB * nblk * R, 0.0f);
     for (int p = 0; p < n; p++) {
-        const int k = p >> 2, i = p & 3;
+        const int k = p / R, i = p % R;
         for (int j = 0; j < B; j++) {
             const float w = wT[(size_t) j * n + p];
             if (w == 0.0f) continue;
             const int r = base[(size_t) p] + j - bb[(size_t) k];
             if (r < 0 || r >= BB) return -1;
-            w4[((size_t) r * nblk + k) * 4 + i] = w;
+            w4[((size_t) r * nblk + k) * R + i] = w;
         }
     }
     return 0;
@@ -157,7 +158,7 @@ static int pack_band_blocks(int n, int B, const std::vector<float> &wT, const st
 
 // Device copy of an axis band, built at first use and cached for the life of the process (a few
 // tens of KB per (axis length, spacing, filter)); the upload is synchronous, once.
-static int get_band(int n_line, int org, float uf, const sift3d_cuda_filter &f, int align, BandAxis &out) {
+static int get_band(int n_line, int org, float uf, const sift3d_cuda_filter &f, int align, int R, BandAxis &out) {
     static std::mutex mu;
     static std::vector<BandEntry> cache;
     BandKey K;
@@ -170,7 +171,7 @@ static int get_band(int n_line, int org, float uf, const sift3d_cuda_filter &f, 
     for (int i = 0; i < f.width; i++) K.taps[i] = f.taps[i];
     std::lock_guard<std::mutex> lock(mu);
     for (const BandEntry &e : cache)
-        if (e.align == align && memcmp(&e.key, &K, sizeof(K)) == 0) {
+        if (e.align == align && e.R == R && memcmp(&e.key, &K, sizeof(K)) == 0) {
             out.w4 = e.d_w; out.bb = e.d_bb; out.BB = e.BB; out.nblk = e.nblk; out.n = e.n;
             return 0;
         }
@@ -183,12 +184,13 @@ static int get_band(int n_line, int org, float uf, const sift3d_cuda_filter &f, 
     BandEntry e;
     e.key = K;
     e.align = align;
+    e.R = R;
     e.n = n_line - org;
-    e.nblk = (e.n + 3) / 4;
+    e.nblk = (e.n + R - 1) / R;
     int B = 0;
     // not representable: the literal kernels take it
     if (build_band(K, wT, base, B, &lo_min, &lo_max)) return 1;
-    if (pack_band_blocks(e.n, B, wT, base, lo_min, lo_max, align, w4, bb, e.BB)) return 1;
+    if (pack_band_blocks(e.n, B, wT, base, lo_min, lo_max, align, R, w4, bb, e.BB)) return 1;
     S3D_CK(cudaMalloc((void **) &e.d_w, w4.size() * sizeof(float)));
     S3D_CK(cudaMalloc((void **) &e.d_bb, bb.size() * sizeof(int)));
     S3D_CK(cudaMemcpy(e.d_w, w4.data(), w4.size() * sizeof(float), cudaMemcpyHostToDevice));
@@ -243,15 +245,17 @@ band_x_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, in
     }
 }
 
-// y or z pass: thread = four x-adjacent voxels (16-byte accesses) on the four positions of one
+// y or z pass: thread = four x-adjacent voxels (16-byte accesses) on the R = 8 positions of one
 // block of the axis; the weights are uniform across the warp. The z pass (EPI) carries the
 // epilogue of a level: max|prev - out| and the 2x decimation. Positions [p0, p1) are stored.
+constexpr int kBandR = 4;  // (8: 91-102 registers, two CTAs per SM -- measured 17 % slower on C3)
 template <int AXIS, bool EPI>
 __global__ void __launch_bounds__(256)
 band_blk_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny, int nz, const BandAxis A,
                 const float *__restrict__ dog_prev, float *__restrict__ dogmax, float *__restrict__ ds_dst,
                 int zoff, int p0, int p1) {
     static_assert(AXIS == 1 || AXIS == 2, "the x pass has a kernel of its own");
+    constexpr int R = kBandR;
     const int x = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
     const int u = blockIdx.y * blockDim.y + threadIdx.y;  // AXIS 1: block of y; AXIS 2: y
     const int v_ = blockIdx.z + zoff;                     // AXIS 1: z; AXIS 2: block of z
@@ -261,43 +265,63 @@ band_blk_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, 
         const size_t stride = AXIS == 1 ? (size_t) nx : (size_t) nx * ny;
         const size_t line = AXIS == 1 ? (size_t) v_ * ny * nx + (size_t) x : (size_t) u * nx + (size_t) x;
         const float *__restrict__ q = src + line + (size_t) A.bb[k] * stride;
-        const float4 *__restrict__ w = A.w4 + k;
-        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0, a2 = a0, a3 = a0;
-#pragma unroll 4
-        for (int r = 0; r < A.BB; r++) {
-            const float4 wr = __ldg(w + (size_t) r * A.nblk);
-            const float4 v = *reinterpret_cast<const float4 *>(q + (size_t) r * stride);
-            a0.x = fmaf(wr.x, v.x, a0.x); a0.y = fmaf(wr.x, v.y, a0.y);
-            a0.z = fmaf(wr.x, v.z, a0.z); a0.w = fmaf(wr.x, v.w, a0.w);
-            a1.x = fmaf(wr.y, v.x, a1.x); a1.y = fmaf(wr.y, v.y, a1.y);
-            a1.z = fmaf(wr.y, v.z, a1.z); a1.w = fmaf(wr.y, v.w, a1.w);
-            a2.x = fmaf(wr.z, v.x, a2.x); a2.y = fmaf(wr.z, v.y, a2.y);
-            a2.z = fmaf(wr.z, v.z, a2.z); a2.w = fmaf(wr.z, v.w, a2.w);
-            a3.x = fmaf(wr.w, v.x, a3.x); a3.y = fmaf(wr.w, v.y, a3.y);
-            a3.z = fmaf(wr.w, v.z, a3.z); a3.w = fmaf(wr.w, v.w, a3.w);
-        }
-        const float4 out[4] = {a0, a1, a2, a3};
+        const float4 *__restrict__ w = A.w4 + (size_t) k * (R / 4);
+        const size_t wstep = (size_t) A.nblk * (R / 4);
+        float4 a[R];
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int p = 4 * k + i;
+        for (int i = 0; i < R; i++) a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        // four samples per round, the next round's loads issued before this round's multiply-adds
+        // (the passes are latency-bound: ~40 % occupancy, each load a different row or plane)
+        constexpr int U = 4;
+        const int BB = A.BB;
+        const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 v[U], vn[U];
+#pragma unroll
+        for (int j = 0; j < U; j++) v[j] = j < BB ? *reinterpret_cast<const float4 *>(q + (size_t) j * stride) : zero4;
+        for (int r = 0; r < BB; r += U) {
+#pragma unroll
+            for (int j = 0; j < U; j++)
+                vn[j] = r + U + j < BB ? *reinterpret_cast<const float4 *>(q + (size_t) (r + U + j) * stride) : zero4;
+#pragma unroll
+            for (int j = 0; j < U; j++) {
+                if (r + j < BB) {  // (uniform)
+#pragma unroll
+                    for (int h = 0; h < R / 4; h++) {
+                        const float4 wr = __ldg(w + (size_t) (r + j) * wstep + h);
+                        const float ws[4] = {wr.x, wr.y, wr.z, wr.w};
+#pragma unroll
+                        for (int i = 0; i < 4; i++) {
+                            float4 &t = a[4 * h + i];
+                            t.x = fmaf(ws[i], v[j].x, t.x); t.y = fmaf(ws[i], v[j].y, t.y);
+                            t.z = fmaf(ws[i], v[j].z, t.z); t.w = fmaf(ws[i], v[j].w, t.w);
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < U; j++) v[j] = vn[j];
+        }
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            const int p = R * k + i;
             if (p < p0 || p >= p1) continue;
             const size_t idx = line + (size_t) p * stride;
-            const float4 a = out[i];
-            *reinterpret_cast<float4 *>(dst + idx) = a;
+            const float4 o4 = a[i];
+            *reinterpret_cast<float4 *>(dst + idx) = o4;
             if (EPI) {
                 const int y = u, z = p;
                 if (dogmax != nullptr) {
                     const float4 pq = *reinterpret_cast<const float4 *>(dog_prev + idx);
-                    vmax = fmaxf(vmax, fmaxf(fmaxf(fabsf(__fsub_rn(pq.x, a.x)), fabsf(__fsub_rn(pq.y, a.y))),
-                                             fmaxf(fabsf(__fsub_rn(pq.z, a.z)), fabsf(__fsub_rn(pq.w, a.w)))));
+                    vmax = fmaxf(vmax, fmaxf(fmaxf(fabsf(__fsub_rn(pq.x, o4.x)), fabsf(__fsub_rn(pq.y, o4.y))),
+                                             fmaxf(fabsf(__fsub_rn(pq.z, o4.z)), fabsf(__fsub_rn(pq.w, o4.w)))));
                 }
                 if (ds_dst != nullptr && !((y | z) & 1)) {
                     const int dnx = nx >> 1, dny = ny >> 1, dnz = nz >> 1;
                     const int qx = x >> 1, qy = y >> 1, qz = z >> 1;
                     if (qy < dny && qz < dnz) {
                         float *o = ds_dst + ((size_t) qz * dny + qy) * dnx + qx;
-                        if (qx < dnx) o[0] = a.x;
-                        if (qx + 1 < dnx) o[1] = a.z;
+                        if (qx < dnx) o[0] = o4.x;
+                        if (qx + 1 < dnx) o[1] = o4.z;
                     }
                 }
             }

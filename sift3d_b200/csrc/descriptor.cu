@@ -623,6 +623,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         const int wyc = yb - ya + 1, wzc = zb - za + 1;
         if (wyc <= 0 || wzc <= 0 || x1 < x0) continue;
         const int nrows = wyc * wzc;
+        const float inv_wyc = 1.0f / (float) wyc;
 #pragma unroll 8
         for (int i = 0; i < kCellBins / 4; i++)
             *reinterpret_cast<float4 *>(wacc + i * 128 + lane * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -637,8 +638,15 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
             int len = 0, rz = za;
             xa = x0; ry = ya;
             if (rr < nrows) {
-                rz = za + rr / wyc;
-                ry = ya + (rr - (rz - za) * wyc);
+                // rr / wyc by a float reciprocal and one correction step (exact for any operands
+                // below 2^23; an integer division is ~20 instructions)
+                int q = (int) (((float) rr + 0.5f) * inv_wyc);
+                int rem_y = rr - q * wyc;
+                if (rem_y < 0) { q--; rem_y += wyc; }
+                else if (rem_y >= wyc) { q++; rem_y -= wyc; }
+                if (nrows >= (1 << 22)) { q = rr / wyc; rem_y = rr - q * wyc; }  // (warp-uniform; never in practice)
+                rz = za + q;
+                ry = ya + rem_y;
                 const float dy = ((float) ry - cy) * uyf, dz = ((float) rz - cz) * uzf;
                 const float rem = rad2 * 1.0001f - dy * dy - dz * dz;
                 if (rem >= 0.0f) {
