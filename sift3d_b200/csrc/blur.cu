@@ -834,9 +834,10 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
             const dim3 grid_y((unsigned) ((nbx + vx - 1) / vx), (unsigned) ((by_.nblk + vblock.y - 1) / vblock.y),
                               (unsigned) (zhi - zlo));
             const dim3 grid_z(grid_y.x, (unsigned) ((ny + vblock.y - 1) / vblock.y), (unsigned) (kz1 - kz0));
-            band_blk_kernel<1, false><<<grid_y, vblock, 0, st>>>(tmp_a, tmp_b, nx, ny, nz, by_, nullptr, nullptr,
+            const size_t ring_bytes = (size_t) kBandDepth * 256 * sizeof(float4);
+            band_blk_kernel<1, false><<<grid_y, vblock, ring_bytes, st>>>(tmp_a, tmp_b, nx, ny, nz, by_, nullptr, nullptr,
                                                                 nullptr, zlo, 0, ny);
-            band_blk_kernel<2, true><<<grid_z, vblock, 0, st>>>(tmp_b, dst, nx, ny, nz, bz_, dog_prev,
+            band_blk_kernel<2, true><<<grid_z, vblock, ring_bytes, st>>>(tmp_b, dst, nx, ny, nz, bz_, dog_prev,
                                                                want_max ? d_dogmax_slot : nullptr, ds_dst, kz0,
                                                                z0, z1);
             if (launches) *launches += 3;

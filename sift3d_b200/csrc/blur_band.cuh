@@ -248,6 +248,7 @@ band_x_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, in
 // y or z pass: thread = four x-adjacent voxels (16-byte accesses) on the R = 8 positions of one
 // block of the axis; the weights are uniform across the warp. The z pass (EPI) carries the
 // epilogue of a level: max|prev - out| and the 2x decimation. Positions [p0, p1) are stored.
+constexpr int kBandDepth = 8;  // cp.async ring slots per thread (y and z passes)
 constexpr int kBandR = 4;  // (8: 91-102 registers, two CTAs per SM -- measured 17 % slower on C3)
 template <int AXIS, bool EPI>
 __global__ void __launch_bounds__(256)
@@ -255,6 +256,7 @@ band_blk_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, 
                 const float *__restrict__ dog_prev, float *__restrict__ dogmax, float *__restrict__ ds_dst,
                 int zoff, int p0, int p1) {
     static_assert(AXIS == 1 || AXIS == 2, "the x pass has a kernel of its own");
+    extern __shared__ __align__(16) float4 band_ring[];  // [kBandDepth][threads of the CTA]
     constexpr int R = kBandR;
     const int x = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
     const int u = blockIdx.y * blockDim.y + threadIdx.y;  // AXIS 1: block of y; AXIS 2: y
@@ -270,37 +272,48 @@ band_blk_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, 
         float4 a[R];
 #pragma unroll
         for (int i = 0; i < R; i++) a[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        // four samples per round, the next round's loads issued before this round's multiply-adds
-        // (the passes are latency-bound: ~40 % occupancy, each load a different row or plane)
-        constexpr int U = 4;
+        // The passes are latency-bound (every sample of a thread is a different row or plane): the
+        // samples travel global -> shared memory by cp.async into a ring of kBandDepth 16-byte
+        // slots PRIVATE to the thread (no barriers; lanes are 16 bytes apart: conflict-free), so
+        // kBandDepth - 1 loads per thread are in flight without holding registers.
+        constexpr int D = kBandDepth;
         const int BB = A.BB;
-        const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 v[U], vn[U];
+        const int nthr = blockDim.x * blockDim.y;
+        float4 *ring = band_ring + (threadIdx.y * blockDim.x + threadIdx.x);
+        const unsigned ring_s = (unsigned) __cvta_generic_to_shared(ring);
+        auto issue = [&](int r) {  // sample r -> slot r % D; an empty group past the band keeps the count
+            if (r < BB)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_s + (unsigned) ((r & (D - 1)) * nthr) * 16u),
+                             "l"(q + (size_t) r * stride) : "memory");
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
 #pragma unroll
-        for (int j = 0; j < U; j++) v[j] = j < BB ? *reinterpret_cast<const float4 *>(q + (size_t) j * stride) : zero4;
-        for (int r = 0; r < BB; r += U) {
+        for (int r = 0; r < D - 1; r++) issue(r);
+        float4 wcur[R / 4], wnext[R / 4];
 #pragma unroll
-            for (int j = 0; j < U; j++)
-                vn[j] = r + U + j < BB ? *reinterpret_cast<const float4 *>(q + (size_t) (r + U + j) * stride) : zero4;
+        for (int h = 0; h < R / 4; h++) wcur[h] = __ldg(w + h);
+        for (int r = 0; r < BB; r++) {
+            // (the weights of the next round are requested before the wait: the asm statements
+            // are barriers for the compiler's own scheduling of loads)
+            const int rn = r + 1 < BB ? r + 1 : r;
 #pragma unroll
-            for (int j = 0; j < U; j++) {
-                if (r + j < BB) {  // (uniform)
+            for (int h = 0; h < R / 4; h++) wnext[h] = __ldg(w + (size_t) rn * wstep + h);
+            issue(r + D - 1);  // into the slot read one round ago
+            asm volatile("cp.async.wait_group %0;" ::"n"(D - 1) : "memory");
+            const float4 v = ring[(r & (D - 1)) * nthr];
 #pragma unroll
-                    for (int h = 0; h < R / 4; h++) {
-                        const float4 wr = __ldg(w + (size_t) (r + j) * wstep + h);
-                        const float ws[4] = {wr.x, wr.y, wr.z, wr.w};
+            for (int h = 0; h < R / 4; h++) {
+                const float ws[4] = {wcur[h].x, wcur[h].y, wcur[h].z, wcur[h].w};
 #pragma unroll
-                        for (int i = 0; i < 4; i++) {
-                            float4 &t = a[4 * h + i];
-                            t.x = fmaf(ws[i], v[j].x, t.x); t.y = fmaf(ws[i], v[j].y, t.y);
-                            t.z = fmaf(ws[i], v[j].z, t.z); t.w = fmaf(ws[i], v[j].w, t.w);
-                        }
-                    }
+                for (int i = 0; i < 4; i++) {
+                    float4 &t = a[4 * h + i];
+                    t.x = fmaf(ws[i], v.x, t.x); t.y = fmaf(ws[i], v.y, t.y);
+                    t.z = fmaf(ws[i], v.z, t.z); t.w = fmaf(ws[i], v.w, t.w);
                 }
+                wcur[h] = wnext[h];
             }
-#pragma unroll
-            for (int j = 0; j < U; j++) v[j] = vn[j];
         }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
 #pragma unroll
         for (int i = 0; i < R; i++) {
             const int p = R * k + i;
