@@ -248,8 +248,9 @@ band_x_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, in
 // y or z pass: thread = four x-adjacent voxels (16-byte accesses) on the R = 8 positions of one
 // block of the axis; the weights are uniform across the warp. The z pass (EPI) carries the
 // epilogue of a level: max|prev - out| and the 2x decimation. Positions [p0, p1) are stored.
-constexpr int kBandDepth = 8;  // cp.async ring slots per thread (y and z passes)
-constexpr int kBandR = 4;  // (8: 91-102 registers, two CTAs per SM -- measured 17 % slower on C3)
+constexpr int kBandDepth = 8;      // cp.async ring slots per thread (y and z passes)
+constexpr int kBandThreads = 256;  // threads of a y / z pass CTA (the ring's slot pitch)
+constexpr int kBandR = 4;          // positions per thread along y / z (8 measured slower twice: fewer, longer threads)
 template <int AXIS, bool EPI>
 __global__ void __launch_bounds__(256)
 band_blk_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, int ny, int nz, const BandAxis A,
@@ -275,42 +276,54 @@ band_blk_kernel(const float *__restrict__ src, float *__restrict__ dst, int nx, 
         // The passes are latency-bound (every sample of a thread is a different row or plane): the
         // samples travel global -> shared memory by cp.async into a ring of kBandDepth 16-byte
         // slots PRIVATE to the thread (no barriers; lanes are 16 bytes apart: conflict-free), so
-        // kBandDepth - 1 loads per thread are in flight without holding registers.
+        // kBandDepth - 1 loads per thread are in flight without holding registers. The loop is
+        // unrolled over the ring (static slot offsets, advancing pointers): with the loads out of
+        // the way the passes are bound by instruction issue.
         constexpr int D = kBandDepth;
         const int BB = A.BB;
-        const int nthr = blockDim.x * blockDim.y;
         float4 *ring = band_ring + (threadIdx.y * blockDim.x + threadIdx.x);
         const unsigned ring_s = (unsigned) __cvta_generic_to_shared(ring);
-        auto issue = [&](int r) {  // sample r -> slot r % D; an empty group past the band keeps the count
-            if (r < BB)
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_s + (unsigned) ((r & (D - 1)) * nthr) * 16u),
-                             "l"(q + (size_t) r * stride) : "memory");
+        const float *qi = q;  // next sample to request
+        int ri = 0;
+        auto issue = [&](int slot) {  // an empty group past the band keeps the group count in step
+            if (ri < BB)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring_s + (unsigned) (slot * kBandThreads * 16)),
+                             "l"(qi) : "memory");
             asm volatile("cp.async.commit_group;" ::: "memory");
+            qi += stride;
+            ri++;
         };
 #pragma unroll
-        for (int r = 0; r < D - 1; r++) issue(r);
+        for (int u = 0; u < D - 1; u++) issue(u);
         float4 wcur[R / 4], wnext[R / 4];
 #pragma unroll
         for (int h = 0; h < R / 4; h++) wcur[h] = __ldg(w + h);
-        for (int r = 0; r < BB; r++) {
-            // (the weights of the next round are requested before the wait: the asm statements
-            // are barriers for the compiler's own scheduling of loads)
-            const int rn = r + 1 < BB ? r + 1 : r;
+        const float4 *wp = w;
+        for (int r0 = 0; r0 < BB; r0 += D) {
 #pragma unroll
-            for (int h = 0; h < R / 4; h++) wnext[h] = __ldg(w + (size_t) rn * wstep + h);
-            issue(r + D - 1);  // into the slot read one round ago
-            asm volatile("cp.async.wait_group %0;" ::"n"(D - 1) : "memory");
-            const float4 v = ring[(r & (D - 1)) * nthr];
+            for (int u = 0; u < D; u++) {
+                // (the weights of the next round are requested before the wait: the asm statements
+                // are barriers for the compiler's own scheduling of loads)
+                if (r0 + u + 1 < BB) wp += wstep;
 #pragma unroll
-            for (int h = 0; h < R / 4; h++) {
-                const float ws[4] = {wcur[h].x, wcur[h].y, wcur[h].z, wcur[h].w};
+                for (int h = 0; h < R / 4; h++) wnext[h] = __ldg(wp + h);
+                issue((u + D - 1) % D);  // into the slot read one round ago
+                asm volatile("cp.async.wait_group %0;" ::"n"(D - 1) : "memory");
+                if (r0 + u < BB) {  // (uniform)
+                    const float4 v = ring[u * kBandThreads];
 #pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    float4 &t = a[4 * h + i];
-                    t.x = fmaf(ws[i], v.x, t.x); t.y = fmaf(ws[i], v.y, t.y);
-                    t.z = fmaf(ws[i], v.z, t.z); t.w = fmaf(ws[i], v.w, t.w);
+                    for (int h = 0; h < R / 4; h++) {
+                        const float ws[4] = {wcur[h].x, wcur[h].y, wcur[h].z, wcur[h].w};
+#pragma unroll
+                        for (int i = 0; i < 4; i++) {
+                            float4 &t = a[4 * h + i];
+                            t.x = fmaf(ws[i], v.x, t.x); t.y = fmaf(ws[i], v.y, t.y);
+                            t.z = fmaf(ws[i], v.z, t.z); t.w = fmaf(ws[i], v.w, t.w);
+                        }
+                    }
                 }
-                wcur[h] = wnext[h];
+#pragma unroll
+                for (int h = 0; h < R / 4; h++) wcur[h] = wnext[h];
             }
         }
         asm volatile("cp.async.wait_group 0;" ::: "memory");
