@@ -5,14 +5,18 @@
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
 
 A step = one pass of the hot path (sift3d_detect_keypoints + sift3d_extract_descriptors)
-over one synthetic 256^3 "MRI-like" volume (BASELINE.json configs[1]) per GPU. With N > 1
-every rank owns one GPU and its own volumes (configs[3]: whole volumes per GPU, no data-path
-collective), so scaling is "weak" and `value` = N * 256^3 * K / max-over-ranks time.
+over a batch of P synthetic 256^3 "MRI-like" volumes (BASELINE.json configs[1]) per GPU: P
+independent pipelines ($SIFT3D_BENCH_PIPELINES, default 4: detector + stream + pyramid each)
+driven by the C library's batch call, one volume per pipeline and step. With N > 1 every rank
+owns one GPU and its own volumes (configs[3]: whole volumes per GPU, no data-path collective),
+so scaling is "weak" and `value` = N * P * 256^3 * K / max-over-ranks time.
 
   value        inputs resident in HBM before the timed region (sift3d_image_make_resident),
-               timed with CUDA events on the library's stream
-  e2e          same call sequence with HOST (page-locked) image buffers: the 64 MiB upload,
-               the candidate download and the descriptor download are inside the timed region
+               timed with CUDA events on the library's stream, device idle at both marks
+  e2e          the same batch call with HOST (page-locked) image buffers: every 64 MiB upload,
+               candidate download and descriptor download is inside the timed region
+  single_pipeline / single_volume_latency_ms   one pipeline alone (resident) / one volume at a
+               time from the host: what a caller with one detector and no batch sees
   roofline     the blur (octave-0 Gaussian levels): 8 B per voxel per level / CUDA-event time
   cpu_baseline the unmodified reference (oracle/_ref) on this box's host cores, bounded sample
 
@@ -212,17 +216,41 @@ def run_product_arm(args):
     if s3.cuda_device_count() <= local:
         raise SystemExit("bench.py: no CUDA device for this rank; the product has no CPU path")
 
-    det = s3.Detector(local)
+    # P independent pipelines (detector + stream + pyramid) per GPU, each on a host thread of the
+    # C library (sift3d_detect_describe_batch: volume v on detector v % P). One pipeline leaves
+    # the device idle in its launch gaps, in the tail of the descriptor kernel and -- with host
+    # inputs -- during its upload; the kernels of the other pipelines fill those holes.
+    P = max(1, int(os.environ.get("SIFT3D_BENCH_PIPELINES", "4")))
+    dets = [s3.Detector(local) for _ in range(P)]
+    det = dets[0]
     mode = "exact (0 ULP vs the reference)" if det.exact() else \
         "fast (one FFMA per tap; voxels within 1e-5 of the level's max-abs)"
-    images = []
-    for i in range(NUM_INPUTS):
-        im = s3.Image(DIM, DIM, DIM)
-        make_volume(rank * NUM_INPUTS + i, out=im.array)
-        images.append(im)
-    kp, ds = s3.KeypointStore(), s3.DescriptorStore()
+    # every pipeline rotates through its own copies of the NUM_INPUTS distinct volumes (an image
+    # object carries its upload state, so pipelines do not share them)
+    pools = []
+    for p_ in range(P):
+        pool = []
+        for i in range(NUM_INPUTS):
+            im = s3.Image(DIM, DIM, DIM)
+            if p_ == 0:
+                make_volume(rank * NUM_INPUTS + i, out=im.array)
+            else:
+                np.copyto(im.array, pools[0][i].array)
+            pool.append(im)
+        pools.append(pool)
+    images = pools[0]
+    kps = [s3.KeypointStore() for _ in range(P)]
+    dss = [s3.DescriptorStore() for _ in range(P)]
+    kp, ds = kps[0], dss[0]
 
-    def step(i):
+    def run_batch(nsteps, first=0):
+        """nsteps steps = nsteps volumes on each of the P pipelines, one C call."""
+        n = nsteps * P
+        ims = [pools[v % P][(first + v // P) % NUM_INPUTS] for v in range(n)]
+        s3.detect_describe_batch(dets, ims, kps=[kps[v % P] for v in range(n)],
+                                 dss=[dss[v % P] for v in range(n)])
+
+    def step(i):  # one volume on pipeline 0 alone (latency, profiling pass)
         det.detect(images[i % NUM_INPUTS], kp)
         if len(kp):
             det.extract(kp, ds)
@@ -232,31 +260,35 @@ def run_product_arm(args):
             dist.barrier()
             import torch
             torch.cuda.synchronize()
-        s3.libcuda().sift3d_cuda_synchronize(det.ctx)
+        for d in dets:
+            s3.libcuda().sift3d_cuda_synchronize(d.ctx)
 
-    def timed(nsteps, slot_a, slot_b, collect_blur, drain=None):
-        """K steps bracketed by barrier + synchronize; CUDA-event time, max over ranks.
-        `drain(K)` runs before the closing mark (the pipelined arm waits there for the upload
-        its last step started, so that K whole uploads lie inside the timed region)."""
+    def timed(nsteps, slot_a, slot_b, batch, collect_blur=False):
+        """K steps bracketed by barrier + synchronize; CUDA-event time, max over ranks. The
+        marks are recorded on pipeline 0's stream with the device idle on both sides (every
+        pipeline's last call has returned its results to the host)."""
         blur = {}
         barrier()
-        l0 = det.launch_count()
+        l0 = sum(d.launch_count() for d in dets)
         t0 = time.perf_counter()
         det.mark(slot_a)
-        for i in range(nsteps):
-            step(i)
-            if collect_blur:
-                for s in range(-1, 5):
-                    ms, n = det.blur_ms(0, s)
-                    acc = blur.setdefault(s, [0.0, n])
-                    acc[0] += ms
-        if drain is not None:
-            drain(nsteps)
+        if batch:
+            run_batch(nsteps)
+        else:
+            for i in range(nsteps):
+                step(i)
+                if collect_blur:
+                    for s in range(-1, 5):
+                        ms, n = det.blur_ms(0, s)
+                        acc = blur.setdefault(s, [0.0, n])
+                        acc[0] += ms
+        for d in dets[1:]:
+            s3.libcuda().sift3d_cuda_synchronize(d.ctx)
         det.mark(slot_b)
         barrier()
         wall = time.perf_counter() - t0
         ms = det.elapsed_ms(slot_a, slot_b)
-        launches = det.launch_count() - l0
+        launches = sum(d.launch_count() for d in dets) - l0
         if dist is not None:
             import torch
             t = torch.tensor([ms, wall * 1e3], device="cuda", dtype=torch.float64)
@@ -265,61 +297,42 @@ def run_product_arm(args):
         return ms, wall, launches, blur
 
     # ---- device-resident arm ----
-    for im in images:
-        im.make_resident(local)
-    for i in range(max(args.warmup, 3)):
-        step(i)
+    for pool in pools:
+        for im in pool:
+            im.make_resident(local)
+    run_batch(max(args.warmup, 3))
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ms, wall, launches, _ = timed(args.steps, 0, 1, False)
+    ms, wall, launches, _ = timed(args.steps, 0, 1, True)
     clocks = sampler.stop() if rank == 0 else None
-    stage = det.timings()
     ncand = len(det.candidates())
     nkeys = len(kp)
-    # per-level blur times (the roofline kernel) from a pass of its own, with the per-blur
-    # event pairs switched on: same schedule, same inputs, not part of the headline timing
+    # one pipeline alone: stage times and the per-level blur times (the roofline kernel) with
+    # the per-blur event pairs switched on -- same inputs, not part of the headline timing
+    for i in range(2):
+        step(i)
+    s_ms, _, _, _ = timed(args.steps, 6, 7, False)
+    stage = det.timings()
     det.set_profiling(True)
     step(0)
-    _, _, _, blur = timed(args.steps, 4, 5, True)
+    _, _, _, blur = timed(args.steps, 4, 5, False, collect_blur=True)
     det.set_profiling(False)
 
     # ---- end-to-end arm: host buffers, copies inside the timed region ----
-    for im in images:
-        im.make_resident(-1)
+    for pool in pools:
+        for im in pool:
+            im.make_resident(-1)
     for i in range(2):
         step(i)
-    # (a) one volume at a time: upload, detect, describe, strictly in sequence (latency)
+    # (a) one volume at a time on one pipeline: upload, detect, describe, strictly in sequence
     l_ms, _, _, _ = timed(args.steps, 2, 3, False)
     e_stage = det.timings()
-    # (b) a stream of volumes through the public API: the upload of volume i+1 is started
-    # (sift3d_image_prefetch, page-locked host buffer, copy stream) before detect(i) is
-    # called, so it overlaps the kernels of volume i. Every step still copies its whole
-    # input host->device and its results device->host inside the timed region: K steps,
-    # K uploads (the first step consumes the upload started by the last warm-up step, the
-    # last step starts the one the next step would consume).
-    def step(i):  # noqa: F811 - same sequence, with the next inputs in flight
-        # Uploads run two volumes ahead and are started between detect and extract: an upload
-        # first rides under the single long descriptor kernel and has a whole further step to
-        # finish, so it is never waited for even when 8 ranks share the host's memory and PCIe
-        # bandwidth (at N = 8 a 64 MiB upload takes longer than the descriptor kernel). Started
-        # right before detect it would slow detect's launches down (PCIe traffic in front of
-        # the command fetches: +0.2 .. 0.35 ms per step).
-        det.detect(images[i % NUM_INPUTS], kp)
-        images[(i + 2) % NUM_INPUTS].prefetch(local)
-        if len(kp):
-            det.extract(kp, ds)
-
-    images[0].prefetch(local)
-    images[1].prefetch(local)
-    for i in range(NUM_INPUTS):
-        step(i)
-
-    def drain(k):
-        images[k % NUM_INPUTS].prefetch_wait()
-        images[(k + 1) % NUM_INPUTS].prefetch_wait()
-
-    e_ms, e_wall, _, _ = timed(args.steps, 2, 3, False, drain=drain)
+    # (b) the public batch call on host images: every volume is copied host->device (the worker
+    # of a pipeline starts the upload of its next volume between detect and extract of the
+    # current one, sift3d_image_prefetch) and its results device->host inside the timed region
+    run_batch(2)
+    e_ms, e_wall, _, _ = timed(args.steps, 2, 3, True)
 
     # ---- config 5 at N > 1: ONE 1024^3 volume z-slab sharded over the N GPUs of this box by
     # rank 0's process (sift3d_detect_describe_sharded: one host thread per device, halo
@@ -366,27 +379,33 @@ def run_product_arm(args):
     if os.path.exists(tp):
         tj = json.load(open(tp))
         traffic, traffic_src = tj.get("dram_bytes_per_blur"), tj.get("source")
-    value = world * NVOX * args.steps / (ms * 1e-3)
-    e2e = world * NVOX * args.steps / (e_ms * 1e-3)
+    value = world * P * NVOX * args.steps / (ms * 1e-3)
+    e2e = world * P * NVOX * args.steps / (e_ms * 1e-3)
     line = {
         "metric": "voxels/sec (256^3 detect+describe)", "value": value, "unit": "voxels/s",
         "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "blur_arithmetic": mode, "volumes_per_gpu_per_step": 1,
-                   "parallelism": f"one volume per GPU x{world}, no data-path collective",
+        "config": {"workload": WORKLOAD, "blur_arithmetic": mode, "volumes_per_gpu_per_step": P,
+                   "parallelism": f"{P} independent pipelines (detector, stream, pyramid) per GPU x{world} "
+                                  "GPUs, one volume per pipeline and step, no data-path collective",
                    "l2": f"{NUM_INPUTS} rotating inputs (256 MiB) and a 0.9 GB pyramid rewritten "
                          "every step: working set > 126 MB L2",
                    "candidates": ncand, "keypoints": nkeys},
         "wall_ms_per_step": 1e3 * wall / args.steps,
+        "ms_per_volume": ms / args.steps / P,
+        "single_pipeline": {"ms_per_volume": s_ms / args.steps,
+                            "voxels_per_s": world * NVOX * args.steps / (s_ms * 1e-3),
+                            "stage_ms": stage},
         "stage_ms": stage,
         "e2e": {"value": e2e, "unit": "voxels/s", "ms_per_step": e_ms / args.steps,
-                "mode": "stream of volumes: the upload of volume i+2 (sift3d_image_prefetch) is started "
-                        "during step i; every step uploads one whole input and downloads its "
-                        "results inside the timed region (K steps, K uploads)",
+                "ms_per_volume": e_ms / args.steps / P,
+                "mode": f"sift3d_detect_describe_batch on page-locked HOST images, {P} pipelines per GPU: "
+                        "every volume is uploaded and its results downloaded inside the timed region "
+                        f"(K steps, {P} K uploads per GPU)",
                 "single_volume_latency_ms": l_ms / args.steps,
-                "h2d_bytes_per_step": NVOX * 4 + nkeys * 96,
-                "d2h_bytes_per_step": ncand * 88 + nkeys * 768 * 4 + 64 * 4,
+                "h2d_bytes_per_step": P * (NVOX * 4 + nkeys * 96),
+                "d2h_bytes_per_step": P * (ncand * 88 + nkeys * 768 * 4 + 64 * 4),
                 "stage_ms": e_stage},
         "gpu_launches": launches,
         "clocks": clocks,
@@ -395,7 +414,8 @@ def run_product_arm(args):
                      "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "peak_source": peak_src, "timed": "CUDA events per blur in a separate pass of "
-                     f"{args.steps} steps after the headline timing (same concurrent schedule)",
+                     f"{args.steps} steps of ONE pipeline after the headline timing (the detect's own "
+                     "concurrent schedule of streams; no second pipeline on the device)",
                      "algorithmic_bytes_per_launch": 8 * NVOX, "per_level": per_level},
         # SIFT3D_BENCH_NO_CPU=1: tuning runs only (the line is then incomplete by contract)
         # (rank 0 at N=1 only: at N>1 the reference arm carries the CPU number)

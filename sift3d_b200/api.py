@@ -537,13 +537,15 @@ class Detector:
             pass
 
 
-def detect_describe_batch(detectors, images, describe=True):
+def detect_describe_batch(detectors, images, describe=True, kps=None, dss=None):
     """sift3d_detect_describe_batch: volume i on detector i % len(detectors), one host thread
-    per detector inside the C library. Returns (keypoint stores, descriptor stores)."""
+    per detector inside the C library. Returns (keypoint stores, descriptor stores). `kps` /
+    `dss`: stores to fill (one per volume; a store may repeat for volumes of the same detector,
+    which run in sequence -- it then holds the last of them)."""
     L = lib()
     n = len(images)
-    kps = [KeypointStore() for _ in range(n)]
-    dss = [DescriptorStore() for _ in range(n)] if describe else []
+    kps = [KeypointStore() for _ in range(n)] if kps is None else kps
+    dss = ([DescriptorStore() for _ in range(n)] if dss is None else dss) if describe else []
     vp = C.c_void_p
     a_det = (vp * len(detectors))(*[d.handle for d in detectors])
     a_im = (vp * max(n, 1))(*[im.handle for im in images])

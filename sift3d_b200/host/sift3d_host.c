@@ -297,6 +297,8 @@ int sift3d_image_make_resident(sift3d_image *im, int device) {
 int sift3d_image_prefetch(sift3d_image *im, int device) {
     if (im == NULL || device < 0)
         return SIFT3D_FAILURE;
+    if (im->dev != NULL && im->dev_id == device)
+        return SIFT3D_SUCCESS; /* a resident copy is what the detect will read: nothing to upload */
     im->up = sift3d_cuda_upload_begin(device, im->data, im->size, im->up);
     im->up_pending = im->up != NULL;
     return im->up != NULL ? SIFT3D_SUCCESS : SIFT3D_FAILURE;

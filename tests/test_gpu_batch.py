@@ -61,3 +61,31 @@ def test_upstream_cased_aliases():
     assert np.array_equal(kp.records()["R"], keys["R"])
     assert np.array_equal(ds.to_matrix().view(np.uint32), desc.view(np.uint32))
     det.close()
+
+
+def test_four_pipelines_on_one_device_resident_inputs_and_reused_stores():
+    """bench.py's pattern: P detectors on ONE device, images resident in HBM (the workers'
+    sift3d_image_prefetch is then a no-op), every pipeline filling its own store again and again:
+    the store of a pipeline ends up with its LAST volume, equal to the one-volume calls."""
+    import sift3d_b200 as s3
+    from sift3d_b200.synth import synth_volume
+    P, rounds = 4, 3
+    units = (1.0, 1.0, 1.0)
+    vols = [synth_volume(64, 56, 48, num_blobs=40, seed=300 + i, flags=3) for i in range(P * rounds)]
+    images = [s3.Image.from_array(v, units) for v in vols]
+    for im in images:
+        im.make_resident(0)
+    dets = [s3.Detector(0) for _ in range(P)]
+    kps = [s3.KeypointStore() for _ in range(P)]
+    dss = [s3.DescriptorStore() for _ in range(P)]
+    n = P * rounds
+    s3.detect_describe_batch(dets, images, kps=[kps[v % P] for v in range(n)], dss=[dss[v % P] for v in range(n)])
+    for p in range(P):
+        keys, desc = _single(vols[(rounds - 1) * P + p], units)
+        got = kps[p].records()
+        assert len(got) == len(keys) and len(keys) > 0
+        for f in keys.dtype.names:
+            assert np.array_equal(got[f], keys[f]), (p, f)
+        assert np.array_equal(dss[p].to_matrix().view(np.uint32), desc.view(np.uint32)), p
+    for d in dets:
+        d.close()
