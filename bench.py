@@ -191,7 +191,7 @@ def run_reference_arm(args):
         "unit": "voxels/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": warm,
         "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": sample_desc},
+        "config": {"workload": WORKLOAD, "volumes_per_step": 1, "sample": sample_desc},
         "cpu_baseline": {"value": value, "unit": "voxels/s", "cores": cpu_threads(), "kind": kind,
                          "sample": sample_desc},
         "e2e": {"value": value, "unit": "voxels/s", "h2d_bytes_per_step": 0,
