@@ -30,6 +30,10 @@ import sys
 import threading
 import time
 
+# many streams per device (octave streams of every pipeline, uploads): all the hardware queues the
+# driver offers; read at context creation, so set before anything initialises CUDA
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

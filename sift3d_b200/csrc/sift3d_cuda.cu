@@ -1280,17 +1280,45 @@ struct sift3d_cuda_upload {
     int device = 0;
     void *d = nullptr;
     size_t bytes = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;  // the device's upload stream (shared, not owned)
     cudaEvent_t done = nullptr;
 };
+
+// One upload stream per device, shared by every image: host-to-device copies run one after
+// another on the copy engine anyway, and a stream per image (16 of them under bench.py's four
+// pipelines, next to 7 streams per detector) made the streams share the device's hardware
+// queues -- an upload then sat behind another pipeline's kernels (seen as a bimodal e2e time).
+static cudaStream_t upload_stream(int device) {
+    static std::mutex mu;
+    static cudaStream_t streams[SIFT3D_CUDA_MULTI_MAX_DEVICES] = {};
+    if (device < 0 || device >= SIFT3D_CUDA_MULTI_MAX_DEVICES) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!streams[device]) {
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        if (cudaStreamCreateWithPriority(&streams[device], cudaStreamNonBlocking, hi) != cudaSuccess) {
+            cudaGetLastError();
+            streams[device] = nullptr;
+        }
+    }
+    return streams[device];
+}
+
+// The library runs many streams per device (octave streams of every detector, uploads): ask
+// for the maximum number of hardware queues unless the caller chose a value. Read by the
+// driver when the CUDA context is created, so it is set when the library is loaded.
+__attribute__((constructor)) static void s3d_more_hardware_queues() {
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", /* overwrite */ 0);
+}
 
 void sift3d_cuda_upload_free(sift3d_cuda_upload *up) {
     if (!up) return;
     cudaSetDevice(up->device);
-    if (up->stream) cudaStreamSynchronize(up->stream);
+    if (up->done) {
+        cudaEventSynchronize(up->done);
+        cudaEventDestroy(up->done);
+    }
     if (up->d) cudaFree(up->d);
-    if (up->done) cudaEventDestroy(up->done);
-    if (up->stream) cudaStreamDestroy(up->stream);
     delete up;
 }
 
@@ -1314,12 +1342,13 @@ sift3d_cuda_upload *sift3d_cuda_upload_begin(int device, const float *host, size
     }
     const size_t bytes = count * sizeof(float);
     bool ok = cudaSetDevice(device) == cudaSuccess;
-    if (ok && fresh)
-        ok = cudaStreamCreateWithFlags(&up->stream, cudaStreamNonBlocking) == cudaSuccess &&
-             cudaEventCreateWithFlags(&up->done, cudaEventDisableTiming) == cudaSuccess;
+    if (ok && fresh) {
+        up->stream = upload_stream(device);
+        ok = up->stream != nullptr && cudaEventCreateWithFlags(&up->done, cudaEventDisableTiming) == cudaSuccess;
+    }
     if (ok && up->bytes < bytes) {
         if (up->d) {
-            cudaStreamSynchronize(up->stream);
+            cudaEventSynchronize(up->done);
             cudaFree(up->d);
             up->d = nullptr;
             up->bytes = 0;
