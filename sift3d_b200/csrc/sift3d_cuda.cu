@@ -1318,7 +1318,7 @@ void sift3d_cuda_upload_free(sift3d_cuda_upload *up) {
         cudaEventSynchronize(up->done);
         cudaEventDestroy(up->done);
     }
-    if (up->d) cudaFree(up->d);
+    if (up->d) cudaFreeAsync(up->d, up->stream);
     delete up;
 }
 
@@ -1347,13 +1347,14 @@ sift3d_cuda_upload *sift3d_cuda_upload_begin(int device, const float *host, size
         ok = up->stream != nullptr && cudaEventCreateWithFlags(&up->done, cudaEventDisableTiming) == cudaSuccess;
     }
     if (ok && up->bytes < bytes) {
+        // stream-ordered allocation: cudaMalloc / cudaFree wait for an idle device, which other
+        // pipelines of the process may not offer for a long time (seen as 60 ms stalls)
         if (up->d) {
-            cudaEventSynchronize(up->done);
-            cudaFree(up->d);
+            cudaFreeAsync(up->d, up->stream);
             up->d = nullptr;
             up->bytes = 0;
         }
-        ok = cudaMalloc(&up->d, bytes) == cudaSuccess;
+        ok = cudaMallocAsync(&up->d, bytes, up->stream) == cudaSuccess;
         if (ok) up->bytes = bytes;
     }
     ok = ok && cudaMemcpyAsync(up->d, host, bytes, cudaMemcpyHostToDevice, up->stream) == cudaSuccess &&

@@ -10,6 +10,7 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    config.addinivalue_line("markers", "fast_mode: the library's default blur arithmetic (test_gpu_sharded.py)")
 
 
 def _have_gpu():

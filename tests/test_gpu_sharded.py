@@ -10,10 +10,10 @@ import pytest
 pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
 
 
-def _single(vol, units, params):
+def _single(vol, units, params, exact=True):
     import sift3d_b200 as s3
     det = s3.Detector(0)
-    det.set_exact(True)
+    det.set_exact(exact)
     for k, v in (params or {}).items():
         assert getattr(det, f"set_{k}")(v) == 0
     kp = det.detect(s3.Image.from_array(vol, units))
@@ -44,8 +44,12 @@ def _sharded(vol, units, params, world, octaves):
 
 
 @pytest.fixture(autouse=True)
-def _exact_mode(monkeypatch):
-    monkeypatch.setenv("SIFT3D_CUDA_EXACT", "1")  # contexts made by the library read it at creation
+def _exact_mode(monkeypatch, request):
+    # contexts made by the library read the variable at creation
+    if "fast_mode" in request.keywords:
+        monkeypatch.delenv("SIFT3D_CUDA_EXACT", raising=False)
+    else:
+        monkeypatch.setenv("SIFT3D_CUDA_EXACT", "1")
 
 
 @pytest.mark.parametrize("world,dims,octaves,units,params", [
@@ -69,4 +73,33 @@ def test_sharded_equals_single_device(world, dims, octaves, units, params):
     for f in keys.dtype.names:
         assert np.array_equal(got_keys[f], keys[f]), f
     assert np.array_equal(got_desc.view(np.uint32), desc.view(np.uint32))
+    assert tm["exchanged_mib"] > 0
+
+
+@pytest.mark.fast_mode
+@pytest.mark.parametrize("world,dims,octaves,units", [
+    (2, (96, 96, 320), 2, (1.0, 1.0, 1.0)),      # fused kernels on the slabs, banded kernels below
+    (4, (64, 64, 640), 2, (1.0, 1.0, 1.0)),
+    (2, (64, 64, 320), 1, (0.9, 0.9, 1.4)),      # banded kernels with a z origin (cut faces)
+])
+def test_sharded_fast_mode_matches_single_device(world, dims, octaves, units):
+    """The default (fast) blur arithmetic on the slabs: one FFMA per tap in the fused kernels, the
+    banded kernels with band tables built for a slab's z origin. The slab kernels see other tile
+    and chunk shapes than the whole-volume ones, so the comparison is the fast mode's own:
+    same keypoints (>= 99 % matched by position and scale) and descriptors of cosine >= 0.999."""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(__file__))
+    import parity
+    from sift3d_b200.synth import synth_volume
+    nx, ny, nz = dims
+    vol = synth_volume(nx, ny, nz, num_blobs=nx * ny * nz // 4096, seed=77 + nz, flags=3)
+    keys, desc = _single(vol, units, None, exact=False)
+    got_keys, got_desc, tm = _sharded(vol, units, None, world, octaves)
+    assert len(keys) > 10
+    pairs = parity.match_keypoints(keys, got_keys)
+    assert len(pairs) >= 0.99 * len(keys) and abs(len(got_keys) - len(keys)) <= 0.01 * len(keys) + 1
+    iw = [i for i, _ in pairs]
+    ig = [j for _, j in pairs]
+    cos = parity.cosine_rows(got_desc[ig, 3:], desc[iw, 3:])
+    assert cos.min() >= parity.DESC_COS_MIN, cos.min()
     assert tm["exchanged_mib"] > 0
