@@ -9,6 +9,7 @@
 //   normalize_desc          :1402-1429  L2 norm in double, + DBL_EPSILON
 //   extract_descrip         :1442-1536  window loop, rotate, weight, accumulate,
 //                                       normalise / clamp to 0.2*128/768 / normalise
+#include <cooperative_groups.h>
 #include <float.h>
 #include <math.h>
 
@@ -508,8 +509,13 @@ static int upload_cell_order() {
     });
 }
 
+// `split` CTAs (a thread-block cluster) share one keypoint when there are fewer keypoints than CTA
+// slots (the CLI's 100 strongest, small octaves of a slab): CTA r of the cluster takes the cells
+// r, r + split, ... of the centre-first order, rank 0 adds the others' block histograms through
+// distributed shared memory. The histograms are integers and every cell's sum is formed by one
+// warp in a fixed order, so the descriptor has the same bits for every split.
 __global__ void __launch_bounds__(kDescThreads)
-descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ desc_out) {
+descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restrict__ desc_out, int split) {
     extern __shared__ __align__(16) float wacc_all[];  // [warps][kCellBins][32]
     __shared__ unsigned hlo[kPadNumel];
     __shared__ int hhi[kPadNumel];
@@ -523,8 +529,8 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
     __shared__ double norm_sh;
     __shared__ int next_cell;
     __shared__ unsigned char rowlane_all[kDescThreads];  // per warp: lane of the k-th non-empty row
-    const int ki = blockIdx.x;
-    if (ki >= n) return;
+    const int ki = blockIdx.x / split, part = blockIdx.x - ki * split;
+    if (ki >= n) return;  // (uniform over a cluster)
     const DescJob J = jobs[ki];
     const int tid = threadIdx.x;
     const int lane = tid & 31, warp = tid >> 5;
@@ -553,7 +559,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         for (int k = 0; k < 12; k++)
             sfast[tid * 12 + k] = (k & 3) == 3 ? __int_as_float(c_mesh.idx[f][k >> 2] * 32) : c_mesh.minv[f][k];
     }
-    if (tid == 0) next_cell = 0;
+    if (tid == 0) next_cell = part;
 
     const float *__restrict__ img = J.img;
     const int nx = J.nx, ny = J.ny, nz = J.nz;
@@ -598,7 +604,7 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
 
     for (;;) {
         int ci = 0;
-        if (lane == 0) ci = atomicAdd(&next_cell, 1);
+        if (lane == 0) ci = atomicAdd(&next_cell, split);
         ci = __shfl_sync(full, ci, 0);
         if (ci >= 64) break;
         const int cell = c_cell_order[ci];
@@ -938,6 +944,24 @@ descriptor_cell_kernel(const DescJob *__restrict__ jobs, int n, float *__restric
         __syncwarp();
     }
     __syncthreads();
+    if (split > 1) {
+        namespace cg = cooperative_groups;
+        cg::cluster_group cluster = cg::this_cluster();
+        cluster.sync();  // every CTA of the keypoint has finished its cells
+        if (part == 0) {
+            for (int r = 1; r < split; r++) {
+                const unsigned *rlo = cluster.map_shared_rank(hlo, r);
+                const int *rhi = cluster.map_shared_rank(hhi, r);
+                for (int i = tid; i < kPadNumel; i += kDescThreads) {
+                    hlo[i] += rlo[i];
+                    hhi[i] += rhi[i];
+                }
+            }
+        }
+        cluster.sync();  // the others' shared memory stays alive until rank 0 has read it
+        if (part != 0) return;
+        __syncthreads();
+    }
     float *hist = wacc_all;  // the lane copies are dead: reuse (keeps two CTAs per SM in 228 KB)
     for (int i = tid; i < kDescNumel; i += kDescThreads) {
         const int bin = i % kVerts, cell = i / kVerts;
@@ -1019,7 +1043,28 @@ int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_ro
                 return 0;
             }))
             return -1;
-        descriptor_cell_kernel<<<(unsigned) n, kDescThreads, dyn4, st>>>(d_jobs, n, d_desc);
+        // fewer keypoints than CTA slots (2 per SM): 2 or 4 CTAs per keypoint ($SIFT3D_CUDA_DESC_SPLIT=1|2|4 forces)
+        const char *se = getenv("SIFT3D_CUDA_DESC_SPLIT");  // (read per call: tests switch it)
+        const int split_env = se ? atoi(se) : 0;
+        int split = split_env == 1 || split_env == 2 || split_env == 4 ? split_env
+                    : ((long) n * 4 <= 2L * kNumSMs ? 4 : ((long) n * 2 <= 2L * kNumSMs ? 2 : 1));
+        if (split == 1) {
+            descriptor_cell_kernel<<<(unsigned) n, kDescThreads, dyn4, st>>>(d_jobs, n, d_desc, 1);
+        } else {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned) n * (unsigned) split, 1, 1);
+            cfg.blockDim = dim3(kDescThreads, 1, 1);
+            cfg.dynamicSmemBytes = dyn4;
+            cfg.stream = st;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = (unsigned) split;
+            at[0].val.clusterDim.y = 1;
+            at[0].val.clusterDim.z = 1;
+            cfg.attrs = at;
+            cfg.numAttrs = 1;
+            S3D_CK(cudaLaunchKernelEx(&cfg, descriptor_cell_kernel, d_jobs, n, d_desc, split));
+        }
         if (launches) *launches += 1;
         S3D_CK(cudaGetLastError());
         return 0;

@@ -281,3 +281,25 @@ def test_detector_reuse_mixed_units():
         ig = [j for _, j in pairs]
         np.testing.assert_allclose(keys["R"][ig], want_keys["R"][iw], atol=2e-5)
     d.close()
+
+
+def test_descriptor_cluster_split_is_bit_identical(monkeypatch):
+    """Fewer keypoints than CTA slots: 2 or 4 CTAs (a thread-block cluster) share a keypoint and
+    rank 0 adds their integer block histograms through distributed shared memory -- the
+    descriptors must have the same bits as with one CTA per keypoint."""
+    import sift3d_b200 as s3
+    vol = s3.synth_volume(96, 80, 72, num_blobs=60, seed=4242)
+    det = s3.Detector()
+    kp = det.detect(s3.Image.from_array(vol, (1.0, 1.0, 1.0)))
+    assert 8 <= len(kp) <= 70  # few enough for the 4-way split to be the default
+    out = {}
+    for split in ("1", "2", "4", None):
+        if split is None:
+            monkeypatch.delenv("SIFT3D_CUDA_DESC_SPLIT", raising=False)
+        else:
+            monkeypatch.setenv("SIFT3D_CUDA_DESC_SPLIT", split)
+        out[split] = det.extract(kp).to_matrix().copy()
+    det.close()
+    for split in ("2", "4", None):
+        assert np.array_equal(out[split].view(np.uint32), out["1"].view(np.uint32)), split
+    assert np.abs(out["1"][:, 3:]).max() > 0
