@@ -1043,11 +1043,13 @@ int launch_descriptors(cudaStream_t st, const DescJob *d_jobs, int n, int max_ro
                 return 0;
             }))
             return -1;
-        // fewer keypoints than CTA slots (2 per SM): 2 or 4 CTAs per keypoint ($SIFT3D_CUDA_DESC_SPLIT=1|2|4 forces)
+        // Few keypoints: the kernel lasts as long as its largest keypoint (0.3 - 0.45 ms) however
+        // empty the device is, so keypoints are split over 4 CTAs up to one wave of keypoints (2 CTA
+        // slots per SM) and over 2 up to two waves ($SIFT3D_CUDA_DESC_SPLIT=1|2|4 forces a value)
         const char *se = getenv("SIFT3D_CUDA_DESC_SPLIT");  // (read per call: tests switch it)
         const int split_env = se ? atoi(se) : 0;
         int split = split_env == 1 || split_env == 2 || split_env == 4 ? split_env
-                    : ((long) n * 4 <= 2L * kNumSMs ? 4 : ((long) n * 2 <= 2L * kNumSMs ? 2 : 1));
+                    : (n <= 2 * kNumSMs ? 4 : (n <= 4 * kNumSMs ? 2 : 1));
         if (split == 1) {
             descriptor_cell_kernel<<<(unsigned) n, kDescThreads, dyn4, st>>>(d_jobs, n, d_desc, 1);
         } else {
