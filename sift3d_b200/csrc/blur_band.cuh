@@ -175,10 +175,7 @@ static int get_band(int n_line, int org, float uf, const sift3d_cuda_filter &f, 
             out.w4 = e.d_w; out.bb = e.d_bb; out.BB = e.BB; out.nblk = e.nblk; out.n = e.n;
             return 0;
         }
-    if (cache.size() >= 4096) {
-        S3D_ERR("sift3d_cuda: band table cache full\n");
-        return -1;
-    }
+    if (cache.size() >= 4096) return 1;  // cache full (thousands of shapes in one process): the literal kernels take it
     std::vector<float> wT, w4;
     std::vector<int> base, bb, lo_min, lo_max;
     BandEntry e;
