@@ -65,9 +65,9 @@ def test_blur_vs_reference(det, units, sigma, exact):
         assert rel <= FAST_BLUR_REL_TOL, f"max rel err {rel:.3g}"
 
 
-@pytest.mark.parametrize("dims", [(64, 48, 40), (96, 72, 45), (36, 32, 50), (128, 64, 37)])
+@pytest.mark.parametrize("dims", [(64, 48, 40), (96, 72, 45), (36, 32, 50), (128, 64, 37), (64, 48, 9)])
 @pytest.mark.parametrize("units", [(2, 2, 2), (4, 4, 4), (8, 8, 8), (0.75, 0.75, 1.5), (1.0, 2.0, 0.5),
-                                   (0.9, 0.9, 1.4), (1.3, 0.7, 1.0)])
+                                   (0.9, 0.9, 1.4), (1.3, 0.7, 1.0), (0.25, 0.3, 3.0)])
 @pytest.mark.parametrize("sigma", [0.5387, 1.2263, 2.4525])
 def test_banded_blur_vs_reference(det, dims, units, sigma):
     """Fast mode, general tap spacing (anisotropic units, octaves >= 2): the banded multiply-add
@@ -78,6 +78,11 @@ def test_banded_blur_vs_reference(det, dims, units, sigma):
     rng = np.random.default_rng(int(sigma * 1000) + nx + int(units[0] * 16))
     vol = rng.standard_normal((nz, ny, nx)).astype(np.float32)
     taps = _gauss_taps(sigma)
+    hw = len(taps) // 2
+    if any(int(np.ceil(hw / u)) > n - 2 for u, n in zip(units, dims)):
+        # a mirrored coordinate leaves the line: the reference reads outside it (imutil.c:833-854
+        # mirrors once), there is nothing to compare with
+        pytest.skip("filter reach longer than the line: undefined in the reference")
     want = ref.ref_blur(vol, units, taps)
     assert not det.exact()
     l0 = det.launch_count()
@@ -86,7 +91,7 @@ def test_banded_blur_vs_reference(det, dims, units, sigma):
     rel, _ = parity.level_error(got, want)
     assert rel <= FAST_BLUR_REL_TOL, f"max rel err {rel:.3g}"
     if units != (2, 2, 2):  # (spacing 1/2 has a fused kernel of its own where the shape allows)
-        assert launches == 3
+        assert launches == 3  # (lines shorter than their band still fit one: the band is then the line)
 
 
 @pytest.mark.parametrize("exact", [True, False], ids=["exact", "fast"])
