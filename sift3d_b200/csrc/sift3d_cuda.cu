@@ -113,6 +113,7 @@ struct sift3d_cuda_ctx {
 
     // user marks + per-blur profiling
     cudaEvent_t marks[8] = {};
+    cudaEvent_t sleep_ev = nullptr;     // $SIFT3D_CUDA_BLOCKING_SYNC: the two host waits of a step sleep
     bool profiling = false;
     std::vector<cudaEvent_t> blur_ev;    // 2 per level: [2 * (o * nlev + s + 1)] start, +1 stop
     std::vector<int> blur_launches;      // launches per blur in the last detect
@@ -227,6 +228,7 @@ void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx) {
     ctx->desc_out.release();
     for (int i = 0; i < 8; i++)
         if (ctx->marks[i]) cudaEventDestroy(ctx->marks[i]);
+    if (ctx->sleep_ev) cudaEventDestroy(ctx->sleep_ev);
     for (cudaEvent_t e : ctx->blur_ev) cudaEventDestroy(e);
     if (ctx->h_counts) cudaFreeHost(ctx->h_counts);
     for (int i = 0; i < EV_COUNT; i++)
@@ -254,6 +256,25 @@ void sift3d_cuda_host_free(void *p) {
 // Candidate regions, one per octave: room for 1/32 of the octave's voxels (typical images
 // yield 0.04 - 0.4 %), or for what an earlier detect on this plan was seen to need.
 static void detect_timings(sift3d_cuda_ctx *ctx);
+
+// The host waits at the end of detect and of describe. By default the CUDA runtime spins, which is
+// the lowest latency as long as every waiting thread has a core; with more pipelines than cores
+// in the box (8 ranks x 4 pipelines on 16 hardware threads) the spinning threads take the cores
+// from the ones that have launches and uploads to issue: $SIFT3D_CUDA_BLOCKING_SYNC=1 makes the
+// waits sleep on an event instead.
+static int host_wait(sift3d_cuda_ctx *ctx, cudaStream_t st) {
+    static const bool sleepy = getenv("SIFT3D_CUDA_BLOCKING_SYNC") != nullptr &&
+                               atoi(getenv("SIFT3D_CUDA_BLOCKING_SYNC")) != 0;
+    if (!sleepy) {
+        S3D_CK(cudaStreamSynchronize(st));
+        return 0;
+    }
+    if (!ctx->sleep_ev)
+        S3D_CK(cudaEventCreateWithFlags(&ctx->sleep_ev, cudaEventBlockingSync | cudaEventDisableTiming));
+    S3D_CK(cudaEventRecord(ctx->sleep_ev, st));
+    S3D_CK(cudaEventSynchronize(ctx->sleep_ev));
+    return 0;
+}
 
 static int plan_candidates(sift3d_cuda_ctx *ctx) {
     const int noct = ctx->desc.num_octaves;
@@ -881,7 +902,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     } else if (body()) {
         return -1;
     }
-    S3D_CK(cudaStreamSynchronize(st));
+    if (host_wait(ctx, st)) return -1;
     int total = 0;
     bool overflow = false;
     for (int o = 0; o < noct; o++) {
@@ -1172,7 +1193,7 @@ static int describe_impl(sift3d_cuda_ctx *ctx, const sift3d_cuda_keypoint *keys,
         S3D_CK(cudaMemcpyAsync(desc, d_out, sizeof(float) * SIFT3D_CUDA_DESC_NUMEL * (size_t) num,
                                cudaMemcpyDeviceToHost, st));
     S3D_CK(cudaEventRecord(ctx->dv[DV_D2H], st));
-    S3D_CK(cudaStreamSynchronize(st));
+    if (host_wait(ctx, st)) return -1;
     float ms;
     cudaEventElapsedTime(&ms, ctx->dv[DV_START], ctx->dv[DV_H2D]); ctx->tm.desc_h2d = ms;
     cudaEventElapsedTime(&ms, ctx->dv[DV_H2D], ctx->dv[DV_KERNEL]); ctx->tm.descriptors = ms;
