@@ -398,8 +398,8 @@ def run_product_arm(args):
         "config": {"workload": WORKLOAD, "blur_arithmetic": mode, "volumes_per_gpu_per_step": P,
                    "parallelism": f"{P} independent pipelines (detector, stream, pyramid) per GPU x{world} "
                                   "GPUs, one volume per pipeline and step, no data-path collective",
-                   "l2": f"{NUM_INPUTS} rotating inputs (256 MiB) and a 0.9 GB pyramid rewritten "
-                         "every step: working set > 126 MB L2",
+                   "l2": f"per pipeline {NUM_INPUTS} rotating inputs (256 MiB) and a 0.9 GB pyramid rewritten "
+                         f"every step, {P} pipelines: working set >> 126 MB L2",
                    "candidates": ncand, "keypoints": nkeys},
         "wall_ms_per_step": 1e3 * wall / args.steps,
         "ms_per_volume": ms / args.steps / P,
