@@ -23,6 +23,7 @@ so scaling is "weak" and `value` = N * P * 256^3 * K / max-over-ranks time.
 The reference arm (--impl reference) times the reference's own CPU implementation.
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -388,6 +389,12 @@ def run_product_arm(args):
     if os.path.exists(tp):
         tj = json.load(open(tp))
         traffic, traffic_src = tj.get("dram_bytes_per_blur"), tj.get("source")
+        # the figure belongs to one version of the kernel: stale once its source has changed
+        ks = os.path.join(ROOT, tj.get("kernel_source", ""))
+        if not tj.get("kernel_source_sha256") or not os.path.isfile(ks) or \
+                hashlib.sha256(open(ks, "rb").read()).hexdigest() != tj["kernel_source_sha256"]:
+            traffic, traffic_src = None, "profiles/r2_blur_traffic.json is older than the kernel source (re-run " \
+                                         "tools/make_blur_traffic.py on a fresh ncu capture)"
     value = world * P * NVOX * args.steps / (ms * 1e-3)
     e2e = world * P * NVOX * args.steps / (e_ms * 1e-3)
     line = {
