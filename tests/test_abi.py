@@ -163,3 +163,15 @@ def test_fused_blur_chunk_table(tiles, nzr, hw, ncta, top):
     mean = sum(busy) / len(busy)
     assert worst <= mean + 3 * (2 * hw + minlen) + hw + 2, (worst, mean)
     assert L.sift3d_cuda_blur_chunk_table(0, tiles, nzr, hw, top, b and (C.c_int * 2)()) == -1
+
+
+def test_committed_blur_traffic_belongs_to_the_current_kernel():
+    """bench.py's roofline.traffic comes from an ncu capture committed under profiles/; the file
+    names the kernel source it was taken from and that source's hash (bench.py reports null when
+    they differ). Changing the kernel without a fresh capture should be noticed here."""
+    import hashlib
+    import json
+    tj = json.load(open(os.path.join(ROOT, "profiles", "r2_blur_traffic.json")))
+    src = os.path.join(ROOT, tj["kernel_source"])
+    assert hashlib.sha256(open(src, "rb").read()).hexdigest() == tj["kernel_source_sha256"]
+    assert 0.5 * tj["algorithmic_bytes_per_blur"] < tj["dram_bytes_per_blur"] < 2 * tj["algorithmic_bytes_per_blur"]
