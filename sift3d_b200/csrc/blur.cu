@@ -942,7 +942,66 @@ tiny_octaves_kernel(const TinyChainParams P) {
                 const int sh = O.sh[axis];
                 const int len = axis == 0 ? nx : (axis == 1 ? ny : nz);
                 const size_t stride = axis == 0 ? 1 : (axis == 1 ? (size_t) nx : (size_t) nx * ny);
-                if (vec4 && axis > 0) {
+                if (P.banded) {
+                    // fast mode: at these octaves the taps are a fraction of a voxel apart (2^-4 and
+                    // below), so a 17-tap filter reads 3 - 5 samples: the banded form is a handful of
+                    // multiply-adds per voxel instead of 17 interpolated taps
+                    // (the chain is a sequence of ~30 dependent passes of ~4 items per thread: what
+                    // counts is the latency of one item, so its loads are issued together)
+                    const TinyBand B = P.band[t][s][axis];
+                    if (nx % 4 == 0) {
+                        // item = four x-adjacent voxels. The whole chain runs on ONE SM (1024 threads,
+                        // ~40 dependent phases), so a phase costs its instruction count: per four
+                        // voxels one index computation, BB weight loads and BB 16-byte samples
+                        // (y, z) or BB scalar samples against 16-byte weights (x).
+                        const float4 *__restrict__ w4 = reinterpret_cast<const float4 *>(B.w);
+                        for (int i4 = tid; i4 < n / 4; i4 += kTinyThreads) {
+                            const int i = 4 * i4;
+                            const int yz = i / nx, x = i - yz * nx;
+                            const int z = yz / ny, y = yz - z * ny;
+                            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (axis == 0) {
+                                const int k = x >> 2;
+                                const float *__restrict__ q = src + (size_t) (i - x) + (size_t) B.bb[k];
+                                const float4 *__restrict__ wk = w4 + k;
+#pragma unroll 4
+                                for (int r = 0; r < B.BB; r++) {
+                                    const float4 wr = __ldg(wk + (size_t) r * B.nblk);
+                                    const float v = q[r];
+                                    acc.x = fmaf(wr.x, v, acc.x); acc.y = fmaf(wr.y, v, acc.y);
+                                    acc.z = fmaf(wr.z, v, acc.z); acc.w = fmaf(wr.w, v, acc.w);
+                                }
+                            } else {
+                                const int p = axis == 1 ? y : z;
+                                const int k = p >> 2;
+                                const float *__restrict__ q = src + ((size_t) i - (size_t) p * stride) + (size_t) B.bb[k] * stride;
+                                const float *__restrict__ wq = B.w + (size_t) k * 4 + (p & 3);
+#pragma unroll 4
+                                for (int r = 0; r < B.BB; r++) {
+                                    const float wv = __ldg(wq + (size_t) r * B.nblk * 4);
+                                    const float4 v = *reinterpret_cast<const float4 *>(q + (size_t) r * stride);
+                                    acc.x = fmaf(wv, v.x, acc.x); acc.y = fmaf(wv, v.y, acc.y);
+                                    acc.z = fmaf(wv, v.z, acc.z); acc.w = fmaf(wv, v.w, acc.w);
+                                }
+                            }
+                            *reinterpret_cast<float4 *>(dst + i) = acc;
+                        }
+                    } else {
+                        for (int i = tid; i < n; i += kTinyThreads) {
+                            const int yz = i / nx, x = i - yz * nx;
+                            const int z = yz / ny, y = yz - z * ny;
+                            const int p = axis == 0 ? x : (axis == 1 ? y : z);
+                            const int k = p >> 2, ii = p & 3;
+                            const float *__restrict__ q = src + ((size_t) i - (size_t) p * stride) + (size_t) B.bb[k] * stride;
+                            const float *__restrict__ wq = B.w + (size_t) k * 4 + ii;
+                            float acc = 0.0f;
+#pragma unroll 4
+                            for (int r = 0; r < B.BB; r++)
+                                acc = fmaf(__ldg(wq + (size_t) r * B.nblk * 4), q[(size_t) r * stride], acc);
+                            dst[i] = acc;
+                        }
+                    }
+                } else if (vec4 && axis > 0) {
                     // four x-adjacent voxels per item: one coordinate chain, 16-byte accesses
                     for (int i4 = tid; i4 < n / 4; i4 += kTinyThreads) {
                         const int i = 4 * i4;
@@ -976,10 +1035,22 @@ tiny_octaves_kernel(const TinyChainParams P) {
             float *__restrict__ g = O.lvl[s + 1];
             float vmax = 0.0f;
             const bool want_max = O.dogmax[s] != nullptr;
-            for (int i = tid; i < n; i += kTinyThreads) {
-                const float o = nxt[i];
-                g[i] = o;
-                if (want_max) vmax = fmaxf(vmax, fabsf(__fsub_rn(cur[i], o)));
+            if (n % 4 == 0) {
+                for (int i = 4 * tid; i < n; i += 4 * kTinyThreads) {
+                    const float4 o = *reinterpret_cast<const float4 *>(nxt + i);
+                    *reinterpret_cast<float4 *>(g + i) = o;
+                    if (want_max) {
+                        const float4 c = *reinterpret_cast<const float4 *>(cur + i);
+                        vmax = fmaxf(fmaxf(vmax, fmaxf(fabsf(__fsub_rn(c.x, o.x)), fabsf(__fsub_rn(c.y, o.y)))),
+                                     fmaxf(fabsf(__fsub_rn(c.z, o.z)), fabsf(__fsub_rn(c.w, o.w))));
+                    }
+                }
+            } else {
+                for (int i = tid; i < n; i += kTinyThreads) {
+                    const float o = nxt[i];
+                    g[i] = o;
+                    if (want_max) vmax = fmaxf(vmax, fabsf(__fsub_rn(cur[i], o)));
+                }
             }
             if (want_max) {
                 for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
@@ -1027,6 +1098,18 @@ int launch_tiny_octaves(cudaStream_t st, const TinyChainParams &P, uint64_t *lau
     tiny_octaves_kernel<<<1, kTinyThreads, dyn, st>>>(P);
     if (launches) *launches += 1;
     S3D_CK(cudaGetLastError());
+    return 0;
+}
+
+int tiny_band(int n, double unit, const sift3d_cuda_filter &f, TinyBand *out) {
+    const AxisSpec a = axis_spec(n, unit, f.width / 2);
+    BandAxis A;
+    const int r = get_band(n, 0, a.uf, f, 1, 4, A);
+    if (r) return r;
+    out->w = reinterpret_cast<const float *>(A.w4);
+    out->bb = A.bb;
+    out->BB = A.BB;
+    out->nblk = A.nblk;
     return 0;
 }
 

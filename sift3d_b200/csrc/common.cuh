@@ -103,14 +103,25 @@ struct TinyOctave {
     float *lvl[SIFT3D_CUDA_MAX_FILTERS + 1];      // level -1 .. nfilt-1
     float *dogmax[SIFT3D_CUDA_MAX_FILTERS];       // [s]: slot for max|G(s-1) - G(s)| or nullptr
 };
+// Fast mode: one pass of a blur as banded multiply-adds (blur_band.cuh, positions in blocks of 4):
+// out[p] = sum_r w[(r * nblk + p / 4) * 4 + p % 4] * in[bb[p / 4] + r], r < BB.
+struct TinyBand {
+    const float *w;
+    const int *bb;
+    int BB, nblk;
+};
 struct TinyChainParams {
     int noct, nfilt, ds_level;
+    int banded;                                   // fast mode: `band` is filled, the literal taps are not used
+    TinyBand band[kTinyMaxOct][SIFT3D_CUDA_MAX_FILTERS][3];
     const float *taps[SIFT3D_CUDA_MAX_FILTERS];   // filter s: level s-1 -> s
     int hw[SIFT3D_CUDA_MAX_FILTERS];
     TinyOctave oct[kTinyMaxOct];
 };
 int launch_tiny_octaves(cudaStream_t st, const TinyChainParams &P, uint64_t *launches);
 void tiny_axis(int n, double unit, float *uf, int *sh);
+// Host: band of one axis of a tiny octave (0: filled, 1: not representable, -1: error)
+int tiny_band(int n, double unit, const sift3d_cuda_filter &f, TinyBand *out);
 int launch_downsample(cudaStream_t st, const float *src, float *dst, int snx, int sny, int snz,
                       uint64_t *launches);
 int launch_absmax(cudaStream_t st, const float *src, size_t n, float *d_out, uint64_t *launches);

@@ -660,6 +660,8 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         T.noct = noct - tiny_from;
         T.nfilt = nlev - 1;
         T.ds_level = ds_level;
+        static const bool no_band = getenv("SIFT3D_CUDA_NO_BAND") != nullptr;
+        T.banded = !ctx->exact && !no_band && T.noct <= kTinyMaxOct ? 1 : 0;
         for (int i = 0; i < T.nfilt; i++) {
             T.taps[i] = ctx->d_taps(i);
             T.hw[i] = D.octave[i].width / 2;
@@ -673,6 +675,16 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
             tiny_axis(L.ny, L.uy, &O.uf[1], &O.sh[1]);
             tiny_axis(L.nz, L.uz, &O.uf[2], &O.sh[2]);
             for (int i = 0; i <= T.nfilt; i++) O.lvl[i] = ctx->level(o, i - 1).d;
+            if (T.banded) {
+                const double un[3] = {L.ux, L.uy, L.uz};
+                const int dn[3] = {L.nx, L.ny, L.nz};
+                for (int i = 0; i < T.nfilt && T.banded; i++)
+                    for (int a = 0; a < 3 && T.banded; a++) {
+                        const int r = tiny_band(dn[a], un[a], D.octave[i], &T.band[t][i][a]);
+                        if (r < 0) return -1;
+                        if (r > 0) T.banded = 0;  // not representable: the literal chain
+                    }
+            }
             for (int i = 0; i < T.nfilt; i++)
                 O.dogmax[i] = (i - 1 >= 0 && i - 1 < kp)
                                   ? ctx->d_scalar(1 + o * SIFT3D_CUDA_MAX_FILTERS + (i - 1)) : nullptr;
