@@ -852,17 +852,24 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         // (At 256^3 three quarters of the candidates are in octaves >= 1, which finish long
         // before octave 0 -- orienting everything after the last octave cost 0.2 ms.)
         if (o == 0 && mark(ctx->ev[EV_EXTREMA])) return -1;
+        // The octaves of the tiny chain share a stream and are the tail of detect: their
+        // candidates are ordered and oriented by ONE launch each, after the last of them has
+        // been scanned (two launches of ~10 / ~27 us per octave otherwise).
+        const bool tiny_group = tiny_from >= 0 && o >= tiny_from && !slab;
+        if (tiny_group && o + 1 < noct) continue;
+        const int ob = tiny_group ? tiny_from : o;
         if (launch_order_all(so, (const Cand *) ctx->cand_raw.p, (Cand *) ctx->cand_sorted.p,
                              ctx->cand_base.data(), ctx->cand_cap.data(), noct,
-                             (const int *) ctx->counts.p, &ctx->launches, o, o + 1, &ctx->order_scratch))
+                             (const int *) ctx->counts.p, &ctx->launches, ob, o + 1, &ctx->order_scratch))
             return -1;
         if (o == 0 && mark(ctx->ev[EV_ORDER])) return -1;
         if (launch_orient_all(so, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
-                              (const int *) ctx->counts.p, (int *) ctx->work.p + o, corner_thresh,
-                              ctx->kps_dev(), &ctx->launches, o, o + 1,
+                              (const int *) ctx->counts.p, (int *) ctx->work.p + ob, corner_thresh,
+                              ctx->kps_dev(), &ctx->launches, ob, o + 1,
                               ctx->kps_host ? ctx->kflags_host : nullptr))
             return -1;
-        if (so != st) S3D_CK(cudaEventRecord(ctx->ev_done[o], so));
+        if (so != st)
+            for (int od = ob; od <= o; od++) S3D_CK(cudaEventRecord(ctx->ev_done[od], so));
     }
     if (!serial)
         for (int o = 1; o < noct; o++) S3D_CK(cudaStreamWaitEvent(st, ctx->ev_done[o], 0));
