@@ -771,8 +771,13 @@ int launch_blur(cudaStream_t st, const float *src, float *dst, float *tmp_a, flo
         // not taken after all: the generic path below divides on load from the original
     }
 
-    // Fused single-launch path for tap spacing 1/2 on every axis (octave 1).
-    if (!force_generic && fused_ok && symmetric && ax.uf == 0.5f && ay.uf == 0.5f && az.uf == 0.5f && hw >= 1 &&
+    // Fused single-launch path for tap spacing 1/2 on every axis (octave 1): exact mode. In fast mode
+    // the three banded passes below take octave 1 as well -- its levels (8 MB at 256^3) stay in L2
+    // between the passes and the banded form is far fewer instructions than the upsampled-line
+    // construction of this kernel: 256^3 step 1.97 -> 1.90 ms per volume ($SIFT3D_CUDA_HALF_FUSED=1:
+    // the fused kernel in fast mode too).
+    static const bool half_fused = getenv("SIFT3D_CUDA_HALF_FUSED") != nullptr;
+    if ((exact || half_fused) && !force_generic && fused_ok && symmetric && ax.uf == 0.5f && ay.uf == 0.5f && az.uf == 0.5f && hw >= 1 &&
         hw <= 8 && d_divisor == nullptr && nx % 4 == 0 && nx >= kFTX && ny >= ty_half && nx < (1 << 20) &&
         ny < (1 << 20) && nz < (1 << 20) && ny >= hw + 3 && nz >= hw + 3 &&
         ((uintptr_t) src & 15) == 0 && (d_dogmax_slot == nullptr || dog_prev == src)) {

@@ -90,8 +90,7 @@ def test_banded_blur_vs_reference(det, dims, units, sigma):
     launches = det.launch_count() - l0
     rel, _ = parity.level_error(got, want)
     assert rel <= FAST_BLUR_REL_TOL, f"max rel err {rel:.3g}"
-    if units != (2, 2, 2):  # (spacing 1/2 has a fused kernel of its own where the shape allows)
-        assert launches == 3  # (lines shorter than their band still fit one: the band is then the line)
+    assert launches == 3  # (lines shorter than their band still fit one: the band is then the line)
 
 
 @pytest.mark.parametrize("exact", [True, False], ids=["exact", "fast"])
@@ -141,13 +140,17 @@ def test_fused_half_blur_bit_exact(det, dims, sigma):
     vol = rng.standard_normal((nz, ny, nx)).astype(np.float32)
     taps = _gauss_taps(sigma)
     want = ref.ref_blur(vol, (2, 2, 2), taps)
-    l0 = det.launch_count()
-    got = det.blur(vol, (2, 2, 2), taps)
-    assert det.launch_count() - l0 == 1  # the fused spacing-1/2 kernel, not the generic passes
-    rel, nbits = parity.level_error(got, want)
-    assert nbits == 0, f"{nbits} voxels differ (max rel err {rel:.3g})"
-    gen = det.blur(vol, (2, 2, 2), taps, force_generic=True)
-    assert parity.level_error(gen, want)[1] == 0
+    det.set_exact(True)  # (the fast mode runs octave 1 on the banded passes: test_banded_blur_vs_reference)
+    try:
+        l0 = det.launch_count()
+        got = det.blur(vol, (2, 2, 2), taps)
+        assert det.launch_count() - l0 == 1  # the fused spacing-1/2 kernel, not the generic passes
+        rel, nbits = parity.level_error(got, want)
+        assert nbits == 0, f"{nbits} voxels differ (max rel err {rel:.3g})"
+        gen = det.blur(vol, (2, 2, 2), taps, force_generic=True)
+        assert parity.level_error(gen, want)[1] == 0
+    finally:
+        det.set_exact(False)
 
 
 CASES = [
