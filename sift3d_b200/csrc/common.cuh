@@ -181,7 +181,8 @@ int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d
                       const int *d_counts, int *d_work, double corner_thresh,
                       sift3d_cuda_keypoint *d_out, uint64_t *launches,
                       int o_begin = 0, int o_end = -1,   // octaves [o_begin, o_end); own d_work slot
-                      sift3d_cuda_candidate_flag *d_flags = nullptr);  // (strength, valid) per slot, or NULL
+                      sift3d_cuda_candidate_flag *d_flags = nullptr,  // (strength, valid) per slot, or NULL
+                      bool shared_device = false);  // other detectors run on this device: small grids
 
 // descriptor.cu
 struct DescJob {

@@ -9,6 +9,7 @@
 //   IM_LOOP_SPHERE_START       :86-109     window bounds and physical-unit displacement
 //   IM_GET_GRAD_ISO            :140-145    central differences / units
 //   assign_orientation_thresh  :1091-1102  reject if corner score < corner_thresh
+#include <string.h>
 #include <float.h>
 
 #include "common.cuh"
@@ -466,7 +467,7 @@ int launch_orient_tables(cudaStream_t st, OrientPlan &h, int kp, OrientEntry *d_
 int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d_plan,
                       const int *d_counts, int *d_work, double corner_thresh,
                       sift3d_cuda_keypoint *d_out, uint64_t *launches, int o_begin, int o_end,
-                      sift3d_cuda_candidate_flag *d_flags) {
+                      sift3d_cuda_candidate_flag *d_flags, bool shared_device) {
     if (o_end < 0) o_end = SIFT3D_CUDA_MAX_OCTAVES;
     if (o_end <= o_begin) return 0;
     // persistent grid: 148 SMs x the CTAs that fit (94 registers x 128 threads -> 5 per SM)
@@ -477,8 +478,16 @@ int launch_orient_all(cudaStream_t st, const Cand *d_sorted, const OrientPlan *d
     // candidate counts (6.3k window voxels over 128 threads = 50 dependent load steps, 40 us),
     // so their CTAs are four times as wide.
     static const int wide_env = getenv("SIFT3D_CUDA_ORIENT_WIDE") ? atoi(getenv("SIFT3D_CUDA_ORIENT_WIDE")) : 0;
+    // The kernel is latency-bound (table entry -> voxel loads) and its persistent grid reserves
+    // the registers of the SMs it sits on: 5 CTAs per SM (8 short ones for the other octaves) is
+    // the fastest for a detector that has the device to itself (2.30 against 2.33 ms per 256^3
+    // volume), 2 per SM leaves room for the kernels of the other pipelines of the device (four
+    // pipelines: 9.04 against 8.77 Gvox/s). $SIFT3D_CUDA_ORIENT_CTAS="a,b" forces both values.
+    static const char *ce = getenv("SIFT3D_CUDA_ORIENT_CTAS");
+    const int cta0 = ce ? atoi(ce) : (shared_device ? 2 : 5);
+    const int cta1 = ce && strchr(ce, ',') ? atoi(strchr(ce, ',') + 1) : (shared_device ? 2 : 8);
     if (o_begin == 0 || !wide_env)
-        orient_all_kernel<128><<<o_begin == 0 ? kNumSMs * 5 : kNumSMs * 8, 128, 0, st>>>(
+        orient_all_kernel<128><<<o_begin == 0 ? kNumSMs * cta0 : kNumSMs * cta1, 128, 0, st>>>(
             d_sorted, d_plan, d_counts, d_work, corner_thresh, d_out, o_begin, o_end, d_flags);
     else
         orient_all_kernel<512><<<kNumSMs * 2, 512, 0, st>>>(d_sorted, d_plan, d_counts, d_work, corner_thresh,

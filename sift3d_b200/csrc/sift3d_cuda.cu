@@ -4,6 +4,8 @@
 // descriptors can be extracted later" (sift3d/sift.c:1622-1628).
 #include <math.h>
 #include <stdlib.h>
+
+#include <atomic>
 #include <string.h>
 
 #include <algorithm>
@@ -68,7 +70,8 @@ struct sift3d_cuda_ctx {
     // dimensions changed" point (sift.c:651-656) -- and replayed from then on.
     bool use_graph = true;              // $SIFT3D_CUDA_NO_GRAPH switches it off
     cudaGraphExec_t graph_exec = nullptr;
-    double graph_key[12] = {};
+    double graph_key[13] = {};
+    bool counted = false;               // in g_live_ctx
     int graph_key_runs = 0;             // eager runs seen with graph_key
     uint64_t graph_launches = 0;        // kernel launches inside the graph
     uint64_t plan_gen = 0;              // bumped whenever device buffers may have moved
@@ -141,6 +144,12 @@ int sift3d_cuda_device_count(void) {
     return n;
 }
 
+// Contexts alive per device (pipelines sharing a GPU, see detect_impl).
+static std::atomic<int> g_live_ctx[SIFT3D_CUDA_MULTI_MAX_DEVICES];
+static int live_contexts(int device) {
+    return device >= 0 && device < SIFT3D_CUDA_MULTI_MAX_DEVICES ? g_live_ctx[device].load() : 1;
+}
+
 sift3d_cuda_ctx *sift3d_cuda_ctx_create(int device) {
     int n = sift3d_cuda_device_count();
     if (n <= 0) {
@@ -186,11 +195,16 @@ sift3d_cuda_ctx *sift3d_cuda_ctx_create(int device) {
         sift3d_cuda_ctx_destroy(ctx);
         return nullptr;
     }
+    if (ctx->device >= 0 && ctx->device < SIFT3D_CUDA_MULTI_MAX_DEVICES) {
+        g_live_ctx[ctx->device]++;
+        ctx->counted = true;
+    }
     return ctx;
 }
 
 void sift3d_cuda_ctx_destroy(sift3d_cuda_ctx *ctx) {
     if (!ctx) return;
+    if (ctx->counted) g_live_ctx[ctx->device]--;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
@@ -767,11 +781,15 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
     static const int reserve_env = getenv("SIFT3D_CUDA_RESERVE") ? atoi(getenv("SIFT3D_CUDA_RESERVE")) : 14;
     static const int reserve_first = getenv("SIFT3D_CUDA_RESERVE_FIRST") ? atoi(getenv("SIFT3D_CUDA_RESERVE_FIRST")) : 40;
     const bool graph_eligible = ctx->use_graph && !slab && !from_seed && !serial && !ctx->profiling && attempt == 0;
+    // other detectors (pipelines) live on this device: latency-bound persistent kernels then keep
+    // their grids small so that the other pipelines' kernels fit next to them (launch_orient_all)
+    const bool shared_device = live_contexts(ctx->device) > 1;
     bool replay = false, capturing = false;
     if (graph_eligible) {
-        const double key[12] = {(double) ctx->plan_gen, units[0], units[1], units[2], peak_thresh, corner_thresh,
+        const double key[13] = {(double) ctx->plan_gen, units[0], units[1], units[2], peak_thresh, corner_thresh,
                                 ctx->exact ? 1.0 : 0.0, (double) ctx->base_octave, ctx->orient_tab_ok ? 1.0 : 0.0,
-                                (double) (uintptr_t) ctx->orient_tab.p, (double) reserve_env, (double) reserve_first};
+                                (double) (uintptr_t) ctx->orient_tab.p, (double) reserve_env, (double) reserve_first,
+                                shared_device ? 1.0 : 0.0};
         if (memcmp(key, ctx->graph_key, sizeof(key)) != 0) {
             if (ctx->graph_exec) cudaGraphExecDestroy(ctx->graph_exec);
             ctx->graph_exec = nullptr;
@@ -866,7 +884,7 @@ static int detect_impl(sift3d_cuda_ctx *ctx, const float *image, int image_on_de
         if (launch_orient_all(so, (const Cand *) ctx->cand_sorted.p, (const OrientPlan *) ctx->orient_plan.p,
                               (const int *) ctx->counts.p, (int *) ctx->work.p + ob, corner_thresh,
                               ctx->kps_dev(), &ctx->launches, ob, o + 1,
-                              ctx->kps_host ? ctx->kflags_host : nullptr))
+                              ctx->kps_host ? ctx->kflags_host : nullptr, shared_device))
             return -1;
         if (so != st)
             for (int od = ob; od <= o; od++) S3D_CK(cudaEventRecord(ctx->ev_done[od], so));
