@@ -369,6 +369,10 @@ def run_product_arm(args):
     # describe; cli/kpSift3D.c:116-135), C3 = 512 x 512 x 300 with anisotropic units
     extras = None
     if rank == 0 and world == 1 and not os.environ.get("SIFT3D_BENCH_NO_EXTRAS"):
+        # these are single-detector figures: the pipelines' detectors are released first (a
+        # detector that shares its device launches smaller persistent grids)
+        for d in dets:
+            d.close()
         extras = run_other_configs(local)
 
     if rank != 0:
